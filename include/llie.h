@@ -1,0 +1,141 @@
+/*
+ * llie.h -- C ABI of libllie.so: B200-native MSRCR Retinex and Zero-DCE.
+ *
+ * Drop-in boundary.  The reference (CILAB-IITM/Low_Light_Image_Enhancement) has no
+ * code, operator or FFI interface at all (/root/reference/README.md:1-2 is the whole
+ * repository), so there is no reference entry point for any function below to
+ * "replace".  The boundary is the one BASELINE.json#north_star names -- "Host code is
+ * Python calling CUDA through a thin C-ABI (ctypes) layer, exposing one
+ * enhance(images, method, params) operator" -- with the concrete contract of
+ * SURVEY.md section 8(b).  Each export cites the north_star / SURVEY clause it realises.
+ *
+ * Conventions: plain C types only; every function returns an int status (0 = OK,
+ * negative = LLIE_E_*); nothing throws, aborts or prints; llie_last_error() gives the
+ * thread-local text of the last failure.  All image pointers are DEVICE pointers
+ * unless the name says "host".  There is NO CPU fallback: a build without CUDA kernels
+ * or a box without a B200 fails with LLIE_E_CUDA.
+ */
+#ifndef LLIE_H_
+#define LLIE_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define LLIE_VERSION 100 /* 0.1.0 */
+
+/* status codes (SURVEY.md 8(b) "errors") */
+#define LLIE_OK 0
+#define LLIE_E_ARG (-1)
+#define LLIE_E_SHAPE (-2)
+#define LLIE_E_DTYPE (-3)
+#define LLIE_E_CUDA (-4)
+#define LLIE_E_NOPEER (-5)
+#define LLIE_E_NOMEM (-6)
+#define LLIE_E_STATE (-7)
+
+/* layouts of an image batch */
+#define LLIE_NHWC 0 /* (N,H,W,3) interleaved RGB */
+#define LLIE_NCHW 1 /* (N,3,H,W) planar */
+
+/* element types of Zero-DCE image I/O and arithmetic path */
+#define LLIE_F32 0  /* fp32 I/O, fp32 CUDA-core arithmetic (config 1)            */
+#define LLIE_BF16 1 /* fp32 I/O, bf16 operands on tcgen05, fp32 accumulate (config 2) */
+
+/* MSRCR surround-blur algorithms */
+#define LLIE_BLUR_PYRAMID 0 /* multi-resolution Gaussian cascade, O(1) per pixel in sigma */
+#define LLIE_BLUR_DIRECT 1  /* exact truncated FIR, O(sigma) per pixel; GPU ground truth   */
+
+#define LLIE_MAX_SCALES 8
+
+/* north_star (a): "multi-scale Gaussian surround at sigma=15/80/250, log-ratio, colour
+ * restoration and gain/offset"; defaults pinned by SURVEY.md 9.1. */
+typedef struct llie_msrcr_params {
+  uint32_t struct_size; /* = sizeof(llie_msrcr_params) */
+  int32_t n_scales;
+  float sigma[LLIE_MAX_SCALES];
+  float weight[LLIE_MAX_SCALES];
+  float truncate; /* kernel radius = ceil(truncate * sigma) */
+  float alpha, beta, gain, offset;
+  float in_scale, in_bias; /* I = in_scale * x + in_bias */
+  int32_t blur;            /* LLIE_BLUR_* */
+} llie_msrcr_params;
+
+/* north_star (b): "8 iterations of LE(x)=x+alpha*x*(1-x)"; SURVEY.md 9.2. */
+typedef struct llie_dce_params {
+  uint32_t struct_size; /* = sizeof(llie_dce_params) */
+  int32_t iters;        /* curve iterations; the net always emits 3*8 maps, iters <= 8 */
+  int32_t curve_sign;   /* +1: x + a x (1-x) (north_star); -1: upstream convention */
+  int32_t precision;    /* LLIE_F32 or LLIE_BF16 */
+} llie_dce_params;
+
+typedef struct llie_ctx llie_ctx;
+
+/* library identity / diagnostics */
+int llie_version(void);
+const char* llie_last_error(void);
+/* fills *count with the number of CUDA devices; LLIE_E_CUDA if none (no CPU fallback) */
+int llie_device_count(int* count);
+
+/* Fill a params struct with the SURVEY.md section 9 defaults. */
+int llie_msrcr_default_params(llie_msrcr_params* p);
+int llie_dce_default_params(llie_dce_params* p);
+
+/* A context binds one device (SURVEY.md 8(b) "ownership": streams, workspaces and
+ * packed weights belong to the ctx; no allocation on the hot path after warm-up). */
+int llie_create(llie_ctx** out, int device);
+int llie_destroy(llie_ctx* ctx);
+int llie_sync(llie_ctx* ctx);
+/* bytes of device workspace currently held by the ctx */
+int llie_workspace_bytes(llie_ctx* ctx, size_t* bytes);
+/* kernels launched by this ctx since creation (bench.py's gpu_launches) */
+int llie_launch_count(llie_ctx* ctx, uint64_t* count);
+
+/* Per-kernel device timing for bench.py's roofline figure (SURVEY.md 8(d) "evidence"): between
+ * begin and end every kernel this ctx launches is bracketed by CUDA events on its launching
+ * stream.  end synchronises and writes "kernel_name:launches:total_ms;" records into buf. */
+int llie_profile_begin(llie_ctx* ctx);
+int llie_profile_end(llie_ctx* ctx, char* buf, size_t buflen);
+
+/* north_star kernel (1): MSRCR on a device batch. in/out: n*h*w*3 fp32 in `layout`,
+ * values in [0,1].  stream: cudaStream_t as void*; NULL = the ctx's own stream and a
+ * synchronous return.  out may not alias in. */
+int llie_msrcr_f32(llie_ctx* ctx, const float* in, float* out, int n, int h, int w, int layout,
+                   const llie_msrcr_params* params, void* stream);
+
+/* Host-side planner of the pyramid blur, exposed so that CPU tests can check it without a
+ * GPU: for `sigma`/`truncate` returns the pyramid level stride (2 or 16), the low-res
+ * Gaussian's sigma and radius, and the L1 distance between the cascade's effective kernel
+ * and the oracle's truncated Gaussian.  Needs no device. */
+int llie_msrcr_plan_query(float sigma, float truncate, int* stride, double* sigma_low, int* radius_low,
+                          double* l1_error);
+
+/* north_star kernel (2): upload DCE-Net weights.  host_packed: the 79 416-float blob
+ * W1 b1 ... W7 b7 (OIHW) of SURVEY.md 9.2, in HOST memory. */
+int llie_dce_set_weights(llie_ctx* ctx, const float* host_packed, size_t count);
+
+/* north_star kernels (2)+(3): Zero-DCE forward.  in/out: n*h*w*3 fp32 device arrays in
+ * `layout`; maps_or_null: optional n*h*w*24 fp32 output of the tanh curve maps (same
+ * layout family: NHWC -> (N,H,W,24), NCHW -> (N,24,H,W)). */
+int llie_dce_forward(llie_ctx* ctx, const float* in, float* out, float* maps_or_null, int n, int h, int w,
+                     int layout, const llie_dce_params* params, void* stream);
+
+/* north_star kernel (3) alone: curves from given maps (N,H,W,24)/(N,24,H,W) fp32. */
+int llie_dce_curves(llie_ctx* ctx, const float* in, const float* maps, float* out, int n, int h, int w,
+                    int layout, const llie_dce_params* params, void* stream);
+
+/* Row-tiled MSRCR of ONE image across several devices of this process (config 5):
+ * device d holds rows [row0[d], row0[d]+rows[d]) of the h_total x w image in
+ * in_shard[d]/out_shard[d] (NHWC fp32).  Low-resolution halo rows are exchanged with
+ * cudaMemcpyPeerAsync over NVLink (no NCCL).  ctxs[d] must live on distinct devices with
+ * peer access, or all on one device ("virtual devices" for single-GPU tests). */
+int llie_msrcr_tiled(llie_ctx* const* ctxs, int n_dev, const float* const* in_shard, float* const* out_shard,
+                     const int* row0, const int* rows, int h_total, int w, const llie_msrcr_params* params);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LLIE_H_ */

@@ -1,0 +1,13 @@
+"""llie-b200: B200-native MSRCR Retinex and Zero-DCE behind one operator, `enhance()`.
+
+Python is the host language BASELINE.json#north_star names; all compute happens in the
+hand-written sm_100a kernels of libllie.so, reached through the C ABI of include/llie.h.
+PyTorch is used only for device memory, pinned staging and streams.
+"""
+from .api import (enhance, Enhancer, default_msrcr_params, default_dce_params, init_dce_weights,
+                  shard_slice, plan_query)
+from ._lib import LlieError, LlieCudaError
+
+__all__ = ["enhance", "Enhancer", "default_msrcr_params", "default_dce_params", "init_dce_weights",
+           "shard_slice", "plan_query", "LlieError", "LlieCudaError"]
+__version__ = "0.1.0"

@@ -1,0 +1,409 @@
+"""The public operator: enhance(images, method, params) (BASELINE.json#north_star).
+
+The reference repository has no operator or plugin interface to mirror
+(/root/reference/README.md:1-2 is its entire content), so the interface is the one
+north_star specifies: one function accepting NumPy arrays or PyTorch tensors.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+import threading
+from typing import Any, Sequence
+
+import numpy as np
+import torch
+
+from . import _lib
+from ._lib import LlieError, MsrcrParams, DceParams
+
+DCE_LAYERS = ((32, 3), (32, 32), (32, 32), (32, 32), (32, 64), (32, 64), (24, 64))
+DCE_NUM_PARAMS = sum(co * ci * 9 + co for co, ci in DCE_LAYERS)
+
+
+def default_msrcr_params() -> dict:
+    """SURVEY.md 9.1 defaults (filled by the library so both sides agree)."""
+    p = MsrcrParams()
+    _lib.check(_lib.load().llie_msrcr_default_params(C.byref(p)))
+    n = p.n_scales
+    return dict(sigmas=tuple(p.sigma[:n]), weights=tuple(p.weight[:n]), truncate=p.truncate, alpha=p.alpha,
+                beta=p.beta, gain=p.gain, offset=p.offset, in_scale=p.in_scale, in_bias=p.in_bias, blur="pyramid")
+
+
+def default_dce_params() -> dict:
+    return dict(iters=8, curve_sign=1, precision="fp32", return_maps=False, weights=None)
+
+
+def init_dce_weights(seed: int = 0, last_gain: float = 1.0) -> np.ndarray:
+    """Random-init DCE-Net weights as the packed 79 416-float blob (SURVEY.md 8(d) 'DCE weights':
+    He-normal W ~ N(0, 2/(9 Cin)), b ~ U(-0.05, 0.05), drawn W1,b1,...,W7,b7 from default_rng(seed))."""
+    rng = np.random.default_rng(seed)
+    parts = []
+    for li, (co, ci) in enumerate(DCE_LAYERS):
+        w = rng.normal(0.0, np.sqrt(2.0 / (9.0 * ci)), size=(co, ci, 3, 3)).astype(np.float32)
+        b = rng.uniform(-0.05, 0.05, size=(co,)).astype(np.float32)
+        if li == len(DCE_LAYERS) - 1 and last_gain != 1.0:
+            w = (w * np.float32(last_gain)).astype(np.float32)
+        parts += [w.ravel(), b]
+    return np.concatenate(parts).astype(np.float32)
+
+
+def plan_query(sigma: float, truncate: float = 4.0) -> dict:
+    """Host-side planner of the pyramid blur (needs no GPU): stride, low-res sigma/radius, kernel L1 error."""
+    st, sl, rl, l1 = C.c_int(), C.c_double(), C.c_int(), C.c_double()
+    _lib.check(_lib.load().llie_msrcr_plan_query(float(sigma), float(truncate), C.byref(st), C.byref(sl),
+                                                 C.byref(rl), C.byref(l1)))
+    return dict(stride=st.value, sigma_low=sl.value, radius_low=rl.value, l1_error=l1.value)
+
+
+def shard_slice(n: int, rank: int, world: int) -> slice:
+    """Contiguous split of n independent images over `world` ranks: rank r gets
+    [r*n/world, (r+1)*n/world) with the remainder spread over the first ranks.  No collective."""
+    if world <= 0 or not (0 <= rank < world):
+        raise ValueError(f"bad rank/world {rank}/{world}")
+    base, rem = divmod(n, world)
+    start = rank * base + min(rank, rem)
+    return slice(start, start + base + (1 if rank < rem else 0))
+
+
+def _msrcr_struct(params: dict | None) -> MsrcrParams:
+    d = default_msrcr_params()
+    if params:
+        unknown = set(params) - set(d) - {"layout"}
+        if unknown:
+            raise ValueError(f"unknown msrcr params: {sorted(unknown)}")
+        d.update({k: v for k, v in params.items() if k != "layout"})
+    sig = [float(s) for s in d["sigmas"]]
+    wts = [float(w) for w in d["weights"]]
+    if len(sig) != len(wts) or not (1 <= len(sig) <= _lib.MAX_SCALES):
+        raise ValueError("sigmas and weights must have equal length in [1, 8]")
+    p = MsrcrParams()
+    p.struct_size = C.sizeof(MsrcrParams)
+    p.n_scales = len(sig)
+    for i, (s, w) in enumerate(zip(sig, wts)):
+        p.sigma[i], p.weight[i] = s, w
+    for k in ("truncate", "alpha", "beta", "gain", "offset", "in_scale", "in_bias"):
+        setattr(p, k, float(d[k]))
+    blur = d["blur"]
+    if blur not in ("pyramid", "direct"):
+        raise ValueError("blur must be 'pyramid' or 'direct'")
+    p.blur = _lib.BLUR_PYRAMID if blur == "pyramid" else _lib.BLUR_DIRECT
+    return p
+
+
+def _dce_struct(d: dict) -> DceParams:
+    p = DceParams()
+    p.struct_size = C.sizeof(DceParams)
+    p.iters = int(d["iters"])
+    p.curve_sign = int(d["curve_sign"])
+    prec = d["precision"]
+    if prec not in ("fp32", "bf16"):
+        raise ValueError("precision must be 'fp32' or 'bf16'")
+    p.precision = _lib.F32 if prec == "fp32" else _lib.BF16
+    return p
+
+
+def _resolve_layout(shape: Sequence[int], layout: str | None):
+    """Returns (n, h, w, layout_code, batched) for (H,W,3) / (N,H,W,3) / (N,3,H,W)."""
+    if len(shape) == 3:
+        if shape[2] != 3:
+            raise ValueError(f"3-D input must be (H, W, 3), got {tuple(shape)}")
+        if layout not in (None, "NHWC"):
+            raise ValueError("a 3-D image is (H, W, 3); layout must be NHWC")
+        return 1, shape[0], shape[1], _lib.NHWC, False
+    if len(shape) != 4:
+        raise ValueError(f"images must be (H,W,3), (N,H,W,3) or (N,3,H,W), got {tuple(shape)}")
+    nhwc_ok, nchw_ok = shape[3] == 3, shape[1] == 3
+    if layout is None:
+        if nhwc_ok and nchw_ok:
+            raise ValueError(f"shape {tuple(shape)} is ambiguous; pass params['layout'] = 'NHWC' or 'NCHW'")
+        layout = "NHWC" if nhwc_ok else "NCHW" if nchw_ok else None
+    if layout == "NHWC" and nhwc_ok:
+        return shape[0], shape[1], shape[2], _lib.NHWC, True
+    if layout == "NCHW" and nchw_ok:
+        return shape[0], shape[2], shape[3], _lib.NCHW, True
+    raise ValueError(f"shape {tuple(shape)} does not match layout {layout}")
+
+
+class Enhancer:
+    """One libllie context on one device plus the staging buffers NumPy callers need.
+
+    Not thread-safe: use one Enhancer per host thread.
+    """
+
+    def __init__(self, device: int | None = None):
+        self._lib = _lib.load()
+        n = C.c_int()
+        _lib.check(self._lib.llie_device_count(C.byref(n)))  # raises without a GPU: no CPU fallback
+        self.device = torch.cuda.current_device() if device is None else int(device)
+        h = C.c_void_p()
+        _lib.check(self._lib.llie_create(C.byref(h), self.device))
+        self._h = h
+        self._weights_key = None
+        self._stage: dict[str, torch.Tensor] = {}
+        self._copy_stream = None
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._lib.llie_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # -- diagnostics -------------------------------------------------------------------------
+    def launch_count(self) -> int:
+        c = C.c_uint64()
+        _lib.check(self._lib.llie_launch_count(self._h, C.byref(c)))
+        return c.value
+
+    def workspace_bytes(self) -> int:
+        c = C.c_size_t()
+        _lib.check(self._lib.llie_workspace_bytes(self._h, C.byref(c)))
+        return c.value
+
+    def profile_begin(self) -> None:
+        """Start per-kernel CUDA-event timing of everything this Enhancer launches."""
+        _lib.check(self._lib.llie_profile_begin(self._h))
+
+    def profile_end(self) -> dict:
+        """Stop timing; returns {kernel_name: (launches, total_ms)}."""
+        buf = C.create_string_buffer(1 << 16)
+        _lib.check(self._lib.llie_profile_end(self._h, buf, len(buf)))
+        out = {}
+        for rec in buf.value.decode().split(";"):
+            if rec:
+                name, cnt, ms = rec.split(":")
+                out[name] = (int(cnt), float(ms))
+        return out
+
+    # -- weights -----------------------------------------------------------------------------
+    def set_dce_weights(self, weights) -> None:
+        blob = _as_weight_blob(weights)
+        key = (blob.ctypes.data, blob.size, float(blob[:64].sum()), float(blob[-64:].sum()))
+        if key == self._weights_key:
+            return
+        _lib.check(self._lib.llie_dce_set_weights(self._h, blob.ctypes.data_as(C.POINTER(C.c_float)), blob.size))
+        self._weights_key, self._weights_ref = key, blob
+
+    # -- device-pointer entry points (zero-copy for torch CUDA tensors) -----------------------
+    def msrcr_device(self, x: torch.Tensor, out: torch.Tensor, n, h, w, layout, p: MsrcrParams, stream_ptr):
+        _lib.check(self._lib.llie_msrcr_f32(self._h, x.data_ptr(), out.data_ptr(), n, h, w, layout, C.byref(p),
+                                            stream_ptr))
+
+    def dce_device(self, x, out, maps, n, h, w, layout, p: DceParams, stream_ptr):
+        _lib.check(self._lib.llie_dce_forward(self._h, x.data_ptr(), out.data_ptr(),
+                                              maps.data_ptr() if maps is not None else None, n, h, w, layout,
+                                              C.byref(p), stream_ptr))
+
+    def dce_curves_device(self, x, maps, out, n, h, w, layout, p: DceParams, stream_ptr):
+        _lib.check(self._lib.llie_dce_curves(self._h, x.data_ptr(), maps.data_ptr(), out.data_ptr(), n, h, w,
+                                             layout, C.byref(p), stream_ptr))
+
+    # -- the operator ------------------------------------------------------------------------
+    def enhance(self, images, method: str, params: dict | None = None, *, out=None):
+        params = dict(params or {})
+        if method not in ("msrcr", "zero_dce"):
+            raise ValueError(f"method must be 'msrcr' or 'zero_dce', got {method!r}")
+        is_np = isinstance(images, np.ndarray)
+        if not is_np and not isinstance(images, torch.Tensor):
+            raise TypeError("images must be a numpy.ndarray or a torch.Tensor")
+        t = torch.from_numpy(images) if is_np else images
+        if t.dtype != torch.float32:
+            raise TypeError(f"images must be float32, got {t.dtype}")
+        if not t.is_contiguous():
+            raise ValueError("images must be contiguous")
+        n, h, w, layout, batched = _resolve_layout(t.shape, params.get("layout"))
+        if method == "msrcr":
+            mp, dp, want_maps = _msrcr_struct(params), None, False
+        else:
+            d = default_dce_params()
+            unknown = set(params) - set(d) - {"layout"}
+            if unknown:
+                raise ValueError(f"unknown zero_dce params: {sorted(unknown)}")
+            d.update({k: v for k, v in params.items() if k != "layout"})
+            if d["weights"] is None:
+                raise ValueError("zero_dce needs params['weights'] (packed blob or list of (W, b))")
+            self.set_dce_weights(d["weights"])
+            mp, dp, want_maps = None, _dce_struct(d), bool(d["return_maps"])
+
+        if t.is_cuda:
+            if t.device.index != self.device:
+                raise ValueError(f"tensor on cuda:{t.device.index}, Enhancer on cuda:{self.device}")
+            y = torch.empty_like(t) if out is None else out
+            _check_out(y, t)
+            maps = None
+            if want_maps:
+                mshape = (n, h, w, 24) if layout == _lib.NHWC else (n, 24, h, w)
+                maps = torch.empty(mshape if batched else mshape[1:], dtype=torch.float32, device=t.device)
+            sp = _stream_ptr(torch.cuda.current_stream(t.device))
+            if mp is not None:
+                self.msrcr_device(t, y, n, h, w, layout, mp, sp)
+            else:
+                self.dce_device(t, y, maps, n, h, w, layout, dp, sp)
+            return (y, maps) if want_maps else y
+
+        # host path: stage through pinned memory in frame chunks, overlapping H2D / compute / D2H
+        y_t = self._host_pipeline(t, n, h, w, layout, mp, dp, want_maps, out, is_np)
+        return y_t
+
+    def _pinned(self, name: str, nelem: int) -> torch.Tensor:
+        buf = self._stage.get(name)
+        if buf is None or buf.numel() < nelem:
+            buf = torch.empty(nelem, dtype=torch.float32, pin_memory=True)
+            self._stage[name] = buf
+        return buf[:nelem]
+
+    def _devbuf(self, name: str, nelem: int) -> torch.Tensor:
+        buf = self._stage.get(name)
+        if buf is None or buf.numel() < nelem:
+            buf = torch.empty(nelem, dtype=torch.float32, device=f"cuda:{self.device}")
+            self._stage[name] = buf
+        return buf[:nelem]
+
+    def _host_pipeline(self, t, n, h, w, layout, mp, dp, want_maps, out, is_np):
+        dev = torch.device("cuda", self.device)
+        frame = h * w * 3
+        x_flat = t.reshape(-1)
+        if out is None:
+            y_host = torch.empty(t.shape, dtype=torch.float32)
+        else:
+            y_host = torch.from_numpy(out) if isinstance(out, np.ndarray) else out
+            _check_out(y_host, t)
+        y_flat = y_host.reshape(-1)
+        maps_host = None
+        if want_maps:
+            mshape = (n, h, w, 24) if layout == _lib.NHWC else (n, 24, h, w)
+            maps_host = torch.empty(mshape if t.dim() == 4 else mshape[1:], dtype=torch.float32)
+        in_pinned, out_pinned = x_flat.is_pinned(), y_flat.is_pinned()
+        # chunk: about 64 MiB of input per stage, at least one frame
+        per = max(1, min(n, (64 << 20) // (frame * 4)))
+        n_chunks = math.ceil(n / per)
+        if self._copy_stream is None:
+            self._copy_stream = [torch.cuda.Stream(dev) for _ in range(2)]
+        h2d, d2h = self._copy_stream
+        comp = torch.cuda.current_stream(dev)
+        xd = [self._devbuf(f"x{i}", per * frame) for i in range(2)]
+        yd = [self._devbuf(f"y{i}", per * frame) for i in range(2)]
+        md = [self._devbuf(f"m{i}", per * frame * 8) for i in range(2)] if want_maps else [None, None]
+        xp = None if in_pinned else [self._pinned(f"xp{i}", per * frame) for i in range(2)]
+        yp = None if out_pinned else [self._pinned(f"yp{i}", per * frame) for i in range(2)]
+        ev_in = [torch.cuda.Event() for _ in range(2)]
+        ev_comp = [torch.cuda.Event() for _ in range(2)]
+        ev_out = [torch.cuda.Event() for _ in range(2)]
+        pending = []  # (slot, lo, hi) whose D2H has been issued into a pinned stage
+        for ci in range(n_chunks):
+            s = ci & 1
+            lo, hi = ci * per, min(n, (ci + 1) * per)
+            cnt = (hi - lo) * frame
+            if ci >= 2:
+                ev_out[s].synchronize()            # slot s: its previous D2H is done
+                self._drain(pending, y_flat, yp, frame, upto_slot=s)
+            src = x_flat[lo * frame:hi * frame]
+            if not in_pinned:
+                xp[s][:cnt].copy_(src)             # pageable -> pinned staging (host memcpy)
+                src = xp[s][:cnt]
+            with torch.cuda.stream(h2d):
+                h2d.wait_event(ev_comp[s])         # compute that last read xd[s] has finished
+                xd[s][:cnt].copy_(src, non_blocking=True)
+                ev_in[s].record(h2d)
+            comp.wait_event(ev_in[s])
+            comp.wait_event(ev_out[s])             # previous D2H out of yd[s] has finished
+            nb = hi - lo
+            if mp is not None:
+                self.msrcr_device(xd[s], yd[s], nb, h, w, layout, mp, _stream_ptr(comp))
+            else:
+                self.dce_device(xd[s], yd[s], md[s], nb, h, w, layout, dp, _stream_ptr(comp))
+            ev_comp[s].record(comp)
+            with torch.cuda.stream(d2h):
+                d2h.wait_event(ev_comp[s])
+                dst = y_flat[lo * frame:hi * frame] if out_pinned else yp[s][:cnt]
+                dst.copy_(yd[s][:cnt], non_blocking=True)
+                if want_maps:
+                    maps_host.reshape(-1)[lo * frame * 8:hi * frame * 8].copy_(md[s][:cnt * 8])
+                ev_out[s].record(d2h)
+            if not out_pinned:
+                pending.append((s, lo, hi))
+        d2h.synchronize()
+        self._drain(pending, y_flat, yp, frame, upto_slot=None)
+        y = y_host.numpy() if is_np else y_host
+        if want_maps:
+            return y, (maps_host.numpy() if is_np else maps_host)
+        return y
+
+    @staticmethod
+    def _drain(pending, y_flat, yp, frame, upto_slot):
+        keep = []
+        for (s, lo, hi) in pending:
+            if upto_slot is None or s == upto_slot:
+                y_flat[lo * frame:hi * frame].copy_(yp[s][:(hi - lo) * frame])
+            else:
+                keep.append((s, lo, hi))
+        pending[:] = keep
+
+
+def _stream_ptr(stream: torch.cuda.Stream) -> int:
+    """cudaStream_t for the C ABI.  torch's default stream is the NULL stream, which llie.h reserves
+    for "the ctx's own stream, synchronous"; pass CUDA's explicit legacy-stream handle instead so the
+    work stays ordered with the caller's torch ops."""
+    p = stream.cuda_stream
+    return p if p else 0x1  # cudaStreamLegacy
+
+
+def _check_out(y: torch.Tensor, t: torch.Tensor) -> None:
+    if y.shape != t.shape or y.dtype != torch.float32 or not y.is_contiguous() or y.device != t.device:
+        raise ValueError("out must match images in shape, dtype (float32), device and be contiguous")
+    if y.data_ptr() == t.data_ptr():
+        raise ValueError("out must not alias images")
+
+
+def _as_weight_blob(weights) -> np.ndarray:
+    if isinstance(weights, torch.Tensor):
+        weights = weights.detach().cpu().numpy()
+    if isinstance(weights, np.ndarray):
+        blob = np.ascontiguousarray(weights, dtype=np.float32).ravel()
+    else:  # list of (W, b)
+        blob = np.concatenate([np.concatenate([np.asarray(w, np.float32).ravel(), np.asarray(b, np.float32).ravel()])
+                               for w, b in weights]).astype(np.float32)
+    if blob.size != DCE_NUM_PARAMS:
+        raise ValueError(f"DCE-Net weight blob must hold {DCE_NUM_PARAMS} floats, got {blob.size}")
+    return blob
+
+
+_tls = threading.local()
+
+
+def _enhancer(device: int) -> Enhancer:
+    cache = getattr(_tls, "cache", None)
+    if cache is None:
+        cache = _tls.cache = {}
+    e = cache.get(device)
+    if e is None:
+        e = cache[device] = Enhancer(device)
+    return e
+
+
+def enhance(images, method: str, params: dict | None = None, *, out=None, device: int | None = None):
+    """Enhance a low-light image batch on a B200.
+
+    images : numpy.ndarray or torch.Tensor, float32 in [0, 1], shape (H,W,3), (N,H,W,3) or
+             (N,3,H,W) (params['layout'] = 'NHWC' | 'NCHW' when the shape is ambiguous).
+             CUDA tensors are processed in place on their device and stream (zero copy); NumPy
+             arrays and CPU tensors are staged through pinned memory.
+    method : 'msrcr'  -- params: sigmas, weights, truncate, alpha, beta, gain, offset, in_scale,
+                         in_bias, blur ('pyramid' | 'direct')
+             'zero_dce' -- params: weights (79 416-float blob or [(W, b)] * 7), iters, curve_sign,
+                         precision ('fp32' | 'bf16'), return_maps
+    Returns an array/tensor of the input's type, shape and device (and the 24 curve maps when
+    return_maps is set).  Raises LlieError on any library failure; there is no CPU fallback.
+    """
+    if isinstance(images, torch.Tensor) and images.is_cuda:
+        device = images.device.index
+    elif device is None:
+        n = C.c_int()
+        _lib.check(_lib.load().llie_device_count(C.byref(n)))
+        device = torch.cuda.current_device()
+    return _enhancer(device).enhance(images, method, params, out=out)

@@ -1,0 +1,101 @@
+// Generic edge-clamped 1-D FIR kernels (fp32) shared by the exact MSRCR path (msrcr_direct.cu)
+// and the low-resolution stages of the pyramid path (msrcr_pyramid.cu).
+#pragma once
+#include "llie_common.cuh"
+
+namespace llie {
+namespace {
+
+constexpr int kFold = 64;  // taps accumulated locally before folding into the running sum
+
+// FIR along x.  Data is `rows` rows of W pixels with C interleaved channels (C=3: NHWC image
+// rows; C=1: NCHW plane rows).  Each thread produces 4 consecutive pixels of one channel with a
+// sliding set of 4 weights, reading the clamped input segment from shared memory.
+template <bool kAffine>
+__global__ void __launch_bounds__(128) fir_x_kernel(const float* __restrict__ in, float* __restrict__ out,
+                                                    const float* __restrict__ taps, int r, int W, int C,
+                                                    float a, float b) {
+  extern __shared__ float seg[];
+  const int TX = 128;
+  const int x0 = blockIdx.y * TX;
+  const long long row = blockIdx.x;
+  const float* src = in + row * (long long)W * C;
+  const int seg_px = TX + 2 * r + 3;
+  for (int i = threadIdx.x; i < seg_px * C; i += blockDim.x) {
+    int px = i / C, c = i - px * C;
+    int x = min(max(x0 - r + px, 0), W - 1);
+    float v = src[(long long)x * C + c];
+    seg[i] = kAffine ? fmaf(a, v, b) : v;
+  }
+  __syncthreads();
+  const int groups = TX / 4;
+  for (int t = threadIdx.x; t < groups * C; t += blockDim.x) {
+    int g = t / C, c = t - g * C;
+    float acc[4] = {0.f, 0.f, 0.f, 0.f};
+    float k1 = 0.f, k2 = 0.f, k3 = 0.f;
+    const float* s = seg + (g * 4) * C + c;
+    const int n_steps = 2 * r + 4;
+    for (int u0 = 0; u0 < n_steps; u0 += kFold) {
+      float p[4] = {0.f, 0.f, 0.f, 0.f};
+      int u1 = min(u0 + kFold, n_steps);
+      for (int u = u0; u < u1; ++u) {
+        float v = s[u * C];
+        float k0 = (u <= 2 * r) ? taps[u] : 0.f;
+        p[0] = fmaf(k0, v, p[0]);
+        p[1] = fmaf(k1, v, p[1]);
+        p[2] = fmaf(k2, v, p[2]);
+        p[3] = fmaf(k3, v, p[3]);
+        k3 = k2; k2 = k1; k1 = k0;
+      }
+#pragma unroll
+      for (int j = 0; j < 4; ++j) acc[j] += p[j];
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      int x = x0 + g * 4 + j;
+      if (x < W) out[(row * W + x) * C + c] = acc[j];
+    }
+  }
+}
+
+// FIR along y on `planes` planes stored as in_rows x RW (input) and out_rows x RW (output).
+// Rows are addressed by their index in a level of H rows: buffer row b of the input holds level
+// row in_row0 + b, and outputs are produced for level rows out_row0 .. out_row0+out_rows-1; taps
+// that fall outside [0, H) are clamped (the caller guarantees the clamped rows are in the buffer).
+// One image: in_row0 = out_row0 = 0, in_rows = out_rows = H.  4 consecutive rows per thread.
+__global__ void __launch_bounds__(128) fir_y_kernel(const float* __restrict__ in, float* __restrict__ out,
+                                                    const float* __restrict__ taps, int r, int H, int RW,
+                                                    int in_row0, int in_rows, int out_row0, int out_rows) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= RW) return;
+  const int yb = blockIdx.y * 4;           // first output buffer row of this thread
+  const int y0 = out_row0 + yb;            // its level row
+  const long long plane = blockIdx.z;
+  const float* src = in + plane * (long long)in_rows * RW + j;
+  float acc[4] = {0.f, 0.f, 0.f, 0.f};
+  float k1 = 0.f, k2 = 0.f, k3 = 0.f;
+  const int n_steps = 2 * r + 4;
+  for (int u0 = 0; u0 < n_steps; u0 += kFold) {
+    float p[4] = {0.f, 0.f, 0.f, 0.f};
+    int u1 = min(u0 + kFold, n_steps);
+    for (int u = u0; u < u1; ++u) {
+      int y = min(max(y0 - r + u, 0), H - 1) - in_row0;
+      float v = __ldg(src + (long long)y * RW);
+      float k0 = (u <= 2 * r) ? taps[u] : 0.f;
+      p[0] = fmaf(k0, v, p[0]);
+      p[1] = fmaf(k1, v, p[1]);
+      p[2] = fmaf(k2, v, p[2]);
+      p[3] = fmaf(k3, v, p[3]);
+      k3 = k2; k2 = k1; k1 = k0;
+    }
+#pragma unroll
+    for (int q = 0; q < 4; ++q) acc[q] += p[q];
+  }
+  float* dst = out + plane * (long long)out_rows * RW + j;
+#pragma unroll
+  for (int q = 0; q < 4; ++q)
+    if (yb + q < out_rows) dst[(long long)(yb + q) * RW] = acc[q];
+}
+
+}  // namespace
+}  // namespace llie

@@ -1,0 +1,135 @@
+// Shared host-side plumbing of libllie.so: error handling, the context object and its
+// workspace arena.  SURVEY.md 8(b): the ctx owns streams, workspaces and packed weights;
+// every failure becomes a status code, nothing throws across the C boundary.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+
+#include <cstdarg>
+#include <cstdint>
+#include <cstdio>
+#include <map>
+#include <string>
+#include <vector>
+
+#include "../../include/llie.h"
+
+namespace llie {
+
+void set_error(const char* fmt, ...);
+
+#define LLIE_CUDA_OK(expr)                                                                      \
+  do {                                                                                          \
+    cudaError_t _e = (expr);                                                                    \
+    if (_e != cudaSuccess) {                                                                    \
+      ::llie::set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__); \
+      return LLIE_E_CUDA;                                                                       \
+    }                                                                                           \
+  } while (0)
+
+#define LLIE_TRY(expr)        \
+  do {                        \
+    int _s = (expr);          \
+    if (_s != LLIE_OK) return _s; \
+  } while (0)
+
+#define LLIE_REQUIRE(cond, code, ...) \
+  do {                                \
+    if (!(cond)) {                    \
+      ::llie::set_error(__VA_ARGS__); \
+      return (code);                  \
+    }                                 \
+  } while (0)
+
+// Element (c, y, x) of one image lives at base + c*sc + y*sy + x*sx (in elements).
+struct ImgView {
+  long long sn, sc, sy, sx;
+};
+inline ImgView make_view(int layout, int c, int h, int w) {
+  ImgView v;
+  if (layout == LLIE_NHWC) {
+    v.sx = c; v.sc = 1; v.sy = (long long)w * c;
+  } else {
+    v.sx = 1; v.sc = (long long)h * w; v.sy = w;
+  }
+  v.sn = (long long)h * w * c;
+  return v;
+}
+
+struct MsrcrPlan;   // msrcr_pyramid.cu
+struct DceWeights;  // dce_weights.cu
+
+}  // namespace llie
+
+struct llie_ctx {
+  int device = 0;
+  int sm_count = 0;
+  cudaStream_t stream = nullptr;
+  uint64_t launches = 0;
+  std::map<std::string, std::pair<void*, size_t>> bufs;  // named workspaces, grown on demand
+  llie::MsrcrPlan* plan = nullptr;
+  llie::DceWeights* dce = nullptr;
+  // optional per-kernel timing (llie_profile_begin/end): one event pair per launch
+  bool profiling = false;
+  struct ProfRec { const char* name; cudaEvent_t e0, e1; };
+  std::vector<ProfRec> prof;
+  cudaEvent_t prof_pending = nullptr;
+
+  // Returns a device buffer of at least `bytes` under `name`; reallocates only when growing.
+  int workspace(const char* name, size_t bytes, void** out);
+  size_t workspace_total() const;
+};
+
+namespace llie {
+
+inline void prof_start(llie_ctx* ctx, cudaStream_t st) {
+  if (!ctx->profiling) return;
+  cudaEventCreate(&ctx->prof_pending);
+  cudaEventRecord(ctx->prof_pending, st);
+}
+
+inline int check_launch(llie_ctx* ctx, const char* what, cudaStream_t st = nullptr) {
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    set_error("launch of %s failed: %s", what, cudaGetErrorString(e));
+    return LLIE_E_CUDA;
+  }
+  ctx->launches++;
+  if (ctx->profiling && ctx->prof_pending) {
+    cudaEvent_t e1;
+    cudaEventCreate(&e1);
+    cudaEventRecord(e1, st);
+    ctx->prof.push_back({what, ctx->prof_pending, e1});
+    ctx->prof_pending = nullptr;
+  }
+  return LLIE_OK;
+}
+
+// Launch a kernel with error check, launch counting and optional event timing:
+//   LLIE_LAUNCH(ctx, stream, "name", kernel<<<grid, block, smem, stream>>>(args...));
+#define LLIE_LAUNCH(ctx, st, name, ...)                  \
+  do {                                                   \
+    ::llie::prof_start(ctx, st);                         \
+    __VA_ARGS__;                                         \
+    LLIE_TRY(::llie::check_launch(ctx, name, st));       \
+  } while (0)
+
+// kernels' host entry points (one per .cu)
+int msrcr_direct_run(llie_ctx* ctx, const float* in, float* out, int n, int h, int w, int layout,
+                     const llie_msrcr_params& p, cudaStream_t st);
+int msrcr_pyramid_run(llie_ctx* ctx, const float* in, float* out, int n, int h, int w, int layout,
+                      const llie_msrcr_params& p, cudaStream_t st);
+int msrcr_plan_query(float sigma, float truncate, int* stride, double* sigma_low, int* radius_low, double* l1);
+void msrcr_plan_free(MsrcrPlan* p);
+
+int dce_weights_upload(llie_ctx* ctx, const float* host_packed, size_t count);
+void dce_weights_free(DceWeights* w);
+int dce_forward_f32(llie_ctx* ctx, const float* in, float* out, float* maps, int n, int h, int w, int layout,
+                    const llie_dce_params& p, cudaStream_t st);
+int dce_forward_bf16(llie_ctx* ctx, const float* in, float* out, float* maps, int n, int h, int w, int layout,
+                     const llie_dce_params& p, cudaStream_t st);
+int dce_curves_run(llie_ctx* ctx, const float* in, const float* maps, ImgView maps_view, float* out, float* maps_out,
+                   int n, int h, int w, int layout, const llie_dce_params& p, cudaStream_t st);
+
+}  // namespace llie
