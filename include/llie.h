@@ -123,6 +123,10 @@ int llie_dce_set_weights(llie_ctx* ctx, const float* host_packed, size_t count);
 int llie_dce_forward(llie_ctx* ctx, const float* in, float* out, float* maps_or_null, int n, int h, int w,
                      int layout, const llie_dce_params* params, void* stream);
 
+/* Test hook: after a LLIE_BF16 forward, copies inter-layer activation `which` (1..6 = x1..x6 of
+ * SURVEY.md 9.2) of frame `frame` of the last processed chunk to HOST memory as fp32 [32][h][w]. */
+int llie_debug_dce_activation(llie_ctx* ctx, int which, int frame, float* host_out);
+
 /* north_star kernel (3) alone: curves from given maps (N,H,W,24)/(N,24,H,W) fp32. */
 int llie_dce_curves(llie_ctx* ctx, const float* in, const float* maps, float* out, int n, int h, int w,
                     int layout, const llie_dce_params* params, void* stream);

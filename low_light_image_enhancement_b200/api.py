@@ -180,6 +180,12 @@ class Enhancer:
                 out[name] = (int(cnt), float(ms))
         return out
 
+    def debug_dce_activation(self, which: int, frame: int, h: int, w: int) -> np.ndarray:
+        """Test hook: inter-layer activation x{which} (1..6) of the last bf16 forward as fp32 (32, h, w)."""
+        out = np.empty((32, h, w), np.float32)
+        _lib.check(self._lib.llie_debug_dce_activation(self._h, which, frame, out.ctypes.data_as(C.POINTER(C.c_float))))
+        return out
+
     # -- weights -----------------------------------------------------------------------------
     def set_dce_weights(self, weights) -> None:
         blob = _as_weight_blob(weights)

@@ -151,6 +151,7 @@ int llie_destroy(llie_ctx* ctx) {
   for (auto& kv : ctx->bufs) cudaFree(kv.second.first);
   msrcr_plan_free(ctx->plan);
   dce_weights_free(ctx->dce);
+  dce_tc_release(ctx);
   if (ctx->stream) cudaStreamDestroy(ctx->stream);
   delete ctx;
   return LLIE_OK;
@@ -276,6 +277,12 @@ int llie_dce_forward(llie_ctx* ctx, const float* in, float* out, float* maps_or_
   LLIE_TRY(rc);
   if (!stream) LLIE_CUDA_OK(cudaStreamSynchronize(st));
   return LLIE_OK;
+}
+
+int llie_debug_dce_activation(llie_ctx* ctx, int which, int frame, float* host_out) {
+  LLIE_REQUIRE(ctx, LLIE_E_ARG, "null ctx");
+  DeviceGuard g(ctx->device);
+  return dce_debug_activation(ctx, which, frame, host_out);
 }
 
 int llie_dce_curves(llie_ctx* ctx, const float* in, const float* maps, float* out, int n, int h, int w, int layout,

@@ -54,6 +54,21 @@ def main():
                 mse = float(np.mean((y.astype(np.float64) - ref) ** 2))
                 print(f"dce {prec} {w}x{h} out max-abs {np.abs(y - ref).max():.3e} maps max-abs {np.abs(m - A).max():.3e} "
                       f"PSNR {10*np.log10(1/max(mse,1e-30)):.1f} dB")
+        if "tcdebug" in which:
+            sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests"))
+            from bf16_emulation import dce_activations_bf16
+            from low_light_image_enhancement_b200.api import _enhancer
+            for (h, w, seed) in ((20, 40, 4), (70, 200, 5)):
+                x = oracle.synth_lowlight(h, w, seed) * 6
+                acts, Aem = dce_activations_bf16(x, ws)
+                y, m = L.enhance(torch.from_numpy(x).cuda(), "zero_dce", dict(weights=blob, precision="bf16", return_maps=True))
+                e = _enhancer(0)
+                for i in range(6):
+                    g = e.debug_dce_activation(i + 1, 0, h, w)
+                    d = np.abs(g - acts[i]); k = np.unravel_index(d.argmax(), d.shape)
+                    print(f"  tc {w}x{h} x{i+1}: max-abs {d.max():.3e} (ref max {np.abs(acts[i]).max():.3f}) at c,y,x={k} frac>1e-2 {(d>1e-2).mean():.4f}")
+                mm = m.cpu().numpy(); d = np.abs(mm - Aem.transpose(1, 2, 0))
+                print(f"  tc {w}x{h} maps: max-abs {d.max():.3e}")
         x = torch.from_numpy(oracle.synth_lowlight(1080, 1920, 3)).cuda()[None]
         for prec, nb in (("fp32", 1), ("bf16", 1), ("bf16", 8)):
             xb = x.repeat(nb, 1, 1, 1)
