@@ -1,0 +1,427 @@
+#!/usr/bin/env python
+"""Benchmark of the B200-native low-light enhancement hot path (BASELINE.json metric:
+"Mpixel/s at 1/2/4/8 B200 (Zero-DCE 1080p, MSRCR 4K); % HBM/TC roofline").
+
+    python bench.py --gpus N --steps K --warmup W [--workload c2|c3|c1|c0] [--impl reference]
+
+One process per GPU (torchrun for N > 1; ranks shard independent frames, no data-path
+collective -- torch.distributed is used only for the barrier and the max-over-ranks time).
+Rank 0 prints ONE JSON line.  Workloads (BASELINE.json configs[i] -> "ci"):
+  c2 (default) Zero-DCE bf16, 64 x 1920x1080 frames sharded over the N GPUs (strong scaling)
+  c3           MSRCR sigma 15/80/250 on 3840x2160 frames, 32 frames per GPU (weak scaling)
+  c1           Zero-DCE fp32, 1 x 1920x1080 (replicas only for N > 1)
+  c0           MSRCR on one 600x400 image (the oracle's own CPU-runnable case)
+The default line is c2 and carries short c3/c1 measurements under "also".
+
+Keys beyond the base contract: "roofline" (dominant kernel, CUDA-event time per launch measured
+inside the timed region), "cpu_baseline" (NumPy oracle on the box's host cores, bounded sample),
+"e2e" (same metric through enhance() with pinned HOST buffers, H2D/D2H inside the timed region),
+"clocks", "gpu_launches".  `--impl reference` times the self-written NumPy oracle (the reference
+repository holds no code: /root/reference/README.md:1-2) on the host cores instead.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+H1080, W1080 = 1080, 1920
+H4K, W4K = 2160, 3840
+C2_TOTAL_FRAMES = 64
+C3_FRAMES_PER_GPU = 32
+
+# algorithmic work per pixel (DESIGN.md "Kernels")
+FLOP_PER_PX = {"dce_conv_tc_k32_kernel": 2 * 32 * 32 * 9, "dce_conv_tc_k64_kernel": 2 * 64 * 32 * 9,
+               "dce_conv_tc_last_kernel": 2 * 64 * 24 * 9}
+DCE_TENSOR_FLOP_PER_PX = 156672          # conv2..conv7
+MSRCR_NORTH_STAR_BYTES_PER_PX = 108      # two-pass separable data flow
+# msrcr_final_kernel: reads x (12 B) + writes out (12 B) + the stride-2 surround of sigma=15 (3 B) per pixel;
+# the stride-16 surrounds of sigma=80/250 add 2 * 12/256 B
+MSRCR_FINAL_BYTES_PER_PX = 12 + 12 + 3 + 2 * 12 / 256.0
+
+
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return dict(hbm=float(d["hbm_gbs"]), tc_burst=float(d["bf16_tflops"]),
+                    tc_sustained=float(d.get("bf16_tflops_sustained", d["bf16_tflops"])), source="measured")
+    return dict(hbm=6650.0, tc_burst=1590.0, tc_sustained=1400.0, source="fallback")
+
+
+class ClockSampler:
+    """Samples SM clock and throttle reasons of one GPU every 100 ms while a timed region runs."""
+
+    def __init__(self, index: int):
+        self.index, self.samples, self.reasons, self.max_mhz = index, [], set(), None
+        self._stop = threading.Event()
+        self._thr = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self._nv = pynvml
+            self._h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self._h, pynvml.NVML_CLOCK_SM)
+        except Exception as e:  # noqa: BLE001
+            self._nv, self.error = None, repr(e)
+
+    _NAMES = {0x1: "gpu_idle", 0x2: "applications_clocks_setting", 0x4: "sw_power_cap", 0x8: "hw_slowdown",
+              0x10: "sync_boost", 0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown",
+              0x80: "hw_power_brake_slowdown", 0x100: "display_clock_setting"}
+
+    def _run(self):
+        nv = self._nv
+        while not self._stop.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self._h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksEventReasons(self._h) if hasattr(
+                    nv, "nvmlDeviceGetCurrentClocksEventReasons") else nv.nvmlDeviceGetCurrentClocksThrottleReasons(self._h)
+                for bit, name in self._NAMES.items():
+                    if r & bit and name != "gpu_idle":
+                        self.reasons.add(name)
+            except Exception:  # noqa: BLE001
+                pass
+            self._stop.wait(0.1)
+
+    def __enter__(self):
+        if self._nv is not None:
+            self._thr = threading.Thread(target=self._run, daemon=True)
+            self._thr.start()
+        return self
+
+    def __exit__(self, *a):
+        self._stop.set()
+        if self._thr:
+            self._thr.join()
+
+    def summary(self):
+        if self._nv is None or not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": [], "note": "nvml unavailable or region too short"}
+        return {"sm_mhz": float(np.median(self.samples)), "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(self.samples)}
+
+
+class Dist:
+    """torch.distributed plumbing: barrier + reductions only (the data path has no collective)."""
+
+    def __init__(self, gpus: int):
+        import torch
+        self.torch = torch
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.local = int(os.environ.get("LOCAL_RANK", "0"))
+        if gpus > 1 and self.world == 1:
+            raise SystemExit("--gpus N > 1 must be launched with torch.distributed.run (one rank per GPU)")
+        if not torch.cuda.is_available():
+            raise SystemExit("bench.py needs a B200: the product path has no CPU fallback "
+                             "(use --impl reference for the CPU oracle arm)")
+        torch.cuda.set_device(self.local)
+        self.device = torch.device("cuda", self.local)
+        if self.world > 1:
+            import torch.distributed as dist
+            os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+            dist.init_process_group("nccl", device_id=self.device)
+            self.dist = dist
+
+    def barrier(self):
+        self.torch.cuda.synchronize()
+        if self.world > 1:
+            self.dist.barrier(device_ids=[self.local])
+        self.torch.cuda.synchronize()
+
+    def reduce(self, value: float, op: str) -> float:
+        if self.world == 1:
+            return float(value)
+        t = self.torch.tensor([value], dtype=self.torch.float64, device=self.device)
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX if op == "max" else self.dist.ReduceOp.SUM)
+        return float(t.item())
+
+    def close(self):
+        if self.world > 1:
+            self.dist.destroy_process_group()
+
+
+# ------------------------------------------------------------------ GPU arm -----------------
+def run_timed(dist, enh, step, steps, warmup, flush=None):
+    """W warm-up calls, then K timed calls between barrier+synchronize; CUDA events on the launch
+    stream.  With `flush` (a > L2-sized buffer) every step is timed on its own and the buffer is
+    rewritten between steps, outside the timed intervals.  Returns (ms_per_step max over ranks,
+    per-kernel {name: (launches, total_ms)} of this rank, launches of this rank, clocks)."""
+    torch = dist.torch
+    for _ in range(warmup):
+        step()
+    dist.barrier()
+    l0 = enh.launch_count()
+    enh.profile_begin()
+    with ClockSampler(dist.local) as clk:
+        if flush is None:
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(steps):
+                step()
+            e1.record()
+            torch.cuda.synchronize()
+            ms = e0.elapsed_time(e1) / steps
+        else:
+            evs = []
+            for _ in range(steps):
+                flush.add_(1.0)
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                step()
+                e1.record()
+                evs.append((e0, e1))
+            torch.cuda.synchronize()
+            ms = sum(a.elapsed_time(b) for a, b in evs) / steps
+    prof = enh.profile_end()
+    launches = enh.launch_count() - l0
+    dist.barrier()
+    return dist.reduce(ms, "max"), prof, launches, clk.summary()
+
+
+def run_e2e(dist, step_host, steps, warmup):
+    """Same metric through enhance() on pinned HOST buffers: H2D, kernels and D2H all inside the
+    timed region (host wall clock around synchronous calls, max over ranks)."""
+    for _ in range(max(1, min(warmup, 2))):
+        step_host()
+    dist.barrier()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        step_host()
+    dist.torch.cuda.synchronize()
+    ms = (time.perf_counter() - t0) * 1e3 / steps
+    dist.barrier()
+    return dist.reduce(ms, "max")
+
+
+def tc_roofline(prof, px_per_step, steps, peaks):
+    """Tensor-pipe roofline of the dominant tcgen05 conv kernel + the whole conv2..conv7 chain."""
+    tc = {k: v for k, v in prof.items() if k in FLOP_PER_PX}
+    if not tc:
+        return None
+    dom = max(tc, key=lambda k: tc[k][1])
+    n_dom = {"dce_conv_tc_k32_kernel": 3, "dce_conv_tc_k64_kernel": 2, "dce_conv_tc_last_kernel": 1}[dom]
+    flops_dom = FLOP_PER_PX[dom] * n_dom * px_per_step * steps          # all launches of that kernel
+    ach = flops_dom / (tc[dom][1] * 1e-3) / 1e12
+    chain_ms = sum(v[1] for v in tc.values())
+    chain = DCE_TENSOR_FLOP_PER_PX * px_per_step * steps / (chain_ms * 1e-3) / 1e12
+    peak = peaks["tc_sustained"]
+    return {"bound": "tensor", "kernel": dom, "achieved": round(ach, 2), "peak": peak, "unit": "TFLOP/s",
+            "frac": round(ach / peak, 4), "traffic": None, "peak_source": f"{peaks['source']} bf16 sustained",
+            "launches": tc[dom][0], "avg_launch_ms": round(tc[dom][1] / tc[dom][0], 4),
+            "conv2to7_chain": {"achieved": round(chain, 2), "frac": round(chain / peak, 4),
+                               "frac_of_burst": round(chain / peaks["tc_burst"], 4)},
+            "kernel_ms_per_step": {k: round(v[1] / steps, 4) for k, v in sorted(prof.items())}}
+
+
+def hbm_roofline(prof, px_per_step, steps, peaks, total_ms_per_step):
+    if "msrcr_final_kernel" not in prof:
+        return None
+    cnt, ms = prof["msrcr_final_kernel"]
+    ach = MSRCR_FINAL_BYTES_PER_PX * px_per_step * steps / (ms * 1e-3) / 1e9
+    ns = MSRCR_NORTH_STAR_BYTES_PER_PX * px_per_step / (total_ms_per_step * 1e-3) / 1e9
+    return {"bound": "hbm", "kernel": "msrcr_final_kernel", "achieved": round(ach, 1), "peak": peaks["hbm"], "unit": "GB/s",
+            "frac": round(ach / peaks["hbm"], 4), "traffic": None, "peak_source": f"{peaks['source']} copy",
+            "launches": cnt, "avg_launch_ms": round(ms / cnt, 4),
+            "whole_msrcr_at_108B_per_px": {"achieved": round(ns, 1), "frac": round(ns / peaks["hbm"], 4)},
+            "kernel_ms_per_step": {k: round(v[1] / steps, 4) for k, v in sorted(prof.items())}}
+
+
+def gpu_workload(dist, name, steps, warmup, peaks, with_e2e=True, with_cpu=True):
+    import torch
+    import low_light_image_enhancement_b200 as L
+    from low_light_image_enhancement_b200.api import _enhancer
+    from low_light_image_enhancement_b200.synth import synth_lowlight_batch
+    world, rank, dev = dist.world, dist.rank, dist.device
+    enh = _enhancer(dev.index)
+    flush = None
+    if name == "c2":
+        sl = L.shard_slice(C2_TOTAL_FRAMES, rank, world)
+        n_local, h, w, total_frames, scaling = sl.stop - sl.start, H1080, W1080, C2_TOTAL_FRAMES, "strong"
+        method, params, dtype = "zero_dce", dict(weights=L.init_dce_weights(0), precision="bf16"), "bf16"
+        label = f"Zero-DCE bf16, {C2_TOTAL_FRAMES} x 1920x1080 sharded over {world} GPU(s) (BASELINE configs[2])"
+    elif name == "c3":
+        n_local, h, w, total_frames, scaling = C3_FRAMES_PER_GPU, H4K, W4K, C3_FRAMES_PER_GPU * world, "weak"
+        method, params, dtype = "msrcr", None, "f32"
+        label = f"MSRCR sigma=15/80/250, 3840x2160, {C3_FRAMES_PER_GPU} frames per GPU (BASELINE configs[3])"
+    elif name == "c1":
+        n_local, h, w, total_frames, scaling = 1, H1080, W1080, world, "weak"
+        method, params, dtype = "zero_dce", dict(weights=L.init_dce_weights(0), precision="fp32"), "f32"
+        label = "Zero-DCE fp32, 1 x 1920x1080 per GPU (BASELINE configs[1]; replicas only)"
+    elif name == "c0":
+        n_local, h, w, total_frames, scaling = 1, 400, 600, world, "weak"
+        method, params, dtype = "msrcr", None, "f32"
+        label = "MSRCR sigma=15/80/250, one 600x400 image per GPU (BASELINE configs[0]; replicas only)"
+    else:
+        raise SystemExit(f"unknown workload {name}")
+    if name in ("c1", "c0"):
+        flush = torch.empty(64 << 20, dtype=torch.float32, device=dev)      # 256 MiB > 126 MB L2
+    distinct = min(n_local, 8)
+    x = synth_lowlight_batch(distinct, h, w, seed=1000 * int(name[1]) + rank, device=dev)
+    if distinct < n_local:
+        x = x.repeat((n_local + distinct - 1) // distinct, 1, 1, 1)[:n_local].contiguous()
+    y = torch.empty_like(x)
+    px_local, px_total = n_local * h * w, total_frames * h * w
+
+    def step():
+        enh.enhance(x, method, params, out=y)
+
+    ms, prof, launches, clocks = run_timed(dist, enh, step, steps, warmup, flush)
+    res = {"workload": label, "ms_per_step": round(ms, 4), "value": round(px_total / ms / 1e3, 1), "scaling": scaling,
+           "dtype": dtype, "frames_total": total_frames, "frames_this_rank": n_local, "clocks": clocks,
+           "gpu_launches": int(dist.reduce(launches, "sum")),
+           "l2": "inputs+activations per step exceed the 126 MB L2" if flush is None else "256 MiB flush between timed steps"}
+    res["roofline"] = (tc_roofline(prof, px_local, steps, peaks) if method == "zero_dce" and dtype == "bf16"
+                       else hbm_roofline(prof, px_local, steps, peaks, ms) if method == "msrcr" else
+                       {"bound": "fp32-pipe", "note": "CUDA-core fp32 convolutions", "kernel_ms_per_step":
+                        {k: round(v[1] / steps, 4) for k, v in sorted(prof.items())},
+                        "achieved": round(158400 * px_local / (ms * 1e-3) / 1e12, 2), "unit": "TFLOP/s", "peak": 74.4,
+                        "frac": round(158400 * px_local / (ms * 1e-3) / 1e12 / 74.4, 4), "traffic": None})
+    if with_e2e:
+        xh = torch.empty(x.shape, dtype=torch.float32, pin_memory=True)
+        xh.copy_(x)
+        yh = torch.empty(x.shape, dtype=torch.float32, pin_memory=True)
+        e2e_steps = max(1, min(steps, 5))
+        ms_e = run_e2e(dist, lambda: enh.enhance(xh, method, params, out=yh), e2e_steps, warmup)
+        res["e2e"] = {"value": round(px_total / ms_e / 1e3, 1), "unit": "Mpixel/s", "ms_per_step": round(ms_e, 3),
+                      "h2d_bytes_per_step": int(xh.numel() * 4 * world), "d2h_bytes_per_step": int(yh.numel() * 4 * world),
+                      "steps": e2e_steps, "api": "enhance(pinned torch CPU tensor, out=pinned) -> staged 3-stream pipeline"}
+        if not torch.equal(yh, y.cpu()):
+            res["e2e"]["warning"] = "host-path result differs from device-path result"
+    if with_cpu and rank == 0:
+        res["cpu_baseline"] = cpu_baseline(name, x[0].cpu().numpy(), params)
+    return res
+
+
+# ------------------------------------------------------------------ CPU oracle legs ----------
+def _oracle_step(name, frame_hwc, params, rows):
+    """One bounded CPU sample: the NumPy oracle on the top `rows` rows of one frame."""
+    import oracle
+    crop = np.ascontiguousarray(frame_hwc[:rows])
+    if name in ("c2", "c1"):
+        ws = oracle.unpack_weights(params["weights"])
+        oracle.zero_dce(crop, ws, band=135)
+    elif name == "c0":
+        oracle.msrcr(crop, mode="direct")
+    else:
+        oracle.msrcr(crop, mode="fft")
+    return crop.shape[0] * crop.shape[1]
+
+
+def _oracle_rows(name):
+    # about 10-30 s of CPU work per sample on ~8 cores (measured in the build container)
+    return {"c2": 270, "c1": 270, "c3": 2160, "c0": 400}[name]
+
+
+def _oracle_desc(name):
+    return {"c2": "fp64 NumPy im2col+BLAS DCE-Net + curves", "c1": "fp64 NumPy im2col+BLAS DCE-Net + curves",
+            "c3": "fp64 NumPy MSRCR, scipy.fft surround (all cores)", "c0": "fp64 NumPy MSRCR, direct FIR (definition)"}[name]
+
+
+def cpu_baseline(name, frame_hwc, params):
+    rows = min(_oracle_rows(name), frame_hwc.shape[0])
+    t0 = time.perf_counter()
+    px = _oracle_step(name, frame_hwc, params, rows)
+    dt = time.perf_counter() - t0
+    return {"value": round(px / dt / 1e6, 4), "unit": "Mpixel/s", "cores": os.cpu_count(), "kind": "port",
+            "seconds": round(dt, 2),
+            "sample": f"top {rows} rows of frame 0 ({px / 1e6:.3f} Mpixel), {_oracle_desc(name)}; "
+                      "self-written oracle (the reference repository ships no code)"}
+
+
+def reference_arm(args):
+    """`--impl reference`: the reference repository contains no implementation
+    (/root/reference/README.md:1-2), so the CPU arm is the self-written NumPy oracle, run with all
+    the host threads NumPy/SciPy use, on a bounded sample of the same workload per step."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import oracle
+    name = args.workload
+    h, w = {"c2": (H1080, W1080), "c1": (H1080, W1080), "c3": (H4K, W4K), "c0": (400, 600)}[name]
+    rows = min(_oracle_rows(name), h)
+    frame = oracle.synth_lowlight(rows, w, seed=1000 * int(name[1]))
+    params = dict(weights=oracle.pack_weights(oracle.init_weights(0))) if name in ("c1", "c2") else None
+    # size the sample so that (K + W) steps end within ~4 minutes
+    t0 = time.perf_counter()
+    probe_rows = max(16, rows // 8)
+    _oracle_step(name, frame, params, probe_rows)
+    per_row = (time.perf_counter() - t0) / probe_rows
+    budget = 240.0 / max(1, args.steps + args.warmup)
+    rows = int(max(16, min(rows, budget / max(per_row, 1e-9))))
+    for _ in range(args.warmup):
+        _oracle_step(name, frame, params, rows)
+    t0 = time.perf_counter()
+    px = 0
+    for _ in range(args.steps):
+        px += _oracle_step(name, frame, params, rows)
+    dt = time.perf_counter() - t0
+    val = round(px / dt / 1e6, 4)
+    sample = f"top {rows} rows x {w} px of one synthetic frame per step, {_oracle_desc(name)}"
+    line = {"impl": "reference", "metric": "Mpixel/s", "value": val, "unit": "Mpixel/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(dt * 1e3 / args.steps, 2),
+            "higher_is_better": True, "scaling": "strong" if name == "c2" else "weak", "vs_baseline": None,
+            "dtype": "f64", "data": "synthetic", "config": {"workload": workload_label(name, args.gpus)},
+            "cpu_baseline": {"value": val, "unit": "Mpixel/s", "cores": os.cpu_count(), "kind": "port", "sample": sample},
+            "e2e": {"value": val, "unit": "Mpixel/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0,
+            "note": "the reference repository holds only README.md; this arm is the self-written NumPy oracle on the host cores"}
+    print(json.dumps(line), flush=True)
+
+
+def workload_label(name, world):
+    return {"c2": f"Zero-DCE bf16, {C2_TOTAL_FRAMES} x 1920x1080 sharded over {world} GPU(s) (BASELINE configs[2])",
+            "c3": f"MSRCR sigma=15/80/250, 3840x2160, {C3_FRAMES_PER_GPU} frames per GPU (BASELINE configs[3])",
+            "c1": "Zero-DCE fp32, 1 x 1920x1080 per GPU (BASELINE configs[1]; replicas only)",
+            "c0": "MSRCR sigma=15/80/250, one 600x400 image per GPU (BASELINE configs[0]; replicas only)"}[name]
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--workload", default="c2", choices=["c0", "c1", "c2", "c3"])
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-also", action="store_true", help="skip the short secondary workloads")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+    if args.impl == "reference":
+        reference_arm(args)
+        return
+    peaks = load_peaks()
+    dist = Dist(args.gpus)
+    main_res = gpu_workload(dist, args.workload, args.steps, args.warmup, peaks, not args.no_e2e, not args.no_cpu)
+    also = {}
+    if not args.no_also and args.workload == "c2":
+        for other in ("c3", "c1"):
+            r = gpu_workload(dist, other, max(3, args.steps // 2), 3, peaks, with_e2e=False, with_cpu=(dist.world == 1))
+            also[other] = r
+    if dist.rank == 0:
+        line = {"metric": "Mpixel/s", "value": main_res["value"], "unit": "Mpixel/s", "n_gpus": dist.world,
+                "steps": args.steps, "warmup": args.warmup, "ms_per_step": main_res["ms_per_step"],
+                "higher_is_better": True, "scaling": main_res["scaling"], "vs_baseline": None,
+                "dtype": main_res["dtype"], "data": "synthetic (device-generated low-light frames, random-init He weights)",
+                "config": {"workload": main_res["workload"], "frames_total": main_res["frames_total"],
+                           "l2": main_res["l2"], "peaks": peaks},
+                "roofline": main_res["roofline"], "cpu_baseline": main_res.get("cpu_baseline"),
+                "e2e": main_res.get("e2e"), "clocks": main_res["clocks"], "gpu_launches": main_res["gpu_launches"]}
+        if also:
+            line["also"] = also
+        print(json.dumps(line), flush=True)
+    dist.close()
+
+
+if __name__ == "__main__":
+    main()

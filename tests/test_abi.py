@@ -1,0 +1,141 @@
+"""CPU-only checks of the drop-in boundary (include/llie.h <-> libllie.so <-> ctypes shim):
+the library loads without a GPU, exports every symbol the header declares, the host-side
+logic (planner, shard split, layout resolution, parameter validation) works, and computing
+entry points fail loudly -- never fall back -- when no CUDA device exists."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+import torch
+
+import low_light_image_enhancement_b200 as L
+from low_light_image_enhancement_b200 import _lib, api
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+HAS_GPU = torch.cuda.is_available()
+
+
+def _header_functions():
+    src = open(os.path.join(ROOT, "include", "llie.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(llie_[a-z0-9_]+)\s*\(", src)))
+
+
+def test_library_exports_every_declared_symbol(lib_built):
+    names = _header_functions()
+    assert len(names) >= 18 and "llie_msrcr_f32" in names and "llie_dce_forward" in names
+    for n in names:
+        assert hasattr(lib_built, n), f"{n} declared in include/llie.h but not exported"
+    # the ctypes table binds exactly the header's functions
+    assert sorted(_lib.EXPORTS) == names
+
+
+def test_version_and_defaults(lib_built):
+    assert lib_built.llie_version() == 100
+    d = L.default_msrcr_params()
+    assert d["sigmas"] == (15.0, 80.0, 250.0) and d["truncate"] == 4.0
+    assert d["alpha"] == 125.0 and d["beta"] == 46.0 and abs(d["gain"] - 0.6) < 1e-7 and d["offset"] == 128.0
+    assert L.default_dce_params()["iters"] == 8
+    p = _lib.DceParams()
+    _lib.check(lib_built.llie_dce_default_params(C.byref(p)))
+    assert (p.struct_size, p.iters, p.curve_sign) == (C.sizeof(_lib.DceParams), 8, 1)
+
+
+def test_struct_sizes_match_header_layout():
+    # uint32 + int32 + 8f + 8f + 7f + int32
+    assert C.sizeof(_lib.MsrcrParams) == 4 + 4 + 32 + 32 + 28 + 4
+    assert C.sizeof(_lib.DceParams) == 16
+
+
+def test_pyramid_planner_matches_the_oracle_kernel():
+    # the cascade's effective kernel must sit within ~1e-4 (L1) of the oracle's truncated Gaussian
+    for sigma, stride in ((15.0, 2), (80.0, 16), (250.0, 16), (6.0, 2), (33.0, 2), (120.0, 16)):
+        q = L.plan_query(sigma)
+        assert q["stride"] == stride
+        assert q["l1_error"] < 4e-4, (sigma, q)
+        eff = (q["sigma_low"] * stride) ** 2
+        assert abs(np.sqrt(eff + (4 if stride == 2 else 4 + 4 * 64) + stride ** 2) / sigma - 1) < 0.03
+    with pytest.raises(L.LlieError):
+        L.plan_query(1.0)  # below the pyramid's range: an error, not a silent fallback
+
+
+def test_shard_slice_partitions_exactly():
+    for n in (0, 1, 7, 64, 65):
+        for world in (1, 2, 4, 8):
+            sl = [L.shard_slice(n, r, world) for r in range(world)]
+            assert sl[0].start == 0 and sl[-1].stop == n
+            assert all(a.stop == b.start for a, b in zip(sl, sl[1:]))
+            sizes = [s.stop - s.start for s in sl]
+            assert max(sizes) - min(sizes) <= 1
+    with pytest.raises(ValueError):
+        L.shard_slice(4, 2, 2)
+
+
+def test_layout_resolution():
+    r = api._resolve_layout
+    assert r((5, 7, 3), None) == (1, 5, 7, _lib.NHWC, False)
+    assert r((2, 5, 7, 3), None) == (2, 5, 7, _lib.NHWC, True)
+    assert r((2, 3, 5, 7), None) == (2, 5, 7, _lib.NCHW, True)
+    assert r((2, 3, 5, 3), "NCHW") == (2, 5, 3, _lib.NCHW, True)
+    for bad in ((2, 3, 5, 3), (5, 7, 4), (5, 7), (1, 2, 3, 4, 5)):
+        with pytest.raises(ValueError):
+            r(bad, None)
+
+
+def test_weight_blob_validation():
+    blob = L.init_dce_weights(0)
+    assert blob.dtype == np.float32 and blob.size == 79416
+    assert api._as_weight_blob(blob) is not None
+    with pytest.raises(ValueError):
+        api._as_weight_blob(blob[:-1])
+    # list-of-(W, b) form packs to the same bytes
+    parts, o = [], 0
+    for co, ci in api.DCE_LAYERS:
+        w = blob[o:o + co * ci * 9].reshape(co, ci, 3, 3); o += w.size
+        b = blob[o:o + co]; o += co
+        parts.append((w, b))
+    assert np.array_equal(api._as_weight_blob(parts), blob)
+
+
+def test_param_validation_is_host_side():
+    with pytest.raises(ValueError):
+        api._msrcr_struct(dict(sigmas=(1.0, 2.0), weights=(1.0,)))
+    with pytest.raises(ValueError):
+        api._msrcr_struct(dict(blur="box"))
+    with pytest.raises(ValueError):
+        api._msrcr_struct(dict(nonsense=1))
+    p = api._msrcr_struct(dict(sigmas=(5.0,), weights=(1.0,), blur="direct"))
+    assert p.n_scales == 1 and p.blur == _lib.BLUR_DIRECT and p.struct_size == C.sizeof(_lib.MsrcrParams)
+
+
+@pytest.mark.skipif(HAS_GPU, reason="checks the no-GPU failure mode")
+def test_no_gpu_means_error_not_fallback(lib_built):
+    n = C.c_int(-1)
+    assert lib_built.llie_device_count(C.byref(n)) == _lib.E_CUDA and n.value == 0
+    assert b"no CPU fallback" in lib_built.llie_last_error()
+    h = C.c_void_p()
+    assert lib_built.llie_create(C.byref(h), 0) == _lib.E_CUDA and not h.value
+    x = np.zeros((8, 8, 3), np.float32)
+    with pytest.raises(L.LlieCudaError):
+        L.enhance(x, "msrcr")
+    with pytest.raises(L.LlieCudaError):
+        L.enhance(x, "zero_dce", dict(weights=L.init_dce_weights(0)))
+
+
+def test_null_arguments_return_status_codes(lib_built):
+    assert lib_built.llie_msrcr_default_params(None) == _lib.E_ARG
+    assert lib_built.llie_sync(None) == _lib.E_ARG
+    assert lib_built.llie_destroy(None) == _lib.OK
+    p = _lib.MsrcrParams()
+    assert lib_built.llie_msrcr_f32(None, None, None, 1, 8, 8, 0, C.byref(p), None) == _lib.E_ARG
+
+
+def test_product_package_never_imports_the_oracle():
+    pkg = os.path.join(ROOT, "low_light_image_enhancement_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h")):
+                text = open(os.path.join(dirpath, f)).read()
+                assert not re.search(r"^\s*(import|from)\s+oracle\b", text, flags=re.M), f

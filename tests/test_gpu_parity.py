@@ -1,0 +1,301 @@
+"""GPU parity tests (run with -m gpu on a B200): every CUDA path, called through the C ABI via
+enhance(), against the NumPy oracle and the committed golden vectors.
+
+Tolerances are BASELINE.json#north_star's: fp32 paths max-abs <= 1e-4 on [0,1] pixels; bf16
+Zero-DCE PSNR >= 50 dB against the fp64 oracle with the same (unrounded) weights."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import oracle
+import low_light_image_enhancement_b200 as L
+
+pytestmark = pytest.mark.gpu
+
+G = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+TOL_F32 = 1e-4       # north_star: fp32 paths, max-abs on [0,1] pixels
+PSNR_BF16 = 50.0     # north_star: bf16 Zero-DCE vs fp32/fp64 oracle
+
+
+def psnr(y, ref):
+    mse = float(np.mean((y.astype(np.float64) - ref.astype(np.float64)) ** 2))
+    return 10.0 * np.log10(1.0 / max(mse, 1e-30))
+
+
+@pytest.fixture(scope="module")
+def blob():
+    return oracle.pack_weights(oracle.init_weights(0))
+
+
+# ---------------------------------------------------------------- MSRCR -------------------
+@pytest.mark.parametrize("blur", ["pyramid", "direct"])
+def test_msrcr_golden_default(blur):
+    d = np.load(os.path.join(G, "msrcr_96x128.npz"))
+    y = L.enhance(d["x"], "msrcr", dict(blur=blur))
+    assert y.dtype == np.float32 and y.shape == d["x"].shape
+    assert np.abs(y - d["y"]).max() <= TOL_F32
+
+
+@pytest.mark.parametrize("blur", ["pyramid", "direct"])
+def test_msrcr_golden_custom_scales(blur):
+    d = np.load(os.path.join(G, "msrcr_80x112_custom.npz"))
+    p = dict(sigmas=tuple(float(s) for s in d["sigmas"]), weights=tuple(float(w) for w in d["weights"]),
+             gain=float(d["gain"]), offset=float(d["offset"]), blur=blur)
+    assert np.abs(L.enhance(d["x"], "msrcr", p) - d["y"]).max() <= TOL_F32
+
+
+@pytest.mark.parametrize("blur", ["pyramid", "direct"])
+def test_msrcr_config0_600x400(blur):
+    """BASELINE configs[0]: 600x400, sigma 15/80/250 -- every radius exceeds the image on one axis."""
+    x = oracle.synth_lowlight(400, 600, 0)
+    ref = oracle.msrcr(x, mode="fft")
+    y = L.enhance(x, "msrcr", dict(blur=blur))
+    assert np.abs(y - ref).max() <= TOL_F32
+    xc = np.ascontiguousarray(x.transpose(2, 0, 1))[None]
+    yc = L.enhance(xc, "msrcr", dict(blur=blur, layout="NCHW"))
+    assert np.abs(yc[0].transpose(1, 2, 0) - ref).max() <= TOL_F32
+
+
+def test_msrcr_pyramid_matches_direct_on_gpu():
+    x = torch.from_numpy(oracle.synth_lowlight(333, 517, 21)).cuda()
+    a = L.enhance(x, "msrcr", dict(blur="pyramid"))
+    b = L.enhance(x, "msrcr", dict(blur="direct"))
+    assert float((a - b).abs().max()) <= TOL_F32
+
+
+def test_msrcr_constant_image_kat():
+    for val in (0.0, 0.2, 1.0):
+        x = np.full((70, 90, 3), val, np.float32)
+        for blur in ("pyramid", "direct"):
+            y = L.enhance(x, "msrcr", dict(blur=blur))
+            assert np.abs(y - 128.0 / 255.0).max() <= 2e-5, (val, blur)
+
+
+def test_msrcr_tiny_and_ragged_shapes():
+    for (h, w) in ((1, 1), (1, 37), (37, 1), (5, 130), (63, 65), (129, 31)):
+        x = oracle.synth_lowlight(h, w, 100 + h + w)
+        ref = oracle.msrcr(x)
+        for blur in ("pyramid", "direct"):
+            assert np.abs(L.enhance(x, "msrcr", dict(blur=blur)) - ref).max() <= TOL_F32, (h, w, blur)
+
+
+def test_msrcr_batch_elements_are_independent():
+    xs = np.stack([oracle.synth_lowlight(120, 200, s) for s in (1, 2, 3)])
+    xd = torch.from_numpy(xs).cuda()
+    yb = L.enhance(xd, "msrcr")
+    for i in range(3):
+        assert torch.equal(yb[i], L.enhance(xd[i].contiguous(), "msrcr"))
+
+
+def test_msrcr_channel_permutation_equivariance():
+    x = oracle.synth_lowlight(90, 140, 5)
+    y = L.enhance(x, "msrcr")
+    perm = [2, 0, 1]
+    yp = L.enhance(np.ascontiguousarray(x[:, :, perm]), "msrcr")
+    assert np.abs(yp - y[:, :, perm]).max() <= 1e-6
+
+
+def test_msrcr_4k_windowed_oracle():
+    """configs[3] frame size; checked on windows: corners, edges, interior."""
+    h, w = 2160, 3840
+    x = oracle.synth_lowlight(h, w, 7)
+    y = L.enhance(torch.from_numpy(x).cuda(), "msrcr").cpu().numpy()
+    assert y.min() >= 0.0 and y.max() <= 1.0
+    wins = [(0, 0), (0, w - 96), (h - 96, 0), (h - 96, w - 96), (1000, 1900), (0, 1500), (1100, 0), (700, 2900)]
+    for (y0, x0) in wins:
+        ref = oracle.msrcr_window(x, y0, y0 + 96, x0, x0 + 96)
+        assert np.abs(y[y0:y0 + 96, x0:x0 + 96] - ref).max() <= TOL_F32, (y0, x0)
+
+
+# ---------------------------------------------------------------- Zero-DCE ----------------
+def test_dce_fp32_golden():
+    d = np.load(os.path.join(G, "zero_dce_48x64.npz"))
+    y, m = L.enhance(d["x"], "zero_dce", dict(weights=d["weights"], precision="fp32", return_maps=True))
+    assert np.abs(y - d["y"]).max() <= TOL_F32
+    assert np.abs(m - d["maps"]).max() <= TOL_F32
+
+
+def test_dce_bf16_golden():
+    d = np.load(os.path.join(G, "zero_dce_48x64.npz"))
+    y = L.enhance(d["x"], "zero_dce", dict(weights=d["weights"], precision="bf16"))
+    assert psnr(y, d["y"]) >= PSNR_BF16
+
+
+@pytest.mark.parametrize("prec", ["fp32", "bf16"])
+def test_dce_zero_weights_is_identity(prec):
+    x = oracle.synth_lowlight(40, 150, 1)
+    y, m = L.enhance(x, "zero_dce", dict(weights=np.zeros(79416, np.float32), precision=prec, return_maps=True))
+    assert np.array_equal(y, x) and np.all(m == 0)
+
+
+@pytest.mark.parametrize("prec", ["fp32", "bf16"])
+def test_dce_constant_alpha_closed_form(prec):
+    b = np.linspace(-0.9, 0.9, 24).astype(np.float32)
+    w = np.zeros(79416, np.float32)
+    w[-24:] = b
+    x = (oracle.synth_lowlight(33, 140, 2) * 5).astype(np.float32)
+    y, m = L.enhance(x, "zero_dce", dict(weights=w, precision=prec, return_maps=True))
+    a = np.tanh(b.astype(np.float64))
+    e = x.astype(np.float64)
+    for n in range(8):
+        e = e + a[3 * n:3 * n + 3] * e * (1 - e)
+    assert np.abs(m - a.astype(np.float32)).max() <= 2e-6
+    assert np.abs(y - e).max() <= 5e-6
+
+
+@pytest.mark.parametrize("shape", [(135, 240), (270, 481), (9, 5), (1, 1), (64, 128), (65, 129), (3, 300)])
+def test_dce_fp32_vs_oracle(shape, blob):
+    h, w = shape
+    x = oracle.synth_lowlight(h, w, 3)
+    ref, A = oracle.zero_dce(x, oracle.init_weights(0), return_maps=True)
+    y, m = L.enhance(x, "zero_dce", dict(weights=blob, precision="fp32", return_maps=True))
+    assert np.abs(y - ref).max() <= TOL_F32 and np.abs(m - A).max() <= TOL_F32
+    xc = np.ascontiguousarray(x.transpose(2, 0, 1))[None]
+    yc, mc = L.enhance(xc, "zero_dce", dict(weights=blob, precision="fp32", return_maps=True, layout="NCHW"))
+    assert np.abs(yc[0].transpose(1, 2, 0) - ref).max() <= TOL_F32
+    assert np.abs(mc[0].transpose(1, 2, 0) - A).max() <= TOL_F32
+
+
+@pytest.mark.parametrize("case", ["he", "last_x4", "bright_x6"])
+def test_dce_bf16_psnr(case):
+    """three cases so that the 50 dB bar is exercised where it can fail."""
+    ws = oracle.init_weights(0, last_gain=4.0 if case == "last_x4" else 1.0)
+    for (h, w, seed) in ((135, 240, 1), (270, 481, 2), (70, 200, 5)):
+        x = oracle.synth_lowlight(h, w, seed)
+        if case == "bright_x6":
+            x = np.clip(x * 6, 0, 1).astype(np.float32)
+        ref = oracle.zero_dce(x, ws)
+        y = L.enhance(x, "zero_dce", dict(weights=oracle.pack_weights(ws), precision="bf16"))
+        assert psnr(y, ref) >= PSNR_BF16, (case, h, w, psnr(y, ref))
+        assert y.min() >= 0.0 and y.max() <= 1.0
+
+
+def test_dce_bf16_activations_match_bf16_emulation(blob):
+    """Layer-by-layer check of the tensor-core path against a NumPy emulation of bf16 storage."""
+    from bf16_emulation import dce_activations_bf16
+    from low_light_image_enhancement_b200.api import _enhancer
+    ws = oracle.init_weights(0)
+    x = (oracle.synth_lowlight(70, 200, 5) * 6).astype(np.float32)
+    acts, A = dce_activations_bf16(x, ws)
+    xd = torch.from_numpy(x).cuda()
+    y, m = L.enhance(xd, "zero_dce", dict(weights=blob, precision="bf16", return_maps=True))
+    e = _enhancer(xd.device.index)
+    for i in range(6):
+        g = e.debug_dce_activation(i + 1, 0, 70, 200)
+        scale = max(1.0, float(np.abs(acts[i]).max()))
+        # one bf16 ulp of disagreement where fp32 accumulation order flips a rounding
+        assert np.abs(g - acts[i]).max() <= scale * 2.0 ** -7, i
+        assert (np.abs(g - acts[i]) > scale * 2.0 ** -9).mean() < 0.02, i
+    assert np.abs(m.cpu().numpy() - A.transpose(1, 2, 0)).max() <= 2e-2
+
+
+@pytest.mark.parametrize("prec", ["fp32", "bf16"])
+def test_dce_1080p_windows(prec, blob):
+    """configs[1]/[2] frame size, checked on windows (7-px halo = the net's receptive field)."""
+    h, w = 1080, 1920
+    ws = oracle.init_weights(0)
+    x = oracle.synth_lowlight(h, w, 3)
+    y = L.enhance(torch.from_numpy(x).cuda(), "zero_dce", dict(weights=blob, precision=prec)).cpu().numpy()
+    errs, refs, outs = [], [], []
+    for (y0, x0) in ((0, 0), (0, w - 64), (h - 64, 0), (h - 64, w - 64), (500, 1000), (1016, 1200), (300, 1856),
+                     (64, 100), (640, 1260)):
+        cy0, cy1, cx0, cx1 = max(0, y0 - 7), min(h, y0 + 71), max(0, x0 - 7), min(w, x0 + 71)
+        ref = oracle.zero_dce(np.ascontiguousarray(x[cy0:cy1, cx0:cx1]), ws)[y0 - cy0:y0 - cy0 + 64, x0 - cx0:x0 - cx0 + 64]
+        refs.append(ref); outs.append(y[y0:y0 + 64, x0:x0 + 64])
+    ref, out = np.stack(refs), np.stack(outs)
+    if prec == "fp32":
+        assert np.abs(out - ref).max() <= TOL_F32
+    else:
+        assert psnr(out, ref) >= PSNR_BF16
+
+
+@pytest.mark.parametrize("prec", ["fp32", "bf16"])
+def test_dce_batch_elements_are_independent(prec, blob):
+    xs = np.stack([oracle.synth_lowlight(100, 260, s) for s in (1, 2, 3)])
+    xd = torch.from_numpy(xs).cuda()
+    p = dict(weights=blob, precision=prec)
+    yb = L.enhance(xd, "zero_dce", p)
+    for i in range(3):
+        assert torch.equal(yb[i], L.enhance(xd[i].contiguous(), "zero_dce", p))
+
+
+def test_dce_iters_and_sign(blob):
+    x = oracle.synth_lowlight(50, 70, 9)
+    ws = oracle.init_weights(0)
+    for iters in (0, 1, 5):
+        ref = oracle.zero_dce(x, ws, iters=iters)
+        y = L.enhance(x, "zero_dce", dict(weights=blob, iters=iters))
+        assert np.abs(y - ref).max() <= TOL_F32
+    A = oracle.dce_net(x.transpose(2, 0, 1), ws)
+    ref = oracle.apply_curves(x.transpose(2, 0, 1), A, sign=-1).transpose(1, 2, 0)
+    for prec in ("fp32", "bf16"):
+        y = L.enhance(x, "zero_dce", dict(weights=blob, curve_sign=-1, precision=prec))
+        assert (np.abs(y - ref).max() <= TOL_F32) if prec == "fp32" else (psnr(y, ref) >= PSNR_BF16)
+
+
+# ---------------------------------------------------------------- boundary ----------------
+def test_numpy_torch_cpu_and_cuda_inputs_agree(blob):
+    x = np.stack([oracle.synth_lowlight(64, 96, s) for s in range(5)])
+    for method, p in (("msrcr", None), ("zero_dce", dict(weights=blob))):
+        a = L.enhance(x, method, p)
+        b = L.enhance(torch.from_numpy(x), method, p)
+        c = L.enhance(torch.from_numpy(x).cuda(), method, p)
+        assert isinstance(a, np.ndarray) and isinstance(b, torch.Tensor) and not b.is_cuda and c.is_cuda
+        assert np.array_equal(a, b.numpy()) and np.array_equal(a, c.cpu().numpy())
+
+
+def test_host_pipeline_chunks_large_batches():
+    # > 64 MiB of input forces several staged chunks through the 3-stream pipeline
+    x = np.stack([oracle.synth_lowlight(540, 960, s) for s in range(3)])
+    xb = np.ascontiguousarray(np.tile(x, (5, 1, 1, 1)))          # 15 frames x 6.2 MB
+    y = L.enhance(xb, "msrcr")
+    one = L.enhance(torch.from_numpy(x).cuda(), "msrcr").cpu().numpy()
+    for i in range(15):
+        assert np.array_equal(y[i], one[i % 3])
+
+
+def test_out_argument_and_stream_ordering():
+    x = torch.from_numpy(oracle.synth_lowlight(80, 120, 4)).cuda()
+    out = torch.empty_like(x)
+    s = torch.cuda.Stream()
+    with torch.cuda.stream(s):
+        x2 = x * 1.0
+        r = L.enhance(x2, "msrcr", out=out)
+        z = out + 0.0
+    s.synchronize()
+    assert r.data_ptr() == out.data_ptr() and torch.equal(z, L.enhance(x, "msrcr"))
+
+
+def test_errors_are_exceptions_not_crashes(blob):
+    x = oracle.synth_lowlight(16, 16, 0)
+    with pytest.raises(TypeError):
+        L.enhance(x.astype(np.float64), "msrcr")
+    with pytest.raises(ValueError):
+        L.enhance(x, "clahe")
+    with pytest.raises(ValueError):
+        L.enhance(x[:, ::2], "msrcr")
+    with pytest.raises(ValueError):
+        L.enhance(x, "zero_dce")
+    with pytest.raises(L.LlieError):
+        L.enhance(x, "zero_dce", dict(weights=blob, iters=9))
+    with pytest.raises(L.LlieError):
+        L.enhance(x, "msrcr", dict(sigmas=(2.0,), weights=(1.0,)))      # below the pyramid's range
+    assert L.enhance(x, "msrcr", dict(sigmas=(2.0,), weights=(1.0,), blur="direct")).shape == x.shape
+    xd = torch.from_numpy(x).cuda()
+    with pytest.raises(ValueError):
+        L.enhance(xd, "msrcr", out=xd)
+    e = np.empty((0, 16, 16, 3), np.float32)
+    assert L.enhance(e, "msrcr").shape == e.shape
+
+
+def test_no_allocation_after_warmup(blob):
+    from low_light_image_enhancement_b200.api import _enhancer
+    x = torch.from_numpy(np.stack([oracle.synth_lowlight(200, 300, s) for s in range(2)])).cuda()
+    e = _enhancer(x.device.index)
+    for method, p in (("msrcr", None), ("zero_dce", dict(weights=blob, precision="bf16"))):
+        L.enhance(x, method, p)
+        before, l0 = e.workspace_bytes(), e.launch_count()
+        L.enhance(x, method, p)
+        assert e.workspace_bytes() == before and e.launch_count() > l0
