@@ -46,7 +46,7 @@ extern "C" {
 #define LLIE_BF16 1 /* fp32 I/O, bf16 operands on tcgen05, fp32 accumulate (config 2) */
 
 /* MSRCR surround-blur algorithms */
-#define LLIE_BLUR_PYRAMID 0 /* multi-resolution Gaussian cascade, O(1) per pixel in sigma */
+#define LLIE_BLUR_PYRAMID 0 /* decimated Gaussian cascade, O(1) per pixel in sigma; needs sigma >= 12 */
 #define LLIE_BLUR_DIRECT 1  /* exact truncated FIR, O(sigma) per pixel; GPU ground truth   */
 
 #define LLIE_MAX_SCALES 8
@@ -107,7 +107,7 @@ int llie_msrcr_f32(llie_ctx* ctx, const float* in, float* out, int n, int h, int
                    const llie_msrcr_params* params, void* stream);
 
 /* Host-side planner of the pyramid blur, exposed so that CPU tests can check it without a
- * GPU: for `sigma`/`truncate` returns the pyramid level stride (2 or 16), the low-res
+ * GPU: for `sigma`/`truncate` returns the cascade level's stride (4 or 16), the low-res
  * Gaussian's sigma and radius, and the L1 distance between the cascade's effective kernel
  * and the oracle's truncated Gaussian.  Needs no device. */
 int llie_msrcr_plan_query(float sigma, float truncate, int* stride, double* sigma_low, int* radius_low,

@@ -1,0 +1,501 @@
+// Device kernels of the MSRCR fast path (LLIE_BLUR_PYRAMID): a two-level decimated Gaussian cascade
+// whose cost per pixel does not depend on sigma (north_star kernel (1)).
+// No reference file exists to cite (/root/reference/README.md:1-2).
+//
+// Levels (1-D view; the 2-D operators are separable):
+//   C (stride 4):  C[j] = sum_t g[t] I[clamp(4(j-PC)+t-16)],  g = Gaussian sigma 4, radius 16
+//   B (stride 16): B[j] = sum_t g[t] C[clamp(4(j-PB)+PC+t-16)]   (same g, in C samples)
+// A scale with sigma < 40 is blurred on C, a larger one on B and then brought to C resolution by
+// a Gaussian-weighted x4 upsample (unit sigma in B samples, 9 taps; its variance is part of the
+// budget).  The last x4 step C -> pixels is Lagrange interpolation (6 taps for C-level scales,
+// 4 for B-level ones) fused with the log / ratio / colour-restoration / gain-offset epilogue.
+// Edge clamping is exact: each level stores PC / PB samples beyond the border, which reaches the
+// region where the clamped, prefiltered signal is constant.
+#pragma once
+#include "llie_common.cuh"
+
+namespace llie {
+namespace {
+
+constexpr int kPC = 4;   // C samples stored before pixel 0
+constexpr int kPB = 5;   // B samples stored before pixel 0
+constexpr int kRD = 16;  // radius of the decimation prefilter (33 taps)
+constexpr int kTU = 4;   // half-width of the B -> C Gaussian upsampler (9 taps)
+
+__host__ __device__ inline int level_c_size(int n) { return kPC + (n + 18) / 4 + 1; }
+__host__ __device__ inline int level_b_size(int n) { return kPB + (n + 94) / 16 + 1; }
+
+// Gaussian sigma = 4, radius 16, sum-normalised; g[t] = g[32 - t], first 17 taps listed.
+// Compile-time constants so that fully unrolled filters use immediate-operand FFMAs.
+__device__ constexpr float kGD[17] = {
+    3.345874043e-05f, 8.815204000e-05f, 2.181783944e-04f, 5.072799653e-04f, 1.108001311e-03f, 2.273471076e-03f,
+    4.382230196e-03f, 7.935193759e-03f, 1.349821928e-02f, 2.157009300e-02f, 3.238054475e-02f, 4.566388724e-02f,
+    6.049482184e-02f, 7.528702219e-02f, 8.801944640e-02f, 9.667045004e-02f, 9.973909953e-02f};
+__device__ __forceinline__ constexpr float gd(int t) { return kGD[t <= 16 ? t : 32 - t]; }
+
+// Lagrange interpolation weights at fraction ph/4 (ph = 1..3); ph = 0 is the sample itself.
+// 6 taps at offsets -2..3, 4 taps at offsets -1..2.
+__device__ constexpr float kL6[3][6] = {
+    {9.3994140625e-03f, -8.4594726563e-02f, 8.4594726562e-01f, 2.8198242188e-01f, -6.0424804688e-02f, 7.6904296875e-03f},
+    {1.1718750000e-02f, -9.7656250000e-02f, 5.8593750000e-01f, 5.8593750000e-01f, -9.7656250000e-02f, 1.1718750000e-02f},
+    {7.6904296875e-03f, -6.0424804688e-02f, 2.8198242188e-01f, 8.4594726562e-01f, -8.4594726562e-02f, 9.3994140625e-03f}};
+__device__ constexpr float kL4[3][4] = {{-5.4687500000e-02f, 8.2031250000e-01f, 2.7343750000e-01f, -3.9062500000e-02f},
+                                        {-6.2500000000e-02f, 5.6250000000e-01f, 5.6250000000e-01f, -6.2500000000e-02f},
+                                        {-3.9062500000e-02f, 2.7343750000e-01f, 8.2031250000e-01f, -5.4687500000e-02f}};
+
+// ---- K1: vertical prefilter + decimate by 4, full resolution -> V ------------------------------
+// The image is `planes` planes of rows of RW floats (NHWC: one plane per image, RW = 3W, channels
+// interleaved; NCHW: three planes per image, RW = W).  V[plane][jy][e] = sum_t g[t] x[clamp(4(jy-PC)
+// + t - 16, 0, H-1)][e] on the raw input (the affine map I = a x + b commutes with a sum-1 filter
+// and is applied by K1b).  A thread owns VEC consecutive floats of the row and walks down the raw
+// rows once, scattering each loaded value into the 8-9 output rows whose windows contain it; the
+// 9 live accumulators rotate through a 9-group (36-row) unrolled body so every index is static.
+// `x` points at image row in_row0 and holds in_rows rows (row-tiled shards); rows outside [0, H) clamp.
+template <int VEC>
+__global__ void __launch_bounds__(128)
+down4_rows_kernel(const float* __restrict__ x, long long plane_stride, int RW, int H, int in_row0, int in_rows,
+                  float* __restrict__ V, int hC, int v_row_begin, int v_row_end, int rows_per_strip) {
+  const int e0 = (blockIdx.x * 128 + threadIdx.x) * VEC;
+  if (e0 >= RW) return;
+  const int j0 = v_row_begin + blockIdx.y * rows_per_strip;
+  const int j1 = min(j0 + rows_per_strip, v_row_end);
+  if (j0 >= j1) return;
+  const long long plane = blockIdx.z;
+  const float* src = x + plane * plane_stride + e0;
+  float* dst = V + plane * (long long)hC * RW + e0;
+  const int ngroups = (j1 - j0) + 8;
+  const int ybase = 4 * (j0 - kPC - 4);  // raw row of group 0, phase 0
+
+  float acc[9][VEC];
+#pragma unroll
+  for (int s = 0; s < 9; ++s)
+#pragma unroll
+    for (int i = 0; i < VEC; ++i) acc[s][i] = 0.f;
+
+  float cur[4][VEC], nxt[4][VEC];
+  auto load_group = [&](float (&buf)[4][VEC], int g) {
+#pragma unroll
+    for (int p = 0; p < 4; ++p) {
+      // clamp to the image, then to the rows this pointer holds (the latter only ever bites on
+      // taps of output rows outside [j0, j1), which are never stored)
+      const int y = min(max(min(max(ybase + 4 * g + p, 0), H - 1) - in_row0, 0), in_rows - 1);
+      const float* q = src + (long long)y * RW;
+      if constexpr (VEC == 4) {
+        const float4 t = __ldg(reinterpret_cast<const float4*>(q));
+        buf[p][0] = t.x; buf[p][1] = t.y; buf[p][2] = t.z; buf[p][3] = t.w;
+      } else {
+#pragma unroll
+        for (int i = 0; i < VEC; ++i) buf[p][i] = __ldg(q + i);
+      }
+    }
+  };
+  load_group(cur, 0);
+  for (int gbase = 0; gbase < ngroups; gbase += 9) {
+#pragma unroll
+    for (int gg = 0; gg < 9; ++gg) {
+      const int g = gbase + gg;
+      if (g < ngroups) {
+        if (g + 1 < ngroups) load_group(nxt, g + 1);
+        // phase 0: taps 4q, q = 0..8, into slot (gg - q) mod 9
+#pragma unroll
+        for (int q = 0; q <= 8; ++q)
+#pragma unroll
+          for (int i = 0; i < VEC; ++i) acc[(gg - q + 9) % 9][i] = fmaf(gd(4 * q), cur[0][i], acc[(gg - q + 9) % 9][i]);
+        {  // the row that just received its last tap: jy = j0 + g - 8, slot (gg + 1) mod 9
+          const int jy = j0 + g - 8;
+          if (g >= 8) {
+            float* o = dst + (long long)jy * RW;
+            if constexpr (VEC == 4) {
+              *reinterpret_cast<float4*>(o) = make_float4(acc[(gg + 1) % 9][0], acc[(gg + 1) % 9][1],
+                                                          acc[(gg + 1) % 9][2], acc[(gg + 1) % 9][3]);
+            } else {
+#pragma unroll
+              for (int i = 0; i < VEC; ++i) o[i] = acc[(gg + 1) % 9][i];
+            }
+          }
+#pragma unroll
+          for (int i = 0; i < VEC; ++i) acc[(gg + 1) % 9][i] = 0.f;
+        }
+#pragma unroll
+        for (int p = 1; p < 4; ++p)
+#pragma unroll
+          for (int q = 0; q <= 7; ++q)
+#pragma unroll
+            for (int i = 0; i < VEC; ++i)
+              acc[(gg - q + 9) % 9][i] = fmaf(gd(4 * q + p), cur[p][i], acc[(gg - q + 9) % 9][i]);
+#pragma unroll
+        for (int p = 0; p < 4; ++p)
+#pragma unroll
+          for (int i = 0; i < VEC; ++i) cur[p][i] = nxt[p][i];
+      }
+    }
+  }
+}
+
+// ---- K1b: horizontal prefilter + decimate by 4 on V -> planar level C, with I = a x + b ----------
+// V[plane][jy][px*CS + c] -> C[(plane*CS + c)][jy][jx] = a * sum_t g[t] V[..][clamp(4(jx-PC)+t-16)] + b.
+// A CTA stages one row segment (edge-clamped) in shared memory; thread jx reads its 33*CS words as
+// aligned 128-bit shared loads (48-byte lane stride for CS = 3: bank-conflict free).
+template <int CS>
+__global__ void __launch_bounds__(128)
+down4_cols_kernel(const float* __restrict__ V, float* __restrict__ Cout, int RW, int W, int hC, int wC,
+                  int row_begin, float a, float b) {
+  constexpr int kSegPx = 4 * 128 + 2 * kRD + 4;  // pixels staged (a little padding for the last vector)
+  __shared__ __align__(16) float seg[kSegPx * CS];
+  const int jy = row_begin + blockIdx.y;
+  const long long plane = blockIdx.z;
+  const int jx0 = blockIdx.x * 128;
+  const int px0 = 4 * (jx0 - kPC) - kRD;
+  const float* src = V + (plane * hC + jy) * (long long)RW;
+  for (int i = threadIdx.x; i < kSegPx * CS; i += 128) {
+    const int px = i / CS, c = i - px * CS;
+    const int xx = min(max(px0 + px, 0), W - 1);
+    seg[i] = __ldg(src + xx * CS + c);
+  }
+  __syncthreads();
+  const int jx = jx0 + threadIdx.x;
+  if (jx >= wC) return;
+  constexpr int kWords = 33 * CS, kVecs = (kWords + 3) / 4;
+  const float4* s4 = reinterpret_cast<const float4*>(seg + 4 * threadIdx.x * CS);
+  float w[kVecs * 4];
+#pragma unroll
+  for (int i = 0; i < kVecs; ++i) {
+    const float4 t = s4[i];
+    w[4 * i] = t.x; w[4 * i + 1] = t.y; w[4 * i + 2] = t.z; w[4 * i + 3] = t.w;
+  }
+  float acc[CS];
+#pragma unroll
+  for (int c = 0; c < CS; ++c) acc[c] = 0.f;
+#pragma unroll
+  for (int t = 0; t <= 2 * kRD; ++t)
+#pragma unroll
+    for (int c = 0; c < CS; ++c) acc[c] = fmaf(gd(t), w[t * CS + c], acc[c]);
+#pragma unroll
+  for (int c = 0; c < CS; ++c) Cout[((plane * CS + c) * hC + jy) * (long long)wC + jx] = fmaf(a, acc[c], b);
+}
+
+// ---- level C -> level B: prefilter + decimate by 4 (same 33-tap Gaussian, in C samples) ---------
+// x pass: T[plane][row][jb] = sum_t g[t] C[plane][row][clamp(4(jb-PB)+PC+t-16, 0, wC-1)], rows [r0, r1)
+__global__ void __launch_bounds__(256)
+decim4_x_kernel(const float* __restrict__ Cin, float* __restrict__ T, int hC, int wC, int wB, int r0, int r1) {
+  const long long plane = blockIdx.z;
+  const int i = blockIdx.x * 256 + threadIdx.x;
+  const int n = (r1 - r0) * wB;
+  if (i >= n) return;
+  const int row = r0 + i / wB, jb = i % wB;
+  const float* src = Cin + (plane * hC + row) * (long long)wC;
+  const int c0 = 4 * (jb - kPB) + kPC - kRD;
+  float acc = 0.f;
+#pragma unroll
+  for (int t = 0; t <= 2 * kRD; ++t) acc = fmaf(gd(t), __ldg(src + min(max(c0 + t, 0), wC - 1)), acc);
+  T[(plane * hC + row) * (long long)wB + jb] = acc;
+}
+// y pass: B[plane][jb][x] = sum_t g[t] T[plane][clamp(4(jb-PB)+PC+t-16, 0, hC-1)][x], B rows [b0, b1)
+__global__ void __launch_bounds__(256)
+decim4_y_kernel(const float* __restrict__ T, float* __restrict__ B, int hC, int hB, int wB, int b0, int b1) {
+  const long long plane = blockIdx.z;
+  const int i = blockIdx.x * 256 + threadIdx.x;
+  const int n = (b1 - b0) * wB;
+  if (i >= n) return;
+  const int jb = b0 + i / wB, xx = i % wB;
+  const float* src = T + plane * (long long)hC * wB + xx;
+  const int c0 = 4 * (jb - kPB) + kPC - kRD;
+  float acc = 0.f;
+#pragma unroll
+  for (int t = 0; t <= 2 * kRD; ++t) acc = fmaf(gd(t), __ldg(src + (long long)min(max(c0 + t, 0), hC - 1) * wB), acc);
+  B[(plane * hB + jb) * (long long)wB + xx] = acc;
+}
+
+// ---- level B -> level C: Gaussian-weighted x4 upsample ------------------------------------------
+// C sample jc sits at u = (jc-PC)/4 + PB in B samples; taps j0-4..j0+4 around j0 = round(u) with
+// weights exp(-(j-u)^2/2), normalised per phase (phase = (jc-PC) mod 4).
+struct UpWeights { float w[4][2 * kTU + 1]; };
+__device__ __forceinline__ void up_bc_phase(int jc, int& j0, int& ph) {
+  const int d = jc - kPC + 4;  // >= 0
+  ph = d & 3;
+  j0 = (d >> 2) - 1 + kPB + (ph >= 2 ? 1 : 0);
+}
+// x pass on B rows [b0, b1): T2[plane][jb][jc] (hB x wC)
+__global__ void __launch_bounds__(256)
+up_bc_x_kernel(const float* __restrict__ SB, float* __restrict__ T2, int hB, int wB, int wC, int b0, int b1,
+               const __grid_constant__ UpWeights uw) {
+  const long long plane = blockIdx.z;
+  const int i = blockIdx.x * 256 + threadIdx.x;
+  const int n = (b1 - b0) * wC;
+  if (i >= n) return;
+  const int jb = b0 + i / wC, jc = i % wC;
+  int j0, ph;
+  up_bc_phase(jc, j0, ph);
+  const float* src = SB + (plane * hB + jb) * (long long)wB;
+  float acc = 0.f;
+#pragma unroll
+  for (int t = 0; t <= 2 * kTU; ++t) acc = fmaf(uw.w[ph][t], __ldg(src + min(max(j0 - kTU + t, 0), wB - 1)), acc);
+  T2[(plane * hB + jb) * (long long)wC + jc] = acc;
+}
+// y pass for C rows [c0, c1): SC[plane][jc][x] (hC x wC)
+__global__ void __launch_bounds__(256)
+up_bc_y_kernel(const float* __restrict__ T2, float* __restrict__ SC, int hB, int hC, int wC, int c0, int c1,
+               const __grid_constant__ UpWeights uw) {
+  const long long plane = blockIdx.z;
+  const int i = blockIdx.x * 256 + threadIdx.x;
+  const int n = (c1 - c0) * wC;
+  if (i >= n) return;
+  const int jc = c0 + i / wC, xx = i % wC;
+  int j0, ph;
+  up_bc_phase(jc, j0, ph);
+  const float* src = T2 + plane * (long long)hB * wC + xx;
+  float acc = 0.f;
+#pragma unroll
+  for (int t = 0; t <= 2 * kTU; ++t)
+    acc = fmaf(uw.w[ph][t], __ldg(src + (long long)min(max(j0 - kTU + t, 0), hB - 1) * wC), acc);
+  SC[(plane * hC + jc) * (long long)wC + xx] = acc;
+}
+
+// ---- K5: x4 Lagrange upsample of every scale's surround + MSRCR epilogue -------------------------
+// Thread t of a 128-thread CTA owns coarse column jc0-2+t for the vertical stage and the 4-pixel
+// cell t-2 (123 cells = 492 pixels per CTA) for the horizontal stage.  It walks down a strip of
+// rows four at a time (one coarse row per step) with the 6 / 4 coarse rows each scale needs held
+// in registers, so a step costs one new coarse sample per (scale, channel).  Per step: vertical
+// interpolation at the 4 row phases -> shared memory (double-buffered, one barrier per step) ->
+// per row: 6 / 4 neighbouring columns from shared memory, horizontal interpolation of the cell's
+// 4 pixels, lg2, accumulate, epilogue, 128-bit stores.
+struct FinalParams {
+  const float* map[3];  // per scale: planar [n][3][hC][wC]; the N6 six-tap scales first
+  float w2[3];          // ln2 * weight_k
+  float wsum2;          // ln2 * sum of all weights (including earlier passes)
+  int hC, wC;
+  float beta_ln_alpha, beta_ln2, gain255, offset255, in_scale, in_bias;
+  const float* acc_in;  // optional partial sums  sum_k w2_k lg2 S_k  from an earlier pass (image layout)
+  float* acc_out;       // if set: write the partial sums instead of the finished pixels
+};
+
+constexpr int kFinalCells = 123;
+
+enum { kIoNhwcVec = 0, kIoNchwVec = 1, kIoScalar = 2 };
+
+// 4 pixels x 3 channels of one row of the cell: f[px][c]
+__device__ __forceinline__ void final_load(const float* __restrict__ x, const ImgView& v, int io, long long img,
+                                           int yl, int X0, int W, float (&f)[4][3]) {
+  if (io == kIoNhwcVec) {
+    const float4* p = reinterpret_cast<const float4*>(x + img * v.sn + (long long)yl * v.sy + (long long)X0 * 3);
+    const float4 a = __ldg(p), b = __ldg(p + 1), c = __ldg(p + 2);
+    f[0][0] = a.x; f[0][1] = a.y; f[0][2] = a.z; f[1][0] = a.w; f[1][1] = b.x; f[1][2] = b.y;
+    f[2][0] = b.z; f[2][1] = b.w; f[2][2] = c.x; f[3][0] = c.y; f[3][1] = c.z; f[3][2] = c.w;
+  } else if (io == kIoNchwVec) {
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      const float4 a = __ldg(reinterpret_cast<const float4*>(x + img * v.sn + c * v.sc + (long long)yl * v.sy + X0));
+      f[0][c] = a.x; f[1][c] = a.y; f[2][c] = a.z; f[3][c] = a.w;
+    }
+  } else {
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int c = 0; c < 3; ++c)
+        f[i][c] = (X0 + i < W) ? __ldg(x + img * v.sn + c * v.sc + (long long)yl * v.sy + (long long)(X0 + i) * v.sx) : 0.f;
+  }
+}
+__device__ __forceinline__ void final_store(float* __restrict__ o, const ImgView& v, int io, long long img, int yl,
+                                            int X0, int W, const float (&f)[4][3]) {
+  if (io == kIoNhwcVec) {
+    float4* p = reinterpret_cast<float4*>(o + img * v.sn + (long long)yl * v.sy + (long long)X0 * 3);
+    p[0] = make_float4(f[0][0], f[0][1], f[0][2], f[1][0]);
+    p[1] = make_float4(f[1][1], f[1][2], f[2][0], f[2][1]);
+    p[2] = make_float4(f[2][2], f[3][0], f[3][1], f[3][2]);
+  } else if (io == kIoNchwVec) {
+#pragma unroll
+    for (int c = 0; c < 3; ++c)
+      *reinterpret_cast<float4*>(o + img * v.sn + c * v.sc + (long long)yl * v.sy + X0) =
+          make_float4(f[0][c], f[1][c], f[2][c], f[3][c]);
+  } else {
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int c = 0; c < 3; ++c)
+        if (X0 + i < W) o[img * v.sn + c * v.sc + (long long)yl * v.sy + (long long)(X0 + i) * v.sx] = f[i][c];
+  }
+}
+
+// x / out point at image row in_row0 (row-tiled shards); rows [row_begin, row_end) are produced,
+// row_begin a multiple of 4, rows_per_strip a multiple of 4.
+template <int N6, int N4>
+__global__ void __launch_bounds__(128, 4)
+msrcr_final_kernel(const float* __restrict__ x, float* __restrict__ out, ImgView v, int io, int W, int in_row0,
+                   int row_begin, int row_end, int rows_per_strip, const __grid_constant__ FinalParams p) {
+  constexpr int NV = 3 * (N6 + N4);
+  __shared__ float s_v[2][4][NV][128];
+  const int t = threadIdx.x;
+  const long long img = blockIdx.z;
+  const int cell0 = blockIdx.x * kFinalCells;
+  const int jcv = min(max(kPC + cell0 - 2 + t, 0), p.wC - 1);  // coarse column of the vertical duty
+  const int cell = t - 2;
+  const int X0 = 4 * (cell0 + cell);
+  const bool h_on = cell >= 0 && cell < kFinalCells && X0 < W;
+  const int ys = row_begin + blockIdx.y * rows_per_strip;
+  const int ye = min(ys + rows_per_strip, row_end);
+  if (ys >= ye) return;
+  const int hC = p.hC, wC = p.wC;
+
+  const float* m6[N6 > 0 ? N6 : 1];
+  const float* m4[N4 > 0 ? N4 : 1];
+#pragma unroll
+  for (int k = 0; k < N6; ++k) m6[k] = p.map[k] + img * 3ll * hC * wC + jcv;
+#pragma unroll
+  for (int k = 0; k < N4; ++k) m4[k] = p.map[N6 + k] + img * 3ll * hC * wC + jcv;
+  auto ld = [&](const float* m, int c, int row) { return __ldg(m + ((long long)c * hC + min(row, hC - 1)) * wC); };
+
+  // windows: win6 rows j0-2..j0+3, win4 rows j0-1..j0+2 of the current step
+  float win6[N6 > 0 ? N6 : 1][3][6], win4[N4 > 0 ? N4 : 1][3][4];
+  const int jfirst = ys / 4 + kPC;
+#pragma unroll
+  for (int k = 0; k < N6; ++k)
+#pragma unroll
+    for (int c = 0; c < 3; ++c)
+#pragma unroll
+      for (int i = 0; i < 6; ++i) win6[k][c][i] = ld(m6[k], c, jfirst - 2 + i);
+#pragma unroll
+  for (int k = 0; k < N4; ++k)
+#pragma unroll
+    for (int c = 0; c < 3; ++c)
+#pragma unroll
+      for (int i = 0; i < 4; ++i) win4[k][c][i] = ld(m4[k], c, jfirst - 1 + i);
+
+  const int nsteps = (ye - ys + 3) / 4;
+  for (int s = 0; s < nsteps; ++s) {
+    const int Y0 = ys + 4 * s, j0 = Y0 / 4 + kPC;
+    float (*sv)[NV][128] = s_v[s & 1];
+    // prefetch the next step's new coarse rows
+    float n6[N6 > 0 ? N6 : 1][3], n4[N4 > 0 ? N4 : 1][3];
+#pragma unroll
+    for (int k = 0; k < N6; ++k)
+#pragma unroll
+      for (int c = 0; c < 3; ++c) n6[k][c] = ld(m6[k], c, j0 + 4);
+#pragma unroll
+    for (int k = 0; k < N4; ++k)
+#pragma unroll
+      for (int c = 0; c < 3; ++c) n4[k][c] = ld(m4[k], c, j0 + 3);
+    // vertical stage
+#pragma unroll
+    for (int k = 0; k < N6; ++k)
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        const float* w = win6[k][c];
+        sv[0][k * 3 + c][t] = w[2];
+#pragma unroll
+        for (int ph = 1; ph < 4; ++ph) {
+          float a = kL6[ph - 1][0] * w[0];
+#pragma unroll
+          for (int i = 1; i < 6; ++i) a = fmaf(kL6[ph - 1][i], w[i], a);
+          sv[ph][k * 3 + c][t] = a;
+        }
+      }
+#pragma unroll
+    for (int k = 0; k < N4; ++k)
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        const float* w = win4[k][c];
+        sv[0][(N6 + k) * 3 + c][t] = w[1];
+#pragma unroll
+        for (int ph = 1; ph < 4; ++ph) {
+          float a = kL4[ph - 1][0] * w[0];
+#pragma unroll
+          for (int i = 1; i < 4; ++i) a = fmaf(kL4[ph - 1][i], w[i], a);
+          sv[ph][(N6 + k) * 3 + c][t] = a;
+        }
+      }
+    __syncthreads();
+    // horizontal stage + epilogue, one image row per phase
+    if (h_on) {
+#pragma unroll 1
+      for (int ph = 0; ph < 4; ++ph) {
+        const int Y = Y0 + ph;
+        if (Y >= ye) break;
+        const int yl = Y - in_row0;
+        float f[4][3], acc[4][3];
+        final_load(x, v, io, img, yl, X0, W, f);
+        if (p.acc_in) {
+          final_load(p.acc_in, v, io, img, yl, X0, W, acc);
+        } else {
+#pragma unroll
+          for (int i = 0; i < 4; ++i)
+#pragma unroll
+            for (int c = 0; c < 3; ++c) acc[i][c] = 0.f;
+        }
+#pragma unroll
+        for (int k = 0; k < N6; ++k)
+#pragma unroll
+          for (int c = 0; c < 3; ++c) {
+            float w[6];
+#pragma unroll
+            for (int i = 0; i < 6; ++i) w[i] = sv[ph][k * 3 + c][cell + i];
+            acc[0][c] = fmaf(p.w2[k], __log2f(w[2]), acc[0][c]);
+#pragma unroll
+            for (int q = 1; q < 4; ++q) {
+              float a = kL6[q - 1][0] * w[0];
+#pragma unroll
+              for (int i = 1; i < 6; ++i) a = fmaf(kL6[q - 1][i], w[i], a);
+              acc[q][c] = fmaf(p.w2[k], __log2f(a), acc[q][c]);
+            }
+          }
+#pragma unroll
+        for (int k = 0; k < N4; ++k)
+#pragma unroll
+          for (int c = 0; c < 3; ++c) {
+            float w[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) w[i] = sv[ph][(N6 + k) * 3 + c][cell + 1 + i];
+            acc[0][c] = fmaf(p.w2[N6 + k], __log2f(w[1]), acc[0][c]);
+#pragma unroll
+            for (int q = 1; q < 4; ++q) {
+              float a = kL4[q - 1][0] * w[0];
+#pragma unroll
+              for (int i = 1; i < 4; ++i) a = fmaf(kL4[q - 1][i], w[i], a);
+              acc[q][c] = fmaf(p.w2[N6 + k], __log2f(a), acc[q][c]);
+            }
+          }
+        if (p.acc_out) {
+          final_store(p.acc_out, v, io, img, yl, X0, W, acc);
+        } else {
+          float o[4][3];
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            float I[3], l[3];
+#pragma unroll
+            for (int c = 0; c < 3; ++c) {
+              I[c] = fmaf(p.in_scale, f[i][c], p.in_bias);
+              l[c] = __log2f(I[c]);
+            }
+            const float lsum = __log2f(I[0] + I[1] + I[2]);
+#pragma unroll
+            for (int c = 0; c < 3; ++c) {
+              const float R = fmaf(p.wsum2, l[c], -acc[i][c]);
+              const float Cc = fmaf(p.beta_ln2, l[c] - lsum, p.beta_ln_alpha);
+              o[i][c] = __saturatef(fmaf(p.gain255 * Cc, R, p.offset255));
+            }
+          }
+          final_store(out, v, io, img, yl, X0, W, o);
+        }
+      }
+    }
+    // slide the windows down one coarse row
+#pragma unroll
+    for (int k = 0; k < N6; ++k)
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+#pragma unroll
+        for (int i = 0; i < 5; ++i) win6[k][c][i] = win6[k][c][i + 1];
+        win6[k][c][5] = n6[k][c];
+      }
+#pragma unroll
+    for (int k = 0; k < N4; ++k)
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+#pragma unroll
+        for (int i = 0; i < 3; ++i) win4[k][c][i] = win4[k][c][i + 1];
+        win4[k][c][3] = n4[k][c];
+      }
+  }
+}
+
+}  // namespace
+}  // namespace llie

@@ -1,157 +1,196 @@
-// MSRCR, fast path (LLIE_BLUR_PYRAMID): every Gaussian surround is evaluated as a cascade
-//     prefilter+decimate  ->  small Gaussian at low resolution  ->  Gaussian-weighted upsample
-// whose cost per pixel does not depend on sigma, and the upsample is fused with the per-pixel
-// log / ratio / colour-restoration / gain-offset epilogue (north_star kernel (1); SURVEY.md 8(a)
-// units a1-a4; spec SURVEY.md 9.1).  No reference file exists to cite (/root/reference/README.md:1-2).
+// MSRCR, fast path (LLIE_BLUR_PYRAMID): host-side planner and launch sequence of the decimated
+// Gaussian cascade in msrcr_kernels.cuh (north_star kernel (1); SURVEY.md 8(a) units a1-a4; spec
+// SURVEY.md 9.1).  No reference file exists to cite (/root/reference/README.md:1-2).
 //
 // Why a cascade: a direct 4-sigma FIR costs 33 kFLOP/pixel and tops out at 3.7 % of the HBM
-// roofline.  Gaussians compose (variances add), a Gaussian-prefiltered image
-// can be decimated with aliasing below 1e-9, and a unit-sigma Gaussian sampled on a unit grid is
-// a partition of unity to 5e-9, so it doubles as the interpolator.  Two levels are kept:
-//   level A: stride 2   (prefilter sigma 2, radius 8, on I = in_scale*x + in_bias)
-//   level B: stride 16  (level A prefiltered with sigma 8, radius 32, decimated by 8)
-// A scale with 4 <= sigma < 40 is blurred on A, a scale with sigma >= 40 on B.  The low-res sigma
-// and radius are chosen by a host-side planner that minimises the L1 distance between the
-// cascade's effective kernel and the oracle's truncated Gaussian (tools/pyramid_tune.py is the
-// NumPy twin of that planner).  Edge clamping is exact: every level stores enough samples beyond
-// the image border to reach the region where the clamped, prefiltered signal is constant.
+// roofline.  Gaussians compose (variances add) and a Gaussian-prefiltered image
+// can be decimated with aliasing below 1e-8, so every surround is evaluated at stride 4 or 16 and
+// brought back by interpolation.  The planner picks, per scale, the low-resolution Gaussian
+// (sigma_low, radius_low) that minimises the L1 distance between the cascade's effective kernel
+// and the oracle's truncated Gaussian.
 //
-// HBM traffic: the image is read twice (12 B/px each) and written once (12 B/px); level A adds
-// ~3 B/px per touch, level B is negligible.  SURVEY.md 8(d)'s two-pass figure is 108 B/px.
+// HBM traffic per pixel: the image is read twice (12 B each) and written once (12 B); the stride-4
+// intermediates add ~3 B (V) + ~3 B (level-C maps).  SURVEY.md 8(d)'s two-pass figure is 108 B/px.
 #include "fir.cuh"
+#include "msrcr_kernels.cuh"
 
+#include <algorithm>
 #include <cmath>
+#include <cstring>
 #include <mutex>
 
 namespace llie {
 
 namespace {
 
-constexpr int kT = 4;         // upsample half-width in low-res samples (2*kT+1 taps)
-constexpr int kRA = 8;        // level-A prefilter radius (full-res pixels), sigma 2
-constexpr int kPA = 4;        // level-A samples stored before pixel 0
-constexpr int kRB = 32;       // level-B prefilter radius (level-A samples), sigma 8
-constexpr int kPB = 5;        // level-B samples stored before pixel 0
-constexpr double kSigA = 2.0, kSigB = 8.0, kSigUp = 1.0;
-
-inline int level_a_size(int n0) { return (n0 + 8) / 2 + 9; }
-inline int level_b_size(int n0) { return (n0 + 86) / 16 + 10; }
-
-std::vector<double> gauss_taps(double sigma, int r, double offs = 0.0) {
+std::vector<double> gauss_taps(double sigma, int r) {
   std::vector<double> k(2 * r + 1);
   double sum = 0;
-  for (int t = -r; t <= r; ++t) {
-    double d = t - offs;
-    sum += (k[t + r] = std::exp(-d * d / (2 * sigma * sigma)));
-  }
+  for (int t = -r; t <= r; ++t) sum += (k[t + r] = std::exp(-(double)t * t / (2 * sigma * sigma)));
   for (double& v : k) v /= sum;
   return k;
 }
 
-// weights of the Gaussian upsampler for phase ph of stride s: taps j0-kT .. j0+kT
-std::vector<double> upsample_weights(int s, int ph) {
-  double shift = (ph >= s / 2 ? 1.0 : 0.0) - (double)ph / s;  // (j0 - P) - X/s
-  std::vector<double> w(2 * kT + 1);
+// weights of the B -> C Gaussian upsampler for phase ph: taps j0-4 .. j0+4, j0 - u = [ph>=2] - ph/4
+void up_weights(int ph, double (&w)[2 * kTU + 1]) {
+  const double shift = (ph >= 2 ? 1.0 : 0.0) - ph / 4.0;
   double sum = 0;
-  for (int t = 0; t <= 2 * kT; ++t) {
-    double d = shift - kT + t;
-    sum += (w[t] = std::exp(-d * d / (2 * kSigUp * kSigUp)));
+  for (int t = 0; t <= 2 * kTU; ++t) {
+    const double d = shift - kTU + t;
+    sum += (w[t] = std::exp(-d * d / 2.0));
   }
   for (double& v : w) v /= sum;
-  return w;
+}
+
+void lagrange_weights(int T, double frac, double* w) {  // offsets -(T/2-1) .. T/2
+  for (int i = 0; i < T; ++i) {
+    const double oi = i - (T / 2 - 1);
+    double v = 1;
+    for (int m = 0; m < T; ++m) {
+      if (m == i) continue;
+      const double om = m - (T / 2 - 1);
+      v *= (frac - om) / (oi - om);
+    }
+    w[i] = v;
+  }
 }
 
 // ---- planner ------------------------------------------------------------------------------
+// A finitely supported 1-D signal on an integer grid: v[i] sits at index lo + i.
+struct Sig {
+  int lo = 0;
+  std::vector<double> v;
+};
+Sig conv(const Sig& a, const std::vector<double>& k) {  // k centred (radius (len-1)/2)
+  const int r = ((int)k.size() - 1) / 2;
+  Sig o;
+  o.lo = a.lo - r;
+  o.v.assign(a.v.size() + 2 * r, 0.0);
+  for (size_t i = 0; i < a.v.size(); ++i)
+    for (int t = 0; t <= 2 * r; ++t) o.v[i + t] += a.v[i] * k[t];
+  return o;
+}
+// adjoint of "filter with g, decimate by 4": weights on coarse samples -> weights on fine samples
+Sig spread4(const Sig& a, const std::vector<double>& g) {
+  const int r = ((int)g.size() - 1) / 2;
+  Sig o;
+  o.lo = 4 * a.lo - r;
+  o.v.assign(4 * (a.v.size() - 1) + 2 * r + 1, 0.0);
+  for (size_t i = 0; i < a.v.size(); ++i)
+    for (int t = 0; t <= 2 * r; ++t) o.v[4 * i + t] += a.v[i] * g[t];
+  return o;
+}
+
 struct ScalePlan {
-  int level;          // 0 = A (stride 2), 1 = B (stride 16)
+  int level;         // 0 = C (stride 4), 1 = B (stride 16)
   int stride;
-  double sigma_low;   // in low-res samples
+  double sigma_low;  // in low-res samples
   int radius_low;
-  double l1;          // L1 distance of the effective kernel to the oracle kernel
+  double l1;         // L1 distance of the effective kernel to the oracle kernel (phase average)
   std::vector<float> taps;
 };
 
-// full-res impulse response of "prefilter + decimate" seen from one low-res sample
-std::vector<double> prefilter_fullres(int level) {
-  std::vector<double> ga = gauss_taps(kSigA, kRA);
-  if (level == 0) return ga;
-  std::vector<double> gb = gauss_taps(kSigB, kRB);
-  std::vector<double> g(2 * (2 * kRB + kRA) + 1, 0.0);  // support +-(2*32+8)
-  const int c = 2 * kRB + kRA;
-  for (int m = -kRB; m <= kRB; ++m)
-    for (int t = -kRA; t <= kRA; ++t) g[c + 2 * m + t] += gb[m + kRB] * ga[t + kRA];
-  return g;
+// weights on level-C samples (index j at position 4j) that the final Lagrange step applies for pixel ph
+Sig lagrange_sig(int T, int ph) {
+  Sig s;
+  const int jc0 = ph >> 2, f = ph & 3;
+  if (f == 0) {
+    s.lo = jc0;
+    s.v = {1.0};
+    return s;
+  }
+  s.lo = jc0 - (T / 2 - 1);
+  s.v.resize(T);
+  lagrange_weights(T, f / 4.0, s.v.data());
+  return s;
+}
+// weights on level-B samples (index j at position 16j) equivalent to weights on level-C samples
+Sig through_upsampler(const Sig& c) {
+  Sig b;
+  int lo = 1 << 30, hi = -(1 << 30);
+  for (size_t i = 0; i < c.v.size(); ++i) {
+    const int jc = c.lo + (int)i;
+    const int fl = (int)std::floor(jc / 4.0), ph = jc - 4 * fl;
+    const int j0 = fl + (ph >= 2 ? 1 : 0);
+    lo = std::min(lo, j0 - kTU);
+    hi = std::max(hi, j0 + kTU);
+  }
+  b.lo = lo;
+  b.v.assign(hi - lo + 1, 0.0);
+  for (size_t i = 0; i < c.v.size(); ++i) {
+    const int jc = c.lo + (int)i;
+    const int fl = (int)std::floor(jc / 4.0), ph = jc - 4 * fl;
+    const int j0 = fl + (ph >= 2 ? 1 : 0);
+    double w[2 * kTU + 1];
+    up_weights(ph, w);
+    for (int t = 0; t <= 2 * kTU; ++t) b.v[j0 - kTU + t - lo] += c.v[i] * w[t];
+  }
+  return b;
 }
 
-double cascade_l1(int s, const std::vector<double>& gpre, const std::vector<std::vector<double>>& wup,
-                  const std::vector<double>& klow, const std::vector<double>& kor) {
-  const int rl = ((int)klow.size() - 1) / 2, rp = ((int)gpre.size() - 1) / 2, ro = ((int)kor.size() - 1) / 2;
-  const int nc = 2 * (rl + kT) + 1;              // composite low-res kernel w * klow, centred on j0
-  const int span = s * (rl + kT + 1) + rp + s;   // |delta| bound of the effective kernel
-  std::vector<double> c(nc), e(2 * span + 1);
+double cascade_l1(int level, const std::vector<Sig>& left, const std::vector<double>& gd, const std::vector<double>& klow,
+                  const std::vector<double>& kor) {
+  const int ro = ((int)kor.size() - 1) / 2;
   double total = 0;
-  for (int ph = 0; ph < s; ++ph) {
-    std::fill(c.begin(), c.end(), 0.0);
-    for (int t = 0; t <= 2 * kT; ++t)
-      for (int m = 0; m <= 2 * rl; ++m) c[t + m] += wup[ph][t] * klow[m];
-    std::fill(e.begin(), e.end(), 0.0);
-    // low-res sample j0 + q sits at full-res offset s*(q + [ph >= s/2]) - ph from the pixel
-    const int base = s * (ph >= s / 2 ? 1 : 0) - ph;
-    for (int q = -(rl + kT); q <= rl + kT; ++q) {
-      const double cq = c[q + rl + kT];
-      const int off = base + s * q + span;
-      for (int t = -rp; t <= rp; ++t) e[off + t] += cq * gpre[t + rp];
-    }
+  for (size_t ph = 0; ph < left.size(); ++ph) {
+    Sig e = conv(left[ph], klow);
+    if (level) e = spread4(e, gd);
+    e = spread4(e, gd);  // now on pixels; the pixel itself is index ph
     double l1 = 0;
-    for (int d = -span; d <= span; ++d) {
-      double ko = (d >= -ro && d <= ro) ? kor[d + ro] : 0.0;
-      l1 += std::fabs(e[d + span] - ko);
+    const int lo = std::min(e.lo, (int)ph - ro), hi = std::max(e.lo + (int)e.v.size() - 1, (int)ph + ro);
+    for (int xx = lo; xx <= hi; ++xx) {
+      const double ev = (xx >= e.lo && xx < e.lo + (int)e.v.size()) ? e.v[xx - e.lo] : 0.0;
+      const int d = xx - (int)ph;
+      const double ko = (d >= -ro && d <= ro) ? kor[d + ro] : 0.0;
+      l1 += std::fabs(ev - ko);
     }
     total += l1;
   }
-  return total / s;
+  return total / left.size();
 }
 
+constexpr double kMinSigma = 12.0;  // below this the stride-4 grid is too coarse for 1e-4 parity
+constexpr double kLevelBSigma = 40.0;
+
 int plan_scale(double sigma, double truncate, ScalePlan* out) {
-  const int level = sigma >= 40.0 ? 1 : 0;
-  const int s = level ? 16 : 2;
-  const double var_pre = level ? (kSigA * kSigA + 4.0 * kSigB * kSigB) : kSigA * kSigA;
-  const double var_up = kSigUp * kSigUp * s * s;
-  const double rest = sigma * sigma - var_pre - var_up;
-  if (rest < s * s * 1.0) {
-    set_error("pyramid blur needs sigma >= 4 (got %g); use blur=direct for small scales", sigma);
+  if (sigma < kMinSigma) {
+    set_error("pyramid blur needs sigma >= %g (got %g); use blur=direct for small scales", kMinSigma, sigma);
     return LLIE_E_ARG;
   }
-  const double sl0 = std::sqrt(rest) / s;
+  const int level = sigma >= kLevelBSigma ? 1 : 0;
+  const int s = level ? 16 : 4;
+  const double var_fixed = level ? (16.0 + 256.0 + 256.0) : 16.0;  // prefilters (+ upsampler), pixel^2
+  const double sl0 = std::sqrt(sigma * sigma - var_fixed) / s;
   const int ro = (int)std::ceil(truncate * sigma);
   const std::vector<double> kor = gauss_taps(sigma, ro);
-  const std::vector<double> gpre = prefilter_fullres(level);
-  std::vector<std::vector<double>> wup(s);
-  for (int ph = 0; ph < s; ++ph) wup[ph] = upsample_weights(s, ph);
-
+  const std::vector<double> gd = gauss_taps(4.0, kRD);
+  std::vector<Sig> left;
+  for (int ph = 0; ph < s; ++ph) {
+    Sig c = lagrange_sig(level ? 4 : 6, ph);
+    left.push_back(level ? through_upsampler(c) : c);
+  }
   double best_l1 = 1e30, best_sl = sl0;
   int best_rl = 1;
   const int rl_mid = ro / s;
   for (int rl = std::max(1, rl_mid - 2); rl <= rl_mid + 1; ++rl) {
-    // golden-section search of sigma_low in [0.97, 1.03] * sl0
-    double a = 0.97 * sl0, b = 1.03 * sl0;
+    double a = 0.97 * sl0, b = 1.03 * sl0;  // golden-section search of sigma_low
     const double gr = 0.6180339887498949;
     double x1 = b - gr * (b - a), x2 = a + gr * (b - a);
-    double f1 = cascade_l1(s, gpre, wup, gauss_taps(x1, rl), kor);
-    double f2 = cascade_l1(s, gpre, wup, gauss_taps(x2, rl), kor);
-    for (int it = 0; it < 36; ++it) {
+    double f1 = cascade_l1(level, left, gd, gauss_taps(x1, rl), kor);
+    double f2 = cascade_l1(level, left, gd, gauss_taps(x2, rl), kor);
+    for (int it = 0; it < 32; ++it) {
       if (f1 < f2) {
         b = x2; x2 = x1; f2 = f1;
         x1 = b - gr * (b - a);
-        f1 = cascade_l1(s, gpre, wup, gauss_taps(x1, rl), kor);
+        f1 = cascade_l1(level, left, gd, gauss_taps(x1, rl), kor);
       } else {
         a = x1; x1 = x2; f1 = f2;
         x2 = a + gr * (b - a);
-        f2 = cascade_l1(s, gpre, wup, gauss_taps(x2, rl), kor);
+        f2 = cascade_l1(level, left, gd, gauss_taps(x2, rl), kor);
       }
     }
-    const double x = f1 < f2 ? x1 : x2, f = f1 < f2 ? f1 : f2;
-    if (f < best_l1) { best_l1 = f; best_sl = x; best_rl = rl; }
+    const double xb = f1 < f2 ? x1 : x2, fb = f1 < f2 ? f1 : f2;
+    if (fb < best_l1) { best_l1 = fb; best_sl = xb; best_rl = rl; }
   }
   out->level = level;
   out->stride = s;
@@ -180,213 +219,16 @@ int get_scale_plan(float sigma, float truncate, ScalePlan* out) {
   return LLIE_OK;
 }
 
-// ---- kernels ------------------------------------------------------------------------------
-struct TapsA { float g[2 * kRA + 1]; };
-
-// Level A: A[c][jy][jx] = sum_{ty,tx} g[ty] g[tx] I[clamp(2(jy-P)+ty-8)][clamp(2(jx-P)+tx-8)][c]
-// A CTA produces a 32x16 tile of A from an 80x48 pixel patch staged in shared memory
-// (row filter at the decimated columns, then column filter at the decimated rows).
-// in: image rows [in_row0, in_row0+in_rows) of an H-row image; out: A rows [a_row0, a_row0+a_rows).
-constexpr int kDAW = 32, kDAH = 16, kDPW = 2 * kDAW + 2 * kRA, kDPH = 2 * kDAH + 2 * kRA;  // 80 x 48
-
-__global__ void __launch_bounds__(256)
-down2_kernel(const float* __restrict__ x, ImgView v, int H, int W, int in_row0, float* __restrict__ A, int hA_buf,
-             int wA, int a_row0, float in_scale, float in_bias, const __grid_constant__ TapsA taps) {
-  extern __shared__ __align__(16) float s_dyn[];
-  float (*s_in)[kDPH][kDPW] = reinterpret_cast<float (*)[kDPH][kDPW]>(s_dyn);
-  float (*s_tmp)[kDPH][kDAW] = reinterpret_cast<float (*)[kDPH][kDAW]>(s_dyn + 3 * kDPH * kDPW);
-  const int tid = threadIdx.x;
-  const long long img = blockIdx.z;
-  const int jx0 = blockIdx.x * kDAW, jyb0 = blockIdx.y * kDAH;  // jyb0: buffer row of A
-  const int X0 = 2 * (jx0 - kPA) - kRA, Y0 = 2 * (a_row0 + jyb0 - kPA) - kRA;
-  const float* src = x + img * v.sn;
-  if (v.sx == 3) {  // NHWC: walk (row, x*3+c) so that consecutive threads read consecutive floats
-    for (int i = tid; i < kDPH * kDPW * 3; i += 256) {
-      int row = i / (kDPW * 3), e = i - row * (kDPW * 3);
-      int px = e / 3, c = e - px * 3;
-      int Y = min(max(Y0 + row, 0), H - 1) - in_row0, X = min(max(X0 + px, 0), W - 1);
-      s_in[c][row][px] = fmaf(in_scale, __ldg(src + (long long)Y * v.sy + (long long)X * 3 + c), in_bias);
-    }
-  } else {
-    for (int i = tid; i < kDPH * kDPW * 3; i += 256) {
-      int c = i / (kDPH * kDPW), rem = i - c * (kDPH * kDPW);
-      int row = rem / kDPW, px = rem - row * kDPW;
-      int Y = min(max(Y0 + row, 0), H - 1) - in_row0, X = min(max(X0 + px, 0), W - 1);
-      s_in[c][row][px] = fmaf(in_scale, __ldg(src + c * v.sc + (long long)Y * v.sy + (long long)X * v.sx), in_bias);
-    }
-  }
-  __syncthreads();
-  for (int i = tid; i < 3 * kDPH * kDAW; i += 256) {
-    int jx = i % kDAW, row = (i / kDAW) % kDPH, c = i / (kDAW * kDPH);
-    const float* p = &s_in[c][row][2 * jx];
-    float acc = 0.f;
-#pragma unroll
-    for (int t = 0; t <= 2 * kRA; ++t) acc = fmaf(taps.g[t], p[t], acc);
-    s_tmp[c][row][jx] = acc;
-  }
-  __syncthreads();
-  for (int i = tid; i < 3 * kDAH * kDAW; i += 256) {
-    int jx = i % kDAW, jy = (i / kDAW) % kDAH, c = i / (kDAW * kDAH);
-    if (jx0 + jx >= wA || jyb0 + jy >= hA_buf) continue;
-    float acc = 0.f;
-#pragma unroll
-    for (int t = 0; t <= 2 * kRA; ++t) acc = fmaf(taps.g[t], s_tmp[c][2 * jy + t][jx], acc);
-    A[((img * 3 + c) * hA_buf + jyb0 + jy) * (long long)wA + jx0 + jx] = acc;
-  }
-}
-
-// Level B, row pass: T[plane][row][jx] = sum_t g[t] A[plane][row][clamp(8(jx-PB)+PA+t-32)]
-__global__ void down8_rows_kernel(const float* __restrict__ A, float* __restrict__ T, const float* __restrict__ g,
-                                  long long rows_total, int wA, int wB) {
-  long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
-  if (i >= rows_total * wB) return;
-  long long row = i / wB;
-  int jx = (int)(i - row * wB);
-  const float* src = A + row * wA;
-  const int c0 = 8 * (jx - kPB) + kPA - kRB;
-  float acc = 0.f;
-  for (int t = 0; t <= 2 * kRB; ++t) acc = fmaf(g[t], __ldg(src + min(max(c0 + t, 0), wA - 1)), acc);
-  T[i] = acc;
-}
-
-// Level B, column pass: B[plane][jy][jx] = sum_t g[t] T[plane][clamp(8(jy-PB)+PA+t-32) - a_row0][jx]
-__global__ void down8_cols_kernel(const float* __restrict__ T, float* __restrict__ B, const float* __restrict__ g,
-                                  int planes, int hA, int hA_buf, int a_row0, int wB, int hB_buf, int b_row0) {
-  long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
-  if (i >= (long long)planes * hB_buf * wB) return;
-  int jx = (int)(i % wB);
-  int jyb = (int)((i / wB) % hB_buf);
-  long long plane = i / ((long long)wB * hB_buf);
-  const float* src = T + plane * (long long)hA_buf * wB + jx;
-  const int r0 = 8 * (b_row0 + jyb - kPB) + kPA - kRB;
-  float acc = 0.f;
-  for (int t = 0; t <= 2 * kRB; ++t)
-    acc = fmaf(g[t], __ldg(src + (long long)(min(max(r0 + t, 0), hA - 1) - a_row0) * wB), acc);
-  B[i] = acc;
-}
-
-// Final pass: Gaussian upsample of every scale's low-res surround + MSRCR epilogue.
-struct FinalParams {
-  int n_scales;
-  int level[LLIE_MAX_SCALES];
-  float weight[LLIE_MAX_SCALES];
-  const float* map[LLIE_MAX_SCALES];  // planar [n][3][rows_buf][wL]
-  int rows_buf[2], wL[2], row0[2];    // per level: buffer rows, width, level row held by buffer row 0
-  float log_alpha, beta, gain, offset, in_scale, in_bias;
-  float wup_a[2][2 * kT + 1];
-  float wup_b[16][2 * kT + 1];
-};
-
-constexpr int kFX = 64, kFY = 32;                      // output tile
-constexpr int kSrcRowsA = kFY / 2 + 2 * kT + 1;        // 25
-constexpr int kSrcColsA = kFX / 2 + 2 * kT + 1;        // 41
-constexpr int kSrcRowsB = kFY / 16 + 2 * kT + 1;       // 11
-constexpr int kSrcColsB = kFX / 16 + 2 * kT + 1;       // 13
-
-__global__ void __launch_bounds__(256)
-msrcr_final_kernel(const float* __restrict__ x, float* __restrict__ out, ImgView v, int rows, int W, int row_g0,
-                   const __grid_constant__ FinalParams p) {
-  __shared__ float s_src[3 * kSrcRowsA * kSrcColsA];   // low-res patch of the current scale
-  __shared__ float s_h[3 * kSrcRowsA * kFX];           // horizontally upsampled rows
-  const int tid = threadIdx.x;
-  const int lx = tid & (kFX - 1), yg = tid >> 6;       // thread: column lx, rows yg*8 .. yg*8+7
-  const int x0 = blockIdx.x * kFX, yb0 = blockIdx.y * kFY;  // yb0: row inside this buffer
-  const int Y0 = row_g0 + yb0;                         // image row of the tile (multiple of 32)
-  const long long img = blockIdx.z;
-  const int X = x0 + lx;
-  const bool x_ok = X < W;
-
-  float lI[8][3], acc[8][3];
-#pragma unroll
-  for (int q = 0; q < 8; ++q) {
-    const int yb = yb0 + yg * 8 + q;
-    const bool ok = x_ok && yb < rows;
-    const long long base = img * v.sn + (long long)yb * v.sy + (long long)X * v.sx;
-#pragma unroll
-    for (int c = 0; c < 3; ++c) {
-      lI[q][c] = ok ? fmaf(p.in_scale, __ldg(x + base + c * v.sc), p.in_bias) : 1.f;  // holds I for now
-      acc[q][c] = 0.f;
-    }
-  }
-
-  for (int k = 0; k < p.n_scales; ++k) {
-    const int lv = p.level[k];
-    const int s = lv ? 16 : 2, P = lv ? kPB : kPA;
-    const int sr = lv ? kSrcRowsB : kSrcRowsA, sc = lv ? kSrcColsB : kSrcColsA;
-    const int wL = p.wL[lv], hbuf = p.rows_buf[lv];
-    const int col0 = x0 / s + P - kT, rowb0 = Y0 / s + P - kT - p.row0[lv];
-    const float* m = p.map[k] + img * 3ll * hbuf * wL;
-    __syncthreads();  // previous scale's readers are done with s_src / s_h
-    for (int i = tid; i < 3 * sr * sc; i += 256) {
-      int cc = i % sc, rr = (i / sc) % sr, c = i / (sc * sr);
-      int gr = min(rowb0 + rr, hbuf - 1), gc = min(col0 + cc, wL - 1);
-      s_src[i] = __ldg(m + ((long long)c * hbuf + gr) * wL + gc);
-    }
-    __syncthreads();
-    {  // stage 1: horizontal upsample; this thread's column lx for every (channel, low-res row)
-      const int ph = X % s;
-      const float* wx = lv ? p.wup_b[ph] : p.wup_a[ph];
-      float w[2 * kT + 1];
-#pragma unroll
-      for (int t = 0; t <= 2 * kT; ++t) w[t] = wx[t];
-      const int lc = (lx + s / 2) / s;  // local column of tap 0
-      for (int cr = yg; cr < 3 * sr; cr += 4) {
-        const float* src = s_src + cr * sc + lc;
-        float a = 0.f;
-#pragma unroll
-        for (int t = 0; t <= 2 * kT; ++t) a = fmaf(w[t], src[t], a);
-        s_h[cr * kFX + lx] = a;
-      }
-    }
-    __syncthreads();
-    // stage 2: vertical upsample of this thread's 8 rows, then accumulate -w_k ln S
-    const float wk = p.weight[k];
-#pragma unroll
-    for (int q = 0; q < 8; ++q) {
-      const int yl = yg * 8 + q;
-      const int ph = (Y0 + yl) % s;
-      const float* wy = lv ? p.wup_b[ph] : p.wup_a[ph];
-      const int lr = (yl + s / 2) / s;
-#pragma unroll
-      for (int c = 0; c < 3; ++c) {
-        const float* src = s_h + (c * sr + lr) * kFX + lx;
-        float S = 0.f;
-#pragma unroll
-        for (int t = 0; t <= 2 * kT; ++t) S = fmaf(wy[t], src[t * kFX], S);
-        acc[q][c] = fmaf(-wk, __logf(S), acc[q][c]);
-      }
-    }
-  }
-
-  float wsum = 0.f;
-  for (int k = 0; k < p.n_scales; ++k) wsum += p.weight[k];
-#pragma unroll
-  for (int q = 0; q < 8; ++q) {
-    const int yb = yb0 + yg * 8 + q;
-    if (!x_ok || yb >= rows) continue;
-    const long long base = img * v.sn + (long long)yb * v.sy + (long long)X * v.sx;
-    const float lsum = __logf(lI[q][0] + lI[q][1] + lI[q][2]);
-#pragma unroll
-    for (int c = 0; c < 3; ++c) {
-      const float l = __logf(lI[q][c]);
-      const float R = fmaf(wsum, l, acc[q][c]);
-      const float Cc = p.beta * (p.log_alpha + l - lsum);
-      const float o = fmaf(p.gain * Cc, R, p.offset) * (1.0f / 255.0f);
-      out[base + c * v.sc] = fminf(fmaxf(o, 0.f), 1.f);
-    }
-  }
-}
-
 }  // namespace
 
 // ---- plan object held by the ctx ------------------------------------------------------------
 struct MsrcrPlan {
   llie_msrcr_params key;
   std::vector<ScalePlan> scales;
-  float* d_taps = nullptr;  // [gB(65) | scale taps ...]
+  std::vector<int> order;   // scale indices, level-C (six-tap) scales first
+  float* d_taps = nullptr;  // per-scale low-res taps
   std::vector<int> tap_off;
-  TapsA ga;
-  FinalParams fp;
+  UpWeights uw;
 };
 
 void msrcr_plan_free(MsrcrPlan* p) {
@@ -410,11 +252,6 @@ static int ensure_plan(llie_ctx* ctx, const llie_msrcr_params& p, cudaStream_t s
   MsrcrPlan* pl = new MsrcrPlan;
   pl->key = p;
   std::vector<float> host;
-  {
-    std::vector<double> gb = gauss_taps(kSigB, kRB);
-    for (double v : gb) host.push_back((float)v);
-    host.resize((host.size() + 3) & ~size_t(3));
-  }
   for (int k = 0; k < p.n_scales; ++k) {
     ScalePlan sp;
     int rc = get_scale_plan(p.sigma[k], p.truncate, &sp);
@@ -424,23 +261,13 @@ static int ensure_plan(llie_ctx* ctx, const llie_msrcr_params& p, cudaStream_t s
     host.resize((host.size() + 3) & ~size_t(3));
     pl->scales.push_back(std::move(sp));
   }
-  {
-    std::vector<double> ga = gauss_taps(kSigA, kRA);
-    for (int t = 0; t <= 2 * kRA; ++t) pl->ga.g[t] = (float)ga[t];
-  }
-  FinalParams& fp = pl->fp;
-  memset(&fp, 0, sizeof(fp));
-  fp.n_scales = p.n_scales;
-  for (int k = 0; k < p.n_scales; ++k) { fp.level[k] = pl->scales[k].level; fp.weight[k] = p.weight[k]; }
-  fp.log_alpha = (float)std::log((double)p.alpha);
-  fp.beta = p.beta; fp.gain = p.gain; fp.offset = p.offset; fp.in_scale = p.in_scale; fp.in_bias = p.in_bias;
-  for (int ph = 0; ph < 2; ++ph) {
-    auto w = upsample_weights(2, ph);
-    for (int t = 0; t <= 2 * kT; ++t) fp.wup_a[ph][t] = (float)w[t];
-  }
-  for (int ph = 0; ph < 16; ++ph) {
-    auto w = upsample_weights(16, ph);
-    for (int t = 0; t <= 2 * kT; ++t) fp.wup_b[ph][t] = (float)w[t];
+  for (int lv = 0; lv < 2; ++lv)
+    for (int k = 0; k < p.n_scales; ++k)
+      if (pl->scales[k].level == lv) pl->order.push_back(k);
+  for (int ph = 0; ph < 4; ++ph) {
+    double w[2 * kTU + 1];
+    up_weights(ph, w);
+    for (int t = 0; t <= 2 * kTU; ++t) pl->uw.w[ph][t] = (float)w[t];
   }
   cudaError_t e = cudaMalloc(&pl->d_taps, host.size() * sizeof(float));
   if (e == cudaSuccess) e = cudaMemcpy(pl->d_taps, host.data(), host.size() * sizeof(float), cudaMemcpyHostToDevice);
@@ -457,65 +284,146 @@ static int ensure_plan(llie_ctx* ctx, const llie_msrcr_params& p, cudaStream_t s
   return LLIE_OK;
 }
 
+namespace {
+
+inline int ceil_div(long long a, long long b) { return (int)((a + b - 1) / b); }
+
+// rows per strip so that the launch has at least `want` CTAs when the image allows it
+int pick_strip(int rows, long long ctas_per_strip_row, int want, int lo, int hi, int mult) {
+  int strips = std::max(1, ceil_div(want, std::max(1ll, ctas_per_strip_row)));
+  int rps = ceil_div(rows, strips);
+  rps = std::min(std::max(rps, lo), hi);
+  return (rps + mult - 1) / mult * mult;
+}
+
+template <int N6, int N4>
+void launch_final(dim3 grid, cudaStream_t st, const float* x, float* out, ImgView v, int io, int W, int in_row0,
+                  int row_begin, int row_end, int rps, const FinalParams& fp) {
+  msrcr_final_kernel<N6, N4><<<grid, 128, 0, st>>>(x, out, v, io, W, in_row0, row_begin, row_end, rps, fp);
+}
+
+}  // namespace
+
 int msrcr_pyramid_run(llie_ctx* ctx, const float* in, float* out, int n, int h, int w, int layout,
                       const llie_msrcr_params& p, cudaStream_t st) {
   LLIE_TRY(ensure_plan(ctx, p, st));
   MsrcrPlan* pl = ctx->plan;
-  const int hA = level_a_size(h), wA = level_a_size(w), hB = level_b_size(h), wB = level_b_size(w);
-  bool any_a = false, any_b = false;
-  int n_a = 0, n_b = 0;
-  for (auto& s : pl->scales) (s.level ? (any_b = true, ++n_b) : (any_a = true, ++n_a));
-  const size_t a_elems = (size_t)n * 3 * hA * wA, b_elems = (size_t)n * 3 * hB * wB;
-  void *dA, *dAt, *dAblur, *dBt, *dB, *dBt2, *dBblur;
-  LLIE_TRY(ctx->workspace("msrcr.A", a_elems * 4, &dA));
-  LLIE_TRY(ctx->workspace("msrcr.A.tmp", a_elems * 4, &dAt));
-  LLIE_TRY(ctx->workspace("msrcr.A.blur", a_elems * 4 * (n_a ? n_a : 1), &dAblur));
-  LLIE_TRY(ctx->workspace("msrcr.B.rows", (size_t)n * 3 * hA * wB * 4, &dBt));
-  LLIE_TRY(ctx->workspace("msrcr.B", b_elems * 4, &dB));
-  LLIE_TRY(ctx->workspace("msrcr.B.tmp", b_elems * 4, &dBt2));
-  LLIE_TRY(ctx->workspace("msrcr.B.blur", b_elems * 4 * (n_b ? n_b : 1), &dBblur));
+  const int hC = level_c_size(h), wC = level_c_size(w), hB = level_b_size(h), wB = level_b_size(w);
+  const int planes = n * 3;
+  const bool nhwc = layout == LLIE_NHWC;
+  const int RW = nhwc ? 3 * w : w, CS = nhwc ? 3 : 1, planes_v = nhwc ? n : planes;
+  int n_b = 0;
+  for (auto& s : pl->scales) n_b += s.level;
+  const size_t c_elems = (size_t)planes * hC * wC, b_elems = (size_t)planes * hB * wB;
+  void *dV, *dC, *dCt, *dSC, *dTB = nullptr, *dB = nullptr, *dBt = nullptr, *dSB = nullptr, *dT2 = nullptr, *dAcc = nullptr;
+  LLIE_TRY(ctx->workspace("msrcr.V", (size_t)planes_v * hC * RW * 4, &dV));
+  LLIE_TRY(ctx->workspace("msrcr.C", c_elems * 4, &dC));
+  LLIE_TRY(ctx->workspace("msrcr.C.tmp", c_elems * 4, &dCt));
+  LLIE_TRY(ctx->workspace("msrcr.SC", c_elems * 4 * p.n_scales, &dSC));
+  if (n_b) {
+    LLIE_TRY(ctx->workspace("msrcr.TB", (size_t)planes * hC * wB * 4, &dTB));
+    LLIE_TRY(ctx->workspace("msrcr.B", b_elems * 4, &dB));
+    LLIE_TRY(ctx->workspace("msrcr.B.tmp", b_elems * 4, &dBt));
+    LLIE_TRY(ctx->workspace("msrcr.SB", b_elems * 4, &dSB));
+    LLIE_TRY(ctx->workspace("msrcr.T2", (size_t)planes * hB * wC * 4, &dT2));
+  }
+  if (p.n_scales > 3) LLIE_TRY(ctx->workspace("msrcr.acc", (size_t)n * h * w * 3 * 4, &dAcc));
 
   const ImgView v = make_view(layout, 3, h, w);
-  const int planes = n * 3;
-  {
-    dim3 grid((wA + kDAW - 1) / kDAW, (hA + kDAH - 1) / kDAH, n);
-    constexpr size_t sm = (size_t)3 * kDPH * (kDPW + kDAW) * sizeof(float);
-    LLIE_CUDA_OK(cudaFuncSetAttribute(down2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
-    LLIE_LAUNCH(ctx, st, "down2_kernel", down2_kernel<<<grid, 256, sm, st>>>(in, v, h, w, 0, (float*)dA, hA, wA, 0, p.in_scale, p.in_bias, pl->ga));
+  const bool vec = (w % 4 == 0) && ((reinterpret_cast<uintptr_t>(in) | reinterpret_cast<uintptr_t>(out)) % 16 == 0);
+  const int want = 8 * ctx->sm_count;
+
+  {  // K1: rows
+    const long long plane_stride = nhwc ? (long long)h * RW : (long long)h * w;
+    if (vec) {
+      const int cx = ceil_div(RW, 512);
+      const int rps = pick_strip(hC, (long long)cx * planes_v, want, 16, 64, 1);
+      dim3 grid(cx, ceil_div(hC, rps), planes_v);
+      LLIE_LAUNCH(ctx, st, "down4_rows_kernel",
+                  down4_rows_kernel<4><<<grid, 128, 0, st>>>(in, plane_stride, RW, h, 0, h, (float*)dV, hC, 0, hC, rps));
+    } else {
+      const int cx = ceil_div(RW, 128);
+      const int rps = pick_strip(hC, (long long)cx * planes_v, want, 16, 64, 1);
+      dim3 grid(cx, ceil_div(hC, rps), planes_v);
+      LLIE_LAUNCH(ctx, st, "down4_rows_kernel",
+                  down4_rows_kernel<1><<<grid, 128, 0, st>>>(in, plane_stride, RW, h, 0, h, (float*)dV, hC, 0, hC, rps));
+    }
   }
-  if (any_b) {
-    const float* gB = pl->d_taps;
-    long long rows_total = (long long)planes * hA;
-    LLIE_LAUNCH(ctx, st, "down8_rows_kernel", down8_rows_kernel<<<(unsigned)((rows_total * wB + 255) / 256), 256, 0, st>>>((const float*)dA, (float*)dBt, gB,
-                                                                                  rows_total, wA, wB));
-    long long nb = (long long)planes * hB * wB;
-    LLIE_LAUNCH(ctx, st, "down8_cols_kernel", down8_cols_kernel<<<(unsigned)((nb + 255) / 256), 256, 0, st>>>((const float*)dBt, (float*)dB, gB, planes, hA, hA, 0,
-                                                                     wB, hB, 0));
+  {  // K1b: columns
+    dim3 grid(ceil_div(wC, 128), hC, planes_v);
+    if (nhwc)
+      LLIE_LAUNCH(ctx, st, "down4_cols_kernel",
+                  down4_cols_kernel<3><<<grid, 128, 0, st>>>((const float*)dV, (float*)dC, RW, w, hC, wC, 0, p.in_scale, p.in_bias));
+    else
+      LLIE_LAUNCH(ctx, st, "down4_cols_kernel",
+                  down4_cols_kernel<1><<<grid, 128, 0, st>>>((const float*)dV, (float*)dC, RW, w, hC, wC, 0, p.in_scale, p.in_bias));
   }
-  FinalParams fp = pl->fp;
-  fp.rows_buf[0] = hA; fp.wL[0] = wA; fp.row0[0] = 0;
-  fp.rows_buf[1] = hB; fp.wL[1] = wB; fp.row0[1] = 0;
-  int ia = 0, ib = 0;
+  if (n_b) {
+    dim3 gx(ceil_div((long long)hC * wB, 256), 1, planes), gy(ceil_div((long long)hB * wB, 256), 1, planes);
+    LLIE_LAUNCH(ctx, st, "decim4_x_kernel", decim4_x_kernel<<<gx, 256, 0, st>>>((const float*)dC, (float*)dTB, hC, wC, wB, 0, hC));
+    LLIE_LAUNCH(ctx, st, "decim4_y_kernel", decim4_y_kernel<<<gy, 256, 0, st>>>((const float*)dTB, (float*)dB, hC, hB, wB, 0, hB));
+  }
+  (void)CS;
   for (int k = 0; k < p.n_scales; ++k) {
     const ScalePlan& sp = pl->scales[k];
     const float* taps = pl->d_taps + pl->tap_off[k];
-    const int hL = sp.level ? hB : hA, wL = sp.level ? wB : wA;
-    const float* src = sp.level ? (const float*)dB : (const float*)dA;
-    float* tmp = sp.level ? (float*)dBt2 : (float*)dAt;
-    float* dst = sp.level ? (float*)dBblur + (size_t)(ib++) * b_elems : (float*)dAblur + (size_t)(ia++) * a_elems;
     const int r = sp.radius_low;
-    size_t sm = (size_t)(128 + 2 * r + 3) * sizeof(float);
-    dim3 gx((unsigned)((long long)planes * hL), (wL + 127) / 128);
-    LLIE_LAUNCH(ctx, st, "fir_x_kernel", fir_x_kernel<false><<<gx, 128, sm, st>>>(src, tmp, taps, r, wL, 1, 1.f, 0.f));
-    dim3 gy((wL + 127) / 128, (hL + 3) / 4, planes);
-    LLIE_LAUNCH(ctx, st, "fir_y_kernel", fir_y_kernel<<<gy, 128, 0, st>>>(tmp, dst, taps, r, hL, wL, 0, hL, 0, hL));
-    fp.map[k] = dst;
+    const size_t sm = (size_t)(128 + 2 * r + 3) * sizeof(float);
+    float* sc = (float*)dSC + (size_t)k * c_elems;
+    if (sp.level == 0) {
+      dim3 gx((unsigned)((long long)planes * hC), ceil_div(wC, 128)), gy(ceil_div(wC, 128), ceil_div(hC, 4), planes);
+      LLIE_LAUNCH(ctx, st, "fir_x_kernel", fir_x_kernel<false><<<gx, 128, sm, st>>>((const float*)dC, (float*)dCt, taps, r, wC, 1, 1.f, 0.f));
+      LLIE_LAUNCH(ctx, st, "fir_y_kernel", fir_y_kernel<<<gy, 128, 0, st>>>((const float*)dCt, sc, taps, r, hC, wC, 0, hC, 0, hC));
+    } else {
+      dim3 gx((unsigned)((long long)planes * hB), ceil_div(wB, 128)), gy(ceil_div(wB, 128), ceil_div(hB, 4), planes);
+      LLIE_LAUNCH(ctx, st, "fir_x_kernel", fir_x_kernel<false><<<gx, 128, sm, st>>>((const float*)dB, (float*)dBt, taps, r, wB, 1, 1.f, 0.f));
+      LLIE_LAUNCH(ctx, st, "fir_y_kernel", fir_y_kernel<<<gy, 128, 0, st>>>((const float*)dBt, (float*)dSB, taps, r, hB, wB, 0, hB, 0, hB));
+      dim3 ux(ceil_div((long long)hB * wC, 256), 1, planes), uy(ceil_div((long long)hC * wC, 256), 1, planes);
+      LLIE_LAUNCH(ctx, st, "up_bc_x_kernel", up_bc_x_kernel<<<ux, 256, 0, st>>>((const float*)dSB, (float*)dT2, hB, wB, wC, 0, hB, pl->uw));
+      LLIE_LAUNCH(ctx, st, "up_bc_y_kernel", up_bc_y_kernel<<<uy, 256, 0, st>>>((const float*)dT2, sc, hB, hC, wC, 0, hC, pl->uw));
+    }
   }
-  {
-    dim3 grid((w + kFX - 1) / kFX, (h + kFY - 1) / kFY, n);
-    LLIE_LAUNCH(ctx, st, "msrcr_final_kernel", msrcr_final_kernel<<<grid, 256, 0, st>>>(in, out, v, h, w, 0, fp));
+  {  // K5: final pass(es)
+    const int io = vec ? (nhwc ? kIoNhwcVec : kIoNchwVec) : kIoScalar;
+    const int cx = ceil_div(w, 4 * kFinalCells);
+    const int rps = pick_strip(h, (long long)cx * n, 16 * ctx->sm_count, 16, 64, 4);
+    dim3 grid(cx, ceil_div(h, rps), n);
+    FinalParams fp;
+    memset(&fp, 0, sizeof(fp));
+    fp.hC = hC; fp.wC = wC;
+    const double ln2 = 0.6931471805599453;
+    double wsum = 0;
+    for (int k = 0; k < p.n_scales; ++k) wsum += p.weight[k];
+    fp.wsum2 = (float)(ln2 * wsum);
+    fp.beta_ln_alpha = (float)(p.beta * std::log((double)p.alpha));
+    fp.beta_ln2 = (float)(p.beta * ln2);
+    fp.gain255 = p.gain / 255.f;
+    fp.offset255 = p.offset / 255.f;
+    fp.in_scale = p.in_scale; fp.in_bias = p.in_bias;
+    int n6 = 0;
+    for (auto& s : pl->scales) n6 += (s.level == 0);
+    if (p.n_scales == 3 && n6 == 1) {
+      for (int i = 0; i < 3; ++i) {
+        const int k = pl->order[i];
+        fp.map[i] = (const float*)dSC + (size_t)k * c_elems;
+        fp.w2[i] = (float)(ln2 * p.weight[k]);
+      }
+      LLIE_LAUNCH(ctx, st, "msrcr_final_kernel", (launch_final<1, 2>(grid, st, in, out, v, io, w, 0, 0, h, rps, fp)));
+    } else {
+      for (int k0 = 0; k0 < p.n_scales; k0 += 3) {
+        const int cnt = std::min(3, p.n_scales - k0);
+        for (int i = 0; i < cnt; ++i) {
+          fp.map[i] = (const float*)dSC + (size_t)(k0 + i) * c_elems;
+          fp.w2[i] = (float)(ln2 * p.weight[k0 + i]);
+        }
+        fp.acc_in = k0 > 0 ? (const float*)dAcc : nullptr;
+        fp.acc_out = k0 + cnt < p.n_scales ? (float*)dAcc : nullptr;
+        if (cnt == 1) LLIE_LAUNCH(ctx, st, "msrcr_final_kernel", (launch_final<1, 0>(grid, st, in, out, v, io, w, 0, 0, h, rps, fp)));
+        if (cnt == 2) LLIE_LAUNCH(ctx, st, "msrcr_final_kernel", (launch_final<2, 0>(grid, st, in, out, v, io, w, 0, 0, h, rps, fp)));
+        if (cnt == 3) LLIE_LAUNCH(ctx, st, "msrcr_final_kernel", (launch_final<3, 0>(grid, st, in, out, v, io, w, 0, 0, h, rps, fp)));
+      }
+    }
   }
-  (void)any_a;
   return LLIE_OK;
 }
 

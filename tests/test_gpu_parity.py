@@ -38,9 +38,10 @@ def test_msrcr_golden_default(blur):
     assert np.abs(y - d["y"]).max() <= TOL_F32
 
 
-@pytest.mark.parametrize("blur", ["pyramid", "direct"])
-def test_msrcr_golden_custom_scales(blur):
-    d = np.load(os.path.join(G, "msrcr_80x112_custom.npz"))
+@pytest.mark.parametrize("blur,name", [("direct", "msrcr_80x112_custom.npz"), ("direct", "msrcr_88x120_custom.npz"),
+                                       ("pyramid", "msrcr_88x120_custom.npz")])
+def test_msrcr_golden_custom_scales(blur, name):
+    d = np.load(os.path.join(G, name))
     p = dict(sigmas=tuple(float(s) for s in d["sigmas"]), weights=tuple(float(w) for w in d["weights"]),
              gain=float(d["gain"]), offset=float(d["offset"]), blur=blur)
     assert np.abs(L.enhance(d["x"], "msrcr", p) - d["y"]).max() <= TOL_F32
@@ -63,6 +64,20 @@ def test_msrcr_pyramid_matches_direct_on_gpu():
     a = L.enhance(x, "msrcr", dict(blur="pyramid"))
     b = L.enhance(x, "msrcr", dict(blur="direct"))
     assert float((a - b).abs().max()) <= TOL_F32
+
+
+def test_msrcr_cascade_scale_counts_and_layouts():
+    """1..5 scales (more than 3 takes the multi-pass accumulate route), both layouts, odd width (scalar I/O)."""
+    sig = (13.0, 20.0, 60.0, 150.0, 35.0)
+    for (h, w) in ((150, 212), (97, 131)):
+        x = oracle.synth_lowlight(h, w, 300 + w)
+        for k in (1, 2, 3, 4, 5):
+            p = dict(sigmas=sig[:k], weights=tuple(1.0 / k for _ in range(k)))
+            ref = oracle.msrcr(x, p)
+            assert np.abs(L.enhance(x, "msrcr", p) - ref).max() <= TOL_F32, (h, w, k)
+            xc = np.ascontiguousarray(x.transpose(2, 0, 1))[None]
+            yc = L.enhance(xc, "msrcr", dict(p, layout="NCHW"))
+            assert np.abs(yc[0].transpose(1, 2, 0) - ref).max() <= TOL_F32, (h, w, k, "NCHW")
 
 
 def test_msrcr_constant_image_kat():
