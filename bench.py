@@ -44,9 +44,10 @@ FLOP_PER_PX = {"dce_conv_tc_k32_kernel": 2 * 32 * 32 * 9, "dce_conv_tc_k64_kerne
                "dce_conv_tc_last_kernel": 2 * 64 * 24 * 9}
 DCE_TENSOR_FLOP_PER_PX = 156672          # conv2..conv7
 MSRCR_NORTH_STAR_BYTES_PER_PX = 108      # two-pass separable data flow
-# msrcr_final_kernel: reads x (12 B) + writes out (12 B) + the stride-2 surround of sigma=15 (3 B) per pixel;
-# the stride-16 surrounds of sigma=80/250 add 2 * 12/256 B
-MSRCR_FINAL_BYTES_PER_PX = 12 + 12 + 3 + 2 * 12 / 256.0
+# per-kernel algorithmic HBM bytes per full-resolution pixel of the decimated cascade (DESIGN.md "Kernels"):
+#   down4_rows_kernel : reads x (12 B), writes the stride-4 (vertical) partial V (12/4 B)
+#   msrcr_final_kernel: reads x (12 B), writes out (12 B), reads 3 scales x 3 ch of stride-4 surround (36/16 B)
+MSRCR_KERNEL_BYTES_PER_PX = {"down4_rows_kernel": 12 + 3.0, "msrcr_final_kernel": 12 + 12 + 36 / 16.0}
 
 
 def load_peaks():
@@ -224,13 +225,16 @@ def tc_roofline(prof, px_per_step, steps, peaks):
 
 
 def hbm_roofline(prof, px_per_step, steps, peaks, total_ms_per_step):
-    if "msrcr_final_kernel" not in prof:
+    cand = {k: v for k, v in prof.items() if k in MSRCR_KERNEL_BYTES_PER_PX}
+    if not cand:
         return None
-    cnt, ms = prof["msrcr_final_kernel"]
-    ach = MSRCR_FINAL_BYTES_PER_PX * px_per_step * steps / (ms * 1e-3) / 1e9
+    dom = max(cand, key=lambda k: cand[k][1])
+    cnt, ms = cand[dom]
+    ach = MSRCR_KERNEL_BYTES_PER_PX[dom] * px_per_step * steps / (ms * 1e-3) / 1e9
     ns = MSRCR_NORTH_STAR_BYTES_PER_PX * px_per_step / (total_ms_per_step * 1e-3) / 1e9
-    return {"bound": "hbm", "kernel": "msrcr_final_kernel", "achieved": round(ach, 1), "peak": peaks["hbm"], "unit": "GB/s",
+    return {"bound": "hbm", "kernel": dom, "achieved": round(ach, 1), "peak": peaks["hbm"], "unit": "GB/s",
             "frac": round(ach / peaks["hbm"], 4), "traffic": None, "peak_source": f"{peaks['source']} copy",
+            "kernel_bytes_per_px": MSRCR_KERNEL_BYTES_PER_PX[dom],
             "launches": cnt, "avg_launch_ms": round(ms / cnt, 4),
             "whole_msrcr_at_108B_per_px": {"achieved": round(ns, 1), "frac": round(ns / peaks["hbm"], 4)},
             "kernel_ms_per_step": {k: round(v[1] / steps, 4) for k, v in sorted(prof.items())}}

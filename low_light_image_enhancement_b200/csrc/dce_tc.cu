@@ -107,52 +107,63 @@ __global__ void __launch_bounds__(kThreads, 1) dce_conv_tc_kernel(const __grid_c
 
   if (warp == 0) {
     // ---------------- producer: one bulk copy per (input row, 8-channel chunk) ----------------
-    if (lane == 0) {
+    // The whole warp walks the loop (warp-uniform control flow keeps addresses in uniform
+    // registers); one elected lane issues the copies.
+    if (elect_one()) {
       mbar_expect_tx(wbar, kWBytes);
       bulk_g2s(s_w, a.wpk, kWBytes, wbar);
-      int stage = 0;
-      uint32_t phase = 0;
-      for (int u = blockIdx.x; u < a.units; u += gridDim.x) {
-        int n, sx, ys, ye;
-        decode(u, n, sx, ys, ye);
-        const int yi0 = max(ys - 1, 0), yi1 = min(ye, H - 1);
-        for (int yi = yi0; yi <= yi1; ++yi) {
-          mbar_wait(&empty[stage], phase ^ 1);
+    }
+    __syncwarp();
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int u = blockIdx.x; u < a.units; u += gridDim.x) {
+      int n, sx, ys, ye;
+      decode(u, n, sx, ys, ye);
+      const int yi0 = max(ys - 1, 0), yi1 = min(ye, H - 1);
+      const size_t row_stride = (size_t)4 * a.Wp * 8;  // elements between consecutive rows of one source
+      size_t off = ((size_t)n * H + yi0) * row_stride + (size_t)sx * kTileX * 8;
+      for (int yi = yi0; yi <= yi1; ++yi, off += row_stride) {
+        mbar_wait(&empty[stage], phase ^ 1);
+        if (elect_one()) {
           mbar_expect_tx(&full[stage], kStageBytes);
           uint8_t* dst = s_a + stage * kStageBytes;
 #pragma unroll
           for (int c = 0; c < CHUNKS; ++c) {
             const __nv_bfloat16* src = (c < 4) ? a.in_a : a.in_b;
-            const size_t off = ((((size_t)n * H + yi) * 4 + (c & 3)) * a.Wp + (size_t)sx * kTileX) * 8;
-            bulk_g2s(dst + c * kChunkBytes, src + off, kChunkBytes, &full[stage]);
+            bulk_g2s(dst + c * kChunkBytes, src + off + (size_t)(c & 3) * a.Wp * 8, kChunkBytes, &full[stage]);
           }
-          if (++stage == kStages) { stage = 0; phase ^= 1; }
         }
+        __syncwarp();
+        if (++stage == kStages) { stage = 0; phase ^= 1; }
       }
     }
   } else if (warp == 1) {
     // ---------------- MMA issuer ---------------------------------------------------------------
-    if (lane == 0) {
-      mbar_wait(wbar, 0);
-      const uint32_t w_base = smem_u32(s_w);
-      int stage = 0;
-      uint32_t phase = 0, free_par = 0;
-      for (int u = blockIdx.x; u < a.units; u += gridDim.x) {
-        int n, sx, ys, ye;
-        decode(u, n, sx, ys, ye);
-        const int yi0 = max(ys - 1, 0), yi1 = min(ye, H - 1);
-        int next_untouched = ys, next_uncommitted = ys;
-        for (int yi = yi0; yi <= yi1; ++yi) {
-          const int lo = max(ys, yi - 1), hi = min(ye - 1, yi + 1);
-          while (next_untouched <= hi) {  // slots this row touches first must be drained + bias-initialised
-            const int s = (next_untouched - ys) & (kSlots - 1);
-            mbar_wait(&acc_free[s], (free_par >> s) & 1);
-            free_par ^= 1u << s;
-            ++next_untouched;
-          }
-          mbar_wait(&full[stage], phase);
-          tc_fence_after();
-          const uint32_t a_base = smem_u32(s_a + stage * kStageBytes);
+    // All 32 lanes run the loop and the barrier waits (warp-uniform control flow: descriptors stay
+    // in uniform registers and UTCHMMA issues back to back); one elected lane issues MMAs/commits.
+    mbar_wait(wbar, 0);
+    const uint64_t a_desc0 = smem_desc(smem_u32(s_a), kChunkBytes, 128);
+    const uint64_t b_desc0 = smem_desc(smem_u32(s_w), kBPlane, 128);
+    int stage = 0;
+    uint32_t phase = 0, free_par = 0;
+    for (int u = blockIdx.x; u < a.units; u += gridDim.x) {
+      int n, sx, ys, ye;
+      decode(u, n, sx, ys, ye);
+      const int yi0 = max(ys - 1, 0), yi1 = min(ye, H - 1);
+      int next_untouched = ys, next_uncommitted = ys;
+      for (int yi = yi0; yi <= yi1; ++yi) {
+        const int lo = max(ys, yi - 1), hi = min(ye - 1, yi + 1);
+        while (next_untouched <= hi) {  // slots this row touches first must be drained + bias-initialised
+          const int s = (next_untouched - ys) & (kSlots - 1);
+          mbar_wait(&acc_free[s], (free_par >> s) & 1);
+          free_par ^= 1u << s;
+          ++next_untouched;
+        }
+        mbar_wait(&full[stage], phase);
+        tc_fence_after();
+        const int done_upto = (yi == yi1) ? ye - 1 : yi - 1;
+        if (elect_one()) {
+          const uint64_t a_stage = a_desc0 + (uint64_t)(stage * (kStageBytes >> 4));
           int yo = lo;
           while (yo <= hi) {  // split where the slot ring wraps
             const int s0 = (yo - ys) & (kSlots - 1);
@@ -160,25 +171,24 @@ __global__ void __launch_bounds__(kThreads, 1) dce_conv_tc_kernel(const __grid_c
             const int dyslot = yo - (yi - 1);  // 0: dy=+1 (output above), 1: dy=0, 2: dy=-1
             const uint32_t idesc = idesc_bf16_m128(32 * cnt);
             const uint32_t d = tmem + s0 * 32;
+            const uint64_t b_row = b_desc0 + (uint64_t)(dyslot * (512 >> 4));
 #pragma unroll
             for (int dx = 0; dx < 3; ++dx) {
 #pragma unroll
               for (int kk = 0; kk < CHUNKS / 2; ++kk) {
-                const uint64_t ad = smem_desc(a_base + kk * 2 * kChunkBytes + dx * 16, kChunkBytes, 128);
-                const uint64_t bd = smem_desc(w_base + (dx * (CHUNKS / 2) + kk) * kBTile + dyslot * 512, kBPlane, 128);
+                const uint64_t ad = a_stage + (uint64_t)((kk * 2 * kChunkBytes + dx * 16) >> 4);
+                const uint64_t bd = b_row + (uint64_t)(((dx * (CHUNKS / 2) + kk) * kBTile) >> 4);
                 mma_bf16_ss(d, ad, bd, idesc, 1u);
               }
             }
             yo += cnt;
           }
           mma_commit(&empty[stage]);
-          const int done_upto = (yi == yi1) ? ye - 1 : yi - 1;
-          while (next_uncommitted <= done_upto) {
-            mma_commit(&acc_ready[(next_uncommitted - ys) & (kSlots - 1)]);
-            ++next_uncommitted;
-          }
-          if (++stage == kStages) { stage = 0; phase ^= 1; }
+          for (int yc = next_uncommitted; yc <= done_upto; ++yc) mma_commit(&acc_ready[(yc - ys) & (kSlots - 1)]);
         }
+        __syncwarp();
+        if (done_upto >= next_uncommitted) next_uncommitted = done_upto + 1;
+        if (++stage == kStages) { stage = 0; phase ^= 1; }
       }
     }
   } else {
