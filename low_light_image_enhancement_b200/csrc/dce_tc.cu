@@ -33,6 +33,7 @@ using namespace ptx;
 constexpr int kTileX = 128;                 // pixels per MMA (M)
 constexpr int kRowPx = kTileX + 2;          // staged pixels per input row (1-px halo each side)
 constexpr int kChunkBytes = kRowPx * 16;    // 2080: one 8-channel chunk of one staged row
+constexpr int kFirstRowBytes = (kRowPx + 2) * 16;  // conv1 stages 132 px: its dx=2 MMA's zero-weight K half reads px+3
 constexpr int kSlots = 16;                  // TMEM ring: 16 output rows x 32 fp32 columns = 512
 constexpr int kStages = 8;                  // input-row ring
 constexpr int kBTile = 96 * 16 * 2;         // 3072 B: weight tile of one (dx, k16): N=96 x K=16
@@ -65,11 +66,16 @@ __device__ __forceinline__ float fast_tanh(float v) {
   return 1.f - __fdividef(2.f, e + 1.f);
 }
 
-template <int CHUNKS, bool LAST>
+// FIRST (conv1, 3 -> 32): the input is ONE 8-channel chunk (RGB + 5 zero channels) and the two K
+// halves of an MMA are two ADJACENT PIXELS of it (descriptor LBO = 16 B), so K = 16 covers the taps
+// dx = 0,1 and a second MMA covers dx = 2 (+ a zero-weight half): 2 MMAs per input row.
+template <int CHUNKS, bool LAST, bool FIRST = false>
 __global__ void __launch_bounds__(kThreads, 1) dce_conv_tc_kernel(const __grid_constant__ ConvArgs a) {
   extern __shared__ __align__(128) uint8_t smem[];
-  constexpr int kWBytes = 3 * (CHUNKS / 2) * kBTile;
-  constexpr int kStageBytes = CHUNKS * kChunkBytes;
+  static_assert(!FIRST || (CHUNKS == 1 && !LAST), "conv1 variant is single-chunk");
+  constexpr int kWBytes = FIRST ? 2 * kBTile : 3 * (CHUNKS / 2) * kBTile;
+  constexpr int kRowBytes = FIRST ? kFirstRowBytes : kChunkBytes;  // bytes of one staged chunk row
+  constexpr int kStageBytes = CHUNKS * kRowBytes;
   uint8_t* s_w = smem;
   uint8_t* s_a = smem + kWBytes;
   uint64_t* full = reinterpret_cast<uint64_t*>(s_a + kStages * kStageBytes);
@@ -120,7 +126,7 @@ __global__ void __launch_bounds__(kThreads, 1) dce_conv_tc_kernel(const __grid_c
       int n, sx, ys, ye;
       decode(u, n, sx, ys, ye);
       const int yi0 = max(ys - 1, 0), yi1 = min(ye, H - 1);
-      const size_t row_stride = (size_t)4 * a.Wp * 8;  // elements between consecutive rows of one source
+      const size_t row_stride = (size_t)(FIRST ? 1 : 4) * a.Wp * 8;  // elements between consecutive rows of one source
       size_t off = ((size_t)n * H + yi0) * row_stride + (size_t)sx * kTileX * 8;
       for (int yi = yi0; yi <= yi1; ++yi, off += row_stride) {
         mbar_wait(&empty[stage], phase ^ 1);
@@ -130,7 +136,7 @@ __global__ void __launch_bounds__(kThreads, 1) dce_conv_tc_kernel(const __grid_c
 #pragma unroll
           for (int c = 0; c < CHUNKS; ++c) {
             const __nv_bfloat16* src = (c < 4) ? a.in_a : a.in_b;
-            bulk_g2s(dst + c * kChunkBytes, src + off + (size_t)(c & 3) * a.Wp * 8, kChunkBytes, &full[stage]);
+            bulk_g2s(dst + c * kRowBytes, src + off + (size_t)(c & 3) * a.Wp * 8, kRowBytes, &full[stage]);
           }
         }
         __syncwarp();
@@ -142,7 +148,7 @@ __global__ void __launch_bounds__(kThreads, 1) dce_conv_tc_kernel(const __grid_c
     // All 32 lanes run the loop and the barrier waits (warp-uniform control flow: descriptors stay
     // in uniform registers and UTCHMMA issues back to back); one elected lane issues MMAs/commits.
     mbar_wait(wbar, 0);
-    const uint64_t a_desc0 = smem_desc(smem_u32(s_a), kChunkBytes, 128);
+    const uint64_t a_desc0 = smem_desc(smem_u32(s_a), FIRST ? 16 : kChunkBytes, 128);
     const uint64_t b_desc0 = smem_desc(smem_u32(s_w), kBPlane, 128);
     int stage = 0;
     uint32_t phase = 0, free_par = 0;
@@ -172,13 +178,18 @@ __global__ void __launch_bounds__(kThreads, 1) dce_conv_tc_kernel(const __grid_c
             const uint32_t idesc = idesc_bf16_m128(32 * cnt);
             const uint32_t d = tmem + s0 * 32;
             const uint64_t b_row = b_desc0 + (uint64_t)(dyslot * (512 >> 4));
+            if constexpr (FIRST) {
+              mma_bf16_ss(d, a_stage, b_row, idesc, 1u);                                // dx = 0, 1
+              mma_bf16_ss(d, a_stage + 2, b_row + (uint64_t)(kBTile >> 4), idesc, 1u);  // dx = 2, (zero)
+            } else {
 #pragma unroll
-            for (int dx = 0; dx < 3; ++dx) {
+              for (int dx = 0; dx < 3; ++dx) {
 #pragma unroll
-              for (int kk = 0; kk < CHUNKS / 2; ++kk) {
-                const uint64_t ad = a_stage + (uint64_t)((kk * 2 * kChunkBytes + dx * 16) >> 4);
-                const uint64_t bd = b_row + (uint64_t)(((dx * (CHUNKS / 2) + kk) * kBTile) >> 4);
-                mma_bf16_ss(d, ad, bd, idesc, 1u);
+                for (int kk = 0; kk < CHUNKS / 2; ++kk) {
+                  const uint64_t ad = a_stage + (uint64_t)((kk * 2 * kChunkBytes + dx * 16) >> 4);
+                  const uint64_t bd = b_row + (uint64_t)(((dx * (CHUNKS / 2) + kk) * kBTile) >> 4);
+                  mma_bf16_ss(d, ad, bd, idesc, 1u);
+                }
               }
             }
             yo += cnt;
@@ -268,46 +279,22 @@ __global__ void __launch_bounds__(kThreads, 1) dce_conv_tc_kernel(const __grid_c
   if (warp == 1) tmem_dealloc(tmem, 512);
 }
 
-// conv1 (3 -> 32) + ReLU on the CUDA cores, fp32 arithmetic, output rounded to bf16 in the
-// chunk-planar layout.  One thread per pixel; weights [27][32] + bias in shared memory.
+// Input staging for conv1: fp32 image (any layout) -> bf16 [n][y][Wp][8] (RGB + 5 zero channels),
+// pixel x at column x+1 (column 0 and the columns past W stay zero from the workspace memset).
+// One thread per pixel: 12 B read, one 16 B store.
 __global__ void __launch_bounds__(256)
-dce_conv1_bf16_kernel(const float* __restrict__ x, ImgView v, const float* __restrict__ w27x32,
-                      const float* __restrict__ bias, __nv_bfloat16* __restrict__ out, int N, int H, int W, int Wp) {
-  __shared__ float s_w[27 * 32 + 32];
-  for (int i = threadIdx.x; i < 27 * 32; i += blockDim.x) s_w[i] = w27x32[i];
-  if (threadIdx.x < 32) s_w[27 * 32 + threadIdx.x] = bias[threadIdx.x];
-  __syncthreads();
+dce_pack_input_kernel(const float* __restrict__ x, ImgView v, __nv_bfloat16* __restrict__ out, int H, int W, int Wp) {
   const int xx = blockIdx.x * blockDim.x + threadIdx.x, yy = blockIdx.y;
   const long long n = blockIdx.z;
   if (xx >= W) return;
-  float in[27];
-#pragma unroll
-  for (int c = 0; c < 3; ++c)
-#pragma unroll
-    for (int dy = 0; dy < 3; ++dy)
-#pragma unroll
-      for (int dx = 0; dx < 3; ++dx) {
-        int gy = yy + dy - 1, gx = xx + dx - 1;
-        bool ok = gy >= 0 && gy < H && gx >= 0 && gx < W;
-        in[c * 9 + dy * 3 + dx] = ok ? __ldg(x + n * v.sn + c * v.sc + (long long)gy * v.sy + (long long)gx * v.sx) : 0.f;
-      }
-  uint4* dst = reinterpret_cast<uint4*>(out + (((n * H + yy) * 4) * Wp + (xx + 1)) * 8);
-#pragma unroll
-  for (int c4 = 0; c4 < 4; ++c4) {
-    float acc[8];
-#pragma unroll
-    for (int o = 0; o < 8; ++o) acc[o] = s_w[27 * 32 + c4 * 8 + o];
-#pragma unroll
-    for (int t = 0; t < 27; ++t)
-#pragma unroll
-      for (int o = 0; o < 8; ++o) acc[o] = fmaf(in[t], s_w[t * 32 + c4 * 8 + o], acc[o]);
-    uint4 o4;
-    o4.x = pack_bf16_relu(__float_as_uint(acc[0]), __float_as_uint(acc[1]));
-    o4.y = pack_bf16_relu(__float_as_uint(acc[2]), __float_as_uint(acc[3]));
-    o4.z = pack_bf16_relu(__float_as_uint(acc[4]), __float_as_uint(acc[5]));
-    o4.w = pack_bf16_relu(__float_as_uint(acc[6]), __float_as_uint(acc[7]));
-    dst[(size_t)c4 * Wp] = o4;
-  }
+  const float* p = x + n * v.sn + (long long)yy * v.sy + (long long)xx * v.sx;
+  const __nv_bfloat162 rg = __floats2bfloat162_rn(__ldg(p), __ldg(p + v.sc));
+  const __nv_bfloat162 b0 = __floats2bfloat162_rn(__ldg(p + 2 * v.sc), 0.f);
+  uint4 o;
+  o.x = *reinterpret_cast<const uint32_t*>(&rg);
+  o.y = *reinterpret_cast<const uint32_t*>(&b0);
+  o.z = 0u; o.w = 0u;
+  *reinterpret_cast<uint4*>(out + ((n * H + yy) * (long long)Wp + (xx + 1)) * 8) = o;
 }
 
 // Segments per strip: minimise waves x (rows per segment + halo + pipeline fill) over the grid.
@@ -324,11 +311,12 @@ int choose_segments(int n, int strips, int H, int ctas) {
   return best;
 }
 
-template <int CHUNKS, bool LAST>
+template <int CHUNKS, bool LAST, bool FIRST = false>
 int launch_tc(llie_ctx* ctx, cudaStream_t st, ConvArgs a) {
-  constexpr size_t smem = 3 * (CHUNKS / 2) * kBTile + (size_t)kStages * CHUNKS * kChunkBytes +
+  constexpr size_t smem = (FIRST ? 2 * kBTile : 3 * (CHUNKS / 2) * kBTile) +
+                          (size_t)kStages * CHUNKS * (FIRST ? kFirstRowBytes : kChunkBytes) +
                           (2 * kStages + 2 * kSlots + 1) * sizeof(uint64_t) + 16;
-  LLIE_CUDA_OK(cudaFuncSetAttribute(dce_conv_tc_kernel<CHUNKS, LAST>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+  LLIE_CUDA_OK(cudaFuncSetAttribute(dce_conv_tc_kernel<CHUNKS, LAST, FIRST>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                     (int)smem));
   const int ctas = ctx->sm_count;
   a.segs = choose_segments(a.N, a.strips, a.H, ctas);
@@ -336,47 +324,57 @@ int launch_tc(llie_ctx* ctx, cudaStream_t st, ConvArgs a) {
   a.segs = (a.H + a.seg_rows - 1) / a.seg_rows;
   a.units = a.N * a.strips * a.segs;
   const int grid = a.units < ctas ? a.units : ctas;
-  LLIE_LAUNCH(ctx, st, LAST ? "dce_conv_tc_last_kernel" : (CHUNKS == 4 ? "dce_conv_tc_k32_kernel" : "dce_conv_tc_k64_kernel"),
-              (dce_conv_tc_kernel<CHUNKS, LAST><<<grid, kThreads, smem, st>>>(a)));
+  LLIE_LAUNCH(ctx, st,
+              FIRST ? "dce_conv_tc_first_kernel"
+                    : LAST ? "dce_conv_tc_last_kernel" : (CHUNKS == 4 ? "dce_conv_tc_k32_kernel" : "dce_conv_tc_k64_kernel"),
+              (dce_conv_tc_kernel<CHUNKS, LAST, FIRST><<<grid, kThreads, smem, st>>>(a)));
   return LLIE_OK;
 }
 
 }  // namespace
 
-// Weight tiles for the tensor-core layers (l = 1..6): for every (dx, k16) a 96 x 16 bf16 tile,
-// row n = dyslot*32 + cout with dyslot 0/1/2 <-> kernel row ky = 2/1/0, stored as two 8-channel
-// planes of 96 x 16 B (K-major, no swizzle).  conv1 keeps fp32 weights as [27][32].
+// Weight tiles.  Layers l = 1..6: for every (dx, k16) a 96 x 16 bf16 tile, row n = dyslot*32 + cout
+// with dyslot 0/1/2 <-> kernel row ky = 2/1/0, stored as two 8-channel planes of 96 x 16 B (K-major,
+// no swizzle).  Layer 0 (conv1): two tiles whose K halves are horizontal taps -- tile 0 = (dx=0 |
+// dx=1), tile 1 = (dx=2 | zeros) -- each half holding the 3 input channels + 5 zero channels.
 struct DceTcPack {
-  size_t tile_off[7];  // element offsets into d_bf16 (layers 1..6)
-  float* d_c1 = nullptr;  // [27*32 weights | 32 bias]
+  size_t tile_off[7];  // element offsets into d_bf16 (layers 0..6)
   float* d_bias = nullptr;  // 7 x 32
   // geometry of the activation workspace of the last forward (for the debug hook / pad zeroing)
   int n = 0, h = 0, w = 0, wp = 0;
+  __nv_bfloat16* xin = nullptr;  // packed input [n][h][wp][8]
   __nv_bfloat16* act[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
 };
 static std::map<llie_ctx*, DceTcPack> g_packs;  // keyed by ctx (ctx is single-threaded by contract)
 
 int dce_pack_bf16(llie_ctx* ctx, DceWeights* dw) {
   DceTcPack& pk = g_packs[ctx];
-  cudaFree(pk.d_c1);
   cudaFree(pk.d_bias);
-  pk.d_c1 = pk.d_bias = nullptr;
+  pk.d_bias = nullptr;
   const float* raw = dw->host_raw.data();
   std::vector<__nv_bfloat16> tiles;
-  std::vector<float> c1(27 * 32 + 32, 0.f), biases(7 * 32, 0.f);
+  std::vector<float> biases(7 * 32, 0.f);
   size_t src = 0;
   for (int l = 0; l < 7; ++l) {
     const int co = kCout[l], ci = kCin[l];
     const float* Wl = raw + src;
     const float* bl = raw + src + (size_t)co * ci * 9;
     for (int o = 0; o < co; ++o) biases[l * 32 + o] = bl[o];
+    pk.tile_off[l] = tiles.size();
     if (l == 0) {
-      for (int o = 0; o < co; ++o)
-        for (int i = 0; i < 3; ++i)
-          for (int t = 0; t < 9; ++t) c1[(i * 9 + t) * 32 + o] = Wl[((size_t)o * ci + i) * 9 + t];
-      for (int o = 0; o < 32; ++o) c1[27 * 32 + o] = biases[o];
+      tiles.resize(tiles.size() + (size_t)2 * 96 * 16, __float2bfloat16(0.f));
+      __nv_bfloat16* T = tiles.data() + pk.tile_off[l];
+      for (int tile = 0; tile < 2; ++tile)
+        for (int kc = 0; kc < 2; ++kc) {
+          const int dx = tile * 2 + kc;
+          if (dx > 2) continue;
+          for (int nrow = 0; nrow < 96; ++nrow)
+            for (int e = 0; e < 3; ++e) {
+              const int o = nrow & 31, ky = 2 - (nrow >> 5);
+              T[(((size_t)tile * 2 + kc) * 96 + nrow) * 8 + e] = __float2bfloat16(Wl[(((size_t)o * ci + e) * 3 + ky) * 3 + dx]);
+            }
+        }
     } else {
-      pk.tile_off[l] = tiles.size();
       const int k16 = ci / 16;
       tiles.resize(tiles.size() + (size_t)3 * k16 * 96 * 16, __float2bfloat16(0.f));
       __nv_bfloat16* T = tiles.data() + pk.tile_off[l];
@@ -394,8 +392,6 @@ int dce_pack_bf16(llie_ctx* ctx, DceWeights* dw) {
   }
   LLIE_CUDA_OK(cudaMalloc(&dw->d_bf16, tiles.size() * sizeof(__nv_bfloat16)));
   LLIE_CUDA_OK(cudaMemcpy(dw->d_bf16, tiles.data(), tiles.size() * sizeof(__nv_bfloat16), cudaMemcpyHostToDevice));
-  LLIE_CUDA_OK(cudaMalloc(&pk.d_c1, c1.size() * sizeof(float)));
-  LLIE_CUDA_OK(cudaMemcpy(pk.d_c1, c1.data(), c1.size() * sizeof(float), cudaMemcpyHostToDevice));
   LLIE_CUDA_OK(cudaMalloc(&pk.d_bias, biases.size() * sizeof(float)));
   LLIE_CUDA_OK(cudaMemcpy(pk.d_bias, biases.data(), biases.size() * sizeof(float), cudaMemcpyHostToDevice));
   return LLIE_OK;
@@ -404,7 +400,6 @@ int dce_pack_bf16(llie_ctx* ctx, DceWeights* dw) {
 void dce_tc_release(llie_ctx* ctx) {
   auto it = g_packs.find(ctx);
   if (it == g_packs.end()) return;
-  cudaFree(it->second.d_c1);
   cudaFree(it->second.d_bias);
   g_packs.erase(it);
 }
@@ -415,18 +410,20 @@ int dce_forward_bf16(llie_ctx* ctx, const float* in, float* out, float* maps, in
   LLIE_REQUIRE(dw != nullptr && dw->d_bf16 != nullptr, LLIE_E_STATE, "dce_forward: call llie_dce_set_weights first");
   DceTcPack& pk = g_packs[ctx];
   const int strips = (w + kTileX - 1) / kTileX, wp = strips * kTileX + 2;
-  const size_t act_elems_per_img = (size_t)h * 4 * wp * 8;
-  // frames per pass: six bf16 activations per frame, kept under ~8 GiB
-  long long chunk = (8ll << 30) / (long long)(6 * act_elems_per_img * 2);
+  const size_t act_elems_per_img = (size_t)h * 4 * wp * 8, in_elems_per_img = (size_t)h * wp * 8;
+  // frames per pass: six bf16 activations + the packed input per frame, kept under ~8.5 GiB
+  long long chunk = (17ll << 29) / (long long)((6 * act_elems_per_img + in_elems_per_img) * 2);
   chunk = chunk < 1 ? 1 : (chunk > n ? n : chunk);
   void* ws;
-  const size_t ws_bytes = (size_t)chunk * 6 * act_elems_per_img * 2;
+  // + slack: conv1's staged rows run 2 pixels past a row's end (zero-weighted, but must be readable)
+  const size_t ws_bytes = (size_t)chunk * (6 * act_elems_per_img + in_elems_per_img) * 2 + 256;
   LLIE_TRY(ctx->workspace("dce.bf16.act", ws_bytes, &ws));
   if (pk.n != (int)chunk || pk.h != h || pk.w != w || pk.act[0] != (__nv_bfloat16*)ws) {
     // pad columns must read as zero and move with the geometry: clear on every geometry change
     LLIE_CUDA_OK(cudaMemsetAsync(ws, 0, ws_bytes, st));
     pk.n = (int)chunk; pk.h = h; pk.w = w; pk.wp = wp;
     for (int i = 0; i < 6; ++i) pk.act[i] = (__nv_bfloat16*)ws + (size_t)i * chunk * act_elems_per_img;
+    pk.xin = (__nv_bfloat16*)ws + (size_t)6 * chunk * act_elems_per_img;
   }
   const ImgView vx = make_view(layout, 3, h, w), vm = make_view(layout, 24, h, w);
   for (long long n0 = 0; n0 < n; n0 += chunk) {
@@ -434,8 +431,8 @@ int dce_forward_bf16(llie_ctx* ctx, const float* in, float* out, float* maps, in
     const float* x = in + n0 * (long long)h * w * 3;
     {
       dim3 grid((w + 255) / 256, h, nb);
-      LLIE_LAUNCH(ctx, st, "dce_conv1_bf16_kernel",
-                  dce_conv1_bf16_kernel<<<grid, 256, 0, st>>>(x, vx, pk.d_c1, pk.d_c1 + 27 * 32, pk.act[0], nb, h, w, wp));
+      LLIE_LAUNCH(ctx, st, "dce_pack_input_kernel",
+                  dce_pack_input_kernel<<<grid, 256, 0, st>>>(x, vx, pk.xin, h, w, wp));
     }
     ConvArgs a;
     memset(&a, 0, sizeof(a));
@@ -445,6 +442,7 @@ int dce_forward_bf16(llie_ctx* ctx, const float* in, float* out, float* maps, in
       a.wpk = dw->d_bf16 + pk.tile_off[l];
       a.bias = pk.d_bias + l * 32;
     };
+    layer(0, pk.xin, nullptr, pk.act[0]); LLIE_TRY((launch_tc<1, false, true>(ctx, st, a)));
     layer(1, pk.act[0], nullptr, pk.act[1]); LLIE_TRY((launch_tc<4, false>(ctx, st, a)));
     layer(2, pk.act[1], nullptr, pk.act[2]); LLIE_TRY((launch_tc<4, false>(ctx, st, a)));
     layer(3, pk.act[2], nullptr, pk.act[3]); LLIE_TRY((launch_tc<4, false>(ctx, st, a)));

@@ -1,6 +1,5 @@
 """NumPy emulation of the bf16 Zero-DCE path as SURVEY.md 9.2 defines it (test helper, CPU):
-conv1 in fp32 on the fp32 image, every inter-layer activation and the tensor-core layers'
-weights rounded to bf16 (round-to-nearest-even), fp32-or-better accumulation, bias/ReLU/tanh/
+the input image, every inter-layer activation and all seven layers' weights rounded to bf16 (round-to-nearest-even), fp32-or-better accumulation, bias/ReLU/tanh/
 curves in full precision.  Used to localise errors layer by layer; the acceptance bar itself
 is PSNR >= 50 dB against the un-rounded fp64 oracle."""
 import numpy as np
@@ -19,8 +18,8 @@ def dce_activations_bf16(x_hwc: np.ndarray, ws):
     """Returns [x1..x6] (each (32,H,W) float32, bf16-representable) and A (24,H,W) float64."""
     relu = lambda a: np.maximum(a, 0)
     q = lambda w, b: (bf16_round(w).astype(np.float64), b.astype(np.float64))
-    x = x_hwc.transpose(2, 0, 1).astype(np.float64)
-    x1 = bf16_round(relu(_conv3x3(x, ws[0][0].astype(np.float64), ws[0][1].astype(np.float64))))
+    x = bf16_round(x_hwc.transpose(2, 0, 1)).astype(np.float64)
+    x1 = bf16_round(relu(_conv3x3(x, *q(*ws[0]))))
     f = lambda z, i: bf16_round(relu(_conv3x3(z.astype(np.float64), *q(*ws[i]))))
     x2 = f(x1, 1); x3 = f(x2, 2); x4 = f(x3, 3)
     x5 = f(np.concatenate([x3, x4]), 4)
