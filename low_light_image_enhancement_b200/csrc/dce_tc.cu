@@ -120,16 +120,16 @@ __global__ void __launch_bounds__(kThreads, 1) dce_conv_tc_kernel(const __grid_c
       bulk_g2s(s_w, a.wpk, kWBytes, wbar);
     }
     __syncwarp();
-    int stage = 0;
-    uint32_t phase = 0;
+    uint32_t irow = 0;
     for (int u = blockIdx.x; u < a.units; u += gridDim.x) {
       int n, sx, ys, ye;
       decode(u, n, sx, ys, ye);
       const int yi0 = max(ys - 1, 0), yi1 = min(ye, H - 1);
       const size_t row_stride = (size_t)(FIRST ? 1 : 4) * a.Wp * 8;  // elements between consecutive rows of one source
       size_t off = ((size_t)n * H + yi0) * row_stride + (size_t)sx * kTileX * 8;
-      for (int yi = yi0; yi <= yi1; ++yi, off += row_stride) {
-        mbar_wait(&empty[stage], phase ^ 1);
+      for (int yi = yi0; yi <= yi1; ++yi, off += row_stride, ++irow) {
+        const uint32_t stage = irow & (kStages - 1);
+        mbar_wait(&empty[stage], ((irow / kStages) & 1) ^ 1);
         if (elect_one()) {
           mbar_expect_tx(&full[stage], kStageBytes);
           uint8_t* dst = s_a + stage * kStageBytes;
@@ -140,7 +140,6 @@ __global__ void __launch_bounds__(kThreads, 1) dce_conv_tc_kernel(const __grid_c
           }
         }
         __syncwarp();
-        if (++stage == kStages) { stage = 0; phase ^= 1; }
       }
     }
   } else if (warp == 1) {
@@ -150,57 +149,84 @@ __global__ void __launch_bounds__(kThreads, 1) dce_conv_tc_kernel(const __grid_c
     mbar_wait(wbar, 0);
     const uint64_t a_desc0 = smem_desc(smem_u32(s_a), FIRST ? 16 : kChunkBytes, 128);
     const uint64_t b_desc0 = smem_desc(smem_u32(s_w), kBPlane, 128);
-    int stage = 0;
-    uint32_t phase = 0, free_par = 0;
+    // Ring positions are running counters over the CTA's whole life: input row #irow sits in stage
+    // irow % kStages (phase irow / kStages), output row #o accumulates in slot o % kSlots (use o / kSlots).
+    uint32_t irow = 0, obase = 0;
+    // cnt output rows starting at slot s0; dyslot of the first: 0 = dy+1 (output above), 1 = dy 0, 2 = dy-1
+    auto issue = [&](uint64_t a_stage, uint32_t s0, int cnt, int dyslot) {
+      const uint32_t idesc = idesc_bf16_m128(32 * cnt);
+      const uint32_t d = tmem + s0 * 32;
+      const uint64_t b_row = b_desc0 + (uint64_t)(dyslot * (512 >> 4));
+      if constexpr (FIRST) {
+        mma_bf16_ss(d, a_stage, b_row, idesc, 1u);                                // dx = 0, 1
+        mma_bf16_ss(d, a_stage + 2, b_row + (uint64_t)(kBTile >> 4), idesc, 1u);  // dx = 2, (zero)
+      } else {
+#pragma unroll
+        for (int dx = 0; dx < 3; ++dx) {
+#pragma unroll
+          for (int kk = 0; kk < CHUNKS / 2; ++kk) {
+            const uint64_t ad = a_stage + (uint64_t)((kk * 2 * kChunkBytes + dx * 16) >> 4);
+            const uint64_t bd = b_row + (uint64_t)(((dx * (CHUNKS / 2) + kk) * kBTile) >> 4);
+            mma_bf16_ss(d, ad, bd, idesc, 1u);
+          }
+        }
+      }
+    };
+    // One input row, general form (unit borders, ring wrap).  r = relative output row centred on it.
+    auto row_general = [&](int r, int rows, bool first, bool last) {
+      const int lo = max(r - 1, 0), hi = min(r + 1, rows - 1);  // relative output rows it contributes to
+      // slots touched for the first time must have been drained and re-initialised with the bias
+      for (int o = first ? lo : r + 1; o <= hi; ++o) {
+        const uint32_t og = obase + o;
+        mbar_wait(&acc_free[og & (kSlots - 1)], (og / kSlots) & 1);
+      }
+      const uint32_t stage = irow & (kStages - 1);
+      mbar_wait(&full[stage], (irow / kStages) & 1);
+      tc_fence_after();
+      if (elect_one()) {
+        const uint64_t a_stage = a_desc0 + (uint64_t)(stage * (kStageBytes >> 4));
+        const uint32_t s0 = (obase + lo) & (kSlots - 1);
+        const int cnt = hi - lo + 1, c1 = min(cnt, kSlots - (int)s0), dyslot = lo - (r - 1);
+        issue(a_stage, s0, c1, dyslot);
+        if (c1 < cnt) issue(a_stage, 0, cnt - c1, dyslot + c1);  // the slot ring wrapped
+        mma_commit(&empty[stage]);
+        // output row r-1 has now received its last tap; at the bottom image border so has row r
+        if (r >= 1) mma_commit(&acc_ready[(obase + r - 1) & (kSlots - 1)]);
+        if (last && r == rows - 1) mma_commit(&acc_ready[(obase + r) & (kSlots - 1)]);
+      }
+      __syncwarp();
+      ++irow;
+    };
     for (int u = blockIdx.x; u < a.units; u += gridDim.x) {
       int n, sx, ys, ye;
       decode(u, n, sx, ys, ye);
-      const int yi0 = max(ys - 1, 0), yi1 = min(ye, H - 1);
-      int next_untouched = ys, next_uncommitted = ys;
-      for (int yi = yi0; yi <= yi1; ++yi) {
-        const int lo = max(ys, yi - 1), hi = min(ye - 1, yi + 1);
-        while (next_untouched <= hi) {  // slots this row touches first must be drained + bias-initialised
-          const int s = (next_untouched - ys) & (kSlots - 1);
-          mbar_wait(&acc_free[s], (free_par >> s) & 1);
-          free_par ^= 1u << s;
-          ++next_untouched;
-        }
-        mbar_wait(&full[stage], phase);
+      const int yi0 = max(ys - 1, 0), yi1 = min(ye, H - 1), rows = ye - ys;
+      const int r0 = yi0 - ys, r1 = yi1 - ys;  // relative input rows of the unit: r0 in {-1, 0}, r1 in {rows-1, rows}
+      int r = r0;
+      for (; r <= min(0, r1); ++r) row_general(r, rows, r == r0, r == r1);
+      // interior rows 1 .. rows-2: three output rows r-1..r+1, one new slot (r+1), one finished row (r-1)
+      for (; r <= rows - 2; ++r, ++irow) {
+        const uint32_t og = obase + r + 1;  // the newly touched output row
+        mbar_wait(&acc_free[og & (kSlots - 1)], (og / kSlots) & 1);
+        const uint32_t stage = irow & (kStages - 1);
+        mbar_wait(&full[stage], (irow / kStages) & 1);
         tc_fence_after();
-        const int done_upto = (yi == yi1) ? ye - 1 : yi - 1;
         if (elect_one()) {
           const uint64_t a_stage = a_desc0 + (uint64_t)(stage * (kStageBytes >> 4));
-          int yo = lo;
-          while (yo <= hi) {  // split where the slot ring wraps
-            const int s0 = (yo - ys) & (kSlots - 1);
-            const int cnt = min(hi - yo + 1, kSlots - s0);
-            const int dyslot = yo - (yi - 1);  // 0: dy=+1 (output above), 1: dy=0, 2: dy=-1
-            const uint32_t idesc = idesc_bf16_m128(32 * cnt);
-            const uint32_t d = tmem + s0 * 32;
-            const uint64_t b_row = b_desc0 + (uint64_t)(dyslot * (512 >> 4));
-            if constexpr (FIRST) {
-              mma_bf16_ss(d, a_stage, b_row, idesc, 1u);                                // dx = 0, 1
-              mma_bf16_ss(d, a_stage + 2, b_row + (uint64_t)(kBTile >> 4), idesc, 1u);  // dx = 2, (zero)
-            } else {
-#pragma unroll
-              for (int dx = 0; dx < 3; ++dx) {
-#pragma unroll
-                for (int kk = 0; kk < CHUNKS / 2; ++kk) {
-                  const uint64_t ad = a_stage + (uint64_t)((kk * 2 * kChunkBytes + dx * 16) >> 4);
-                  const uint64_t bd = b_row + (uint64_t)(((dx * (CHUNKS / 2) + kk) * kBTile) >> 4);
-                  mma_bf16_ss(d, ad, bd, idesc, 1u);
-                }
-              }
-            }
-            yo += cnt;
+          const uint32_t s0 = (og - 2) & (kSlots - 1);
+          if (s0 <= kSlots - 3) {
+            issue(a_stage, s0, 3, 0);
+          } else {
+            issue(a_stage, s0, kSlots - (int)s0, 0);
+            issue(a_stage, 0, 3 - (kSlots - (int)s0), kSlots - (int)s0);
           }
           mma_commit(&empty[stage]);
-          for (int yc = next_uncommitted; yc <= done_upto; ++yc) mma_commit(&acc_ready[(yc - ys) & (kSlots - 1)]);
+          mma_commit(&acc_ready[s0]);
         }
         __syncwarp();
-        if (done_upto >= next_uncommitted) next_uncommitted = done_upto + 1;
-        if (++stage == kStages) { stage = 0; phase ^= 1; }
       }
+      for (; r <= r1; ++r) row_general(r, rows, false, r == r1);
+      obase += rows;
     }
   } else {
     // ---------------- epilogue -------------------------------------------------------------------
@@ -215,16 +241,17 @@ __global__ void __launch_bounds__(kThreads, 1) dce_conv_tc_kernel(const __grid_c
     __syncwarp();
     if (lane == 0)
       for (int s = g; s < kSlots; s += 2) mbar_arrive(&acc_free[s]);
-    uint32_t ready_par = 0;
+    uint32_t obase = 0;  // running output-row counter (same sequence as the issuer's)
     for (int u = blockIdx.x; u < a.units; u += gridDim.x) {
       int n, sx, ys, ye;
       decode(u, n, sx, ys, ye);
       const int x = sx * kTileX + q * 32 + lane;
       const bool x_ok = x < a.W;
-      for (int i = g; i < ye - ys; i += 2) {
-        const int y = ys + i, s = i & (kSlots - 1);
-        mbar_wait(&acc_ready[s], (ready_par >> s) & 1);
-        ready_par ^= 1u << s;
+      const int rows = ye - ys;
+      for (int i = (g ^ obase) & 1; i < rows; i += 2) {  // group g owns the output rows with (counter & 1) == g
+        const uint32_t og = obase + i;
+        const int y = ys + i, s = og & (kSlots - 1);
+        mbar_wait(&acc_ready[s], (og / kSlots) & 1);
         tc_fence_after();
         uint32_t v[32];
         tmem_ld32(tmem + lane_base + s * 32, v);
@@ -272,6 +299,7 @@ __global__ void __launch_bounds__(kThreads, 1) dce_conv_tc_kernel(const __grid_c
           }
         }
       }
+      obase += rows;
     }
   }
   tc_fence_before();
