@@ -439,9 +439,12 @@ int dce_forward_bf16(llie_ctx* ctx, const float* in, float* out, float* maps, in
   DceTcPack& pk = g_packs[ctx];
   const int strips = (w + kTileX - 1) / kTileX, wp = strips * kTileX + 2;
   const size_t act_elems_per_img = (size_t)h * 4 * wp * 8, in_elems_per_img = (size_t)h * wp * 8;
-  // frames per pass: six bf16 activations + the packed input per frame, kept under ~8.5 GiB
-  long long chunk = (17ll << 29) / (long long)((6 * act_elems_per_img + in_elems_per_img) * 2);
+  // frames per pass: six bf16 activations + the packed input per frame (0.93 GB at 1080p), kept under
+  // ~24 GiB, and the passes balanced (64 frames -> 22 + 21 + 21, not 25 + 25 + 14)
+  long long chunk = (24ll << 30) / (long long)((6 * act_elems_per_img + in_elems_per_img) * 2);
   chunk = chunk < 1 ? 1 : (chunk > n ? n : chunk);
+  const long long passes = (n + chunk - 1) / chunk;
+  chunk = (n + passes - 1) / passes;
   void* ws;
   // + slack: conv1's staged rows run 2 pixels past a row's end (zero-weighted, but must be readable)
   const size_t ws_bytes = (size_t)chunk * (6 * act_elems_per_img + in_elems_per_img) * 2 + 256;

@@ -8,17 +8,21 @@ namespace {
 
 constexpr int kFold = 64;  // taps accumulated locally before folding into the running sum
 
-// FIR along x.  Data is `rows` rows of W pixels with C interleaved channels (C=3: NHWC image
-// rows; C=1: NCHW plane rows).  Each thread produces 4 consecutive pixels of one channel with a
+// FIR along x.  Data is rows of W pixels with C interleaved channels (C=3: NHWC image rows;
+// C=1: NCHW plane rows).  Each thread produces 4 consecutive pixels of one channel with a
 // sliding set of 4 weights, reading the clamped input segment from shared memory.
+// Row addressing: blockIdx.x = p * rows_per_plane + i handles buffer row p * plane_rows + row_lo + i
+// (a band of rows_per_plane rows in each plane of plane_rows rows).  All rows of a buffer:
+// rows_per_plane = gridDim.x, plane_rows = 0, row_lo = 0.
 template <bool kAffine>
 __global__ void __launch_bounds__(128) fir_x_kernel(const float* __restrict__ in, float* __restrict__ out,
                                                     const float* __restrict__ taps, int r, int W, int C,
-                                                    float a, float b) {
+                                                    float a, float b, int rows_per_plane, int plane_rows, int row_lo) {
   extern __shared__ float seg[];
   const int TX = 128;
   const int x0 = blockIdx.y * TX;
-  const long long row = blockIdx.x;
+  const int pl = blockIdx.x / rows_per_plane;
+  const long long row = (long long)pl * plane_rows + row_lo + (blockIdx.x - pl * rows_per_plane);
   const float* src = in + row * (long long)W * C;
   const int seg_px = TX + 2 * r + 3;
   for (int i = threadIdx.x; i < seg_px * C; i += blockDim.x) {
@@ -58,14 +62,16 @@ __global__ void __launch_bounds__(128) fir_x_kernel(const float* __restrict__ in
   }
 }
 
-// FIR along y on `planes` planes stored as in_rows x RW (input) and out_rows x RW (output).
+// FIR along y on `planes` planes stored as in_rows x RW (input) and out_plane_rows x RW (output).
 // Rows are addressed by their index in a level of H rows: buffer row b of the input holds level
-// row in_row0 + b, and outputs are produced for level rows out_row0 .. out_row0+out_rows-1; taps
-// that fall outside [0, H) are clamped (the caller guarantees the clamped rows are in the buffer).
-// One image: in_row0 = out_row0 = 0, in_rows = out_rows = H.  4 consecutive rows per thread.
+// row in_row0 + b, and outputs are produced for level rows out_row0 .. out_row0+out_rows-1, stored
+// at output buffer rows out_buf_row0 .. ; taps that fall outside [0, H) are clamped (the caller
+// guarantees the clamped rows are in the buffer).  One image: in_row0 = out_row0 = out_buf_row0 = 0,
+// in_rows = out_rows = out_plane_rows = H.  4 consecutive rows per thread.
 __global__ void __launch_bounds__(128) fir_y_kernel(const float* __restrict__ in, float* __restrict__ out,
                                                     const float* __restrict__ taps, int r, int H, int RW,
-                                                    int in_row0, int in_rows, int out_row0, int out_rows) {
+                                                    int in_row0, int in_rows, int out_row0, int out_rows,
+                                                    int out_buf_row0, int out_plane_rows) {
   const int j = blockIdx.x * blockDim.x + threadIdx.x;
   if (j >= RW) return;
   const int yb = blockIdx.y * 4;           // first output buffer row of this thread
@@ -91,7 +97,7 @@ __global__ void __launch_bounds__(128) fir_y_kernel(const float* __restrict__ in
 #pragma unroll
     for (int q = 0; q < 4; ++q) acc[q] += p[q];
   }
-  float* dst = out + plane * (long long)out_rows * RW + j;
+  float* dst = out + (plane * (long long)out_plane_rows + out_buf_row0) * RW + j;
 #pragma unroll
   for (int q = 0; q < 4; ++q)
     if (yb + q < out_rows) dst[(long long)(yb + q) * RW] = acc[q];

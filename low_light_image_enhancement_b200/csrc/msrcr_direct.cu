@@ -100,9 +100,9 @@ int msrcr_direct_run(llie_ctx* ctx, const float* in, float* out, int n, int h, i
       float* sur = (float*)d_sur + (size_t)s * chunk * img_elems;
       dim3 gx((unsigned)rows, (w + 127) / 128);
       size_t sm = (size_t)(128 + 2 * radius[s] + 3) * C * sizeof(float);
-      LLIE_LAUNCH(ctx, st, "fir_x_kernel", fir_x_kernel<true><<<gx, 128, sm, st>>>(src, (float*)d_tmp, k, radius[s], w, C, p.in_scale, p.in_bias));
+      LLIE_LAUNCH(ctx, st, "fir_x_kernel", fir_x_kernel<true><<<gx, 128, sm, st>>>(src, (float*)d_tmp, k, radius[s], w, C, p.in_scale, p.in_bias, (int)rows, 0, 0));
       dim3 gy((RW + 127) / 128, (h + 3) / 4, planes);
-      LLIE_LAUNCH(ctx, st, "fir_y_kernel", fir_y_kernel<<<gy, 128, 0, st>>>((const float*)d_tmp, sur, k, radius[s], h, RW, 0, h, 0, h));
+      LLIE_LAUNCH(ctx, st, "fir_y_kernel", fir_y_kernel<<<gy, 128, 0, st>>>((const float*)d_tmp, sur, k, radius[s], h, RW, 0, h, 0, h, 0, h));
     }
     long long npx = (long long)nb * h * w;
     LLIE_LAUNCH(ctx, st, "msrcr_epilogue_kernel", msrcr_epilogue_kernel<<<(unsigned)((npx + 255) / 256), 256, 0, st>>>(

@@ -372,12 +372,12 @@ int msrcr_pyramid_run(llie_ctx* ctx, const float* in, float* out, int n, int h, 
     float* sc = (float*)dSC + (size_t)k * c_elems;
     if (sp.level == 0) {
       dim3 gx((unsigned)((long long)planes * hC), ceil_div(wC, 128)), gy(ceil_div(wC, 128), ceil_div(hC, 4), planes);
-      LLIE_LAUNCH(ctx, st, "fir_x_kernel", fir_x_kernel<false><<<gx, 128, sm, st>>>((const float*)dC, (float*)dCt, taps, r, wC, 1, 1.f, 0.f));
-      LLIE_LAUNCH(ctx, st, "fir_y_kernel", fir_y_kernel<<<gy, 128, 0, st>>>((const float*)dCt, sc, taps, r, hC, wC, 0, hC, 0, hC));
+      LLIE_LAUNCH(ctx, st, "fir_x_kernel", fir_x_kernel<false><<<gx, 128, sm, st>>>((const float*)dC, (float*)dCt, taps, r, wC, 1, 1.f, 0.f, planes * hC, 0, 0));
+      LLIE_LAUNCH(ctx, st, "fir_y_kernel", fir_y_kernel<<<gy, 128, 0, st>>>((const float*)dCt, sc, taps, r, hC, wC, 0, hC, 0, hC, 0, hC));
     } else {
       dim3 gx((unsigned)((long long)planes * hB), ceil_div(wB, 128)), gy(ceil_div(wB, 128), ceil_div(hB, 4), planes);
-      LLIE_LAUNCH(ctx, st, "fir_x_kernel", fir_x_kernel<false><<<gx, 128, sm, st>>>((const float*)dB, (float*)dBt, taps, r, wB, 1, 1.f, 0.f));
-      LLIE_LAUNCH(ctx, st, "fir_y_kernel", fir_y_kernel<<<gy, 128, 0, st>>>((const float*)dBt, (float*)dSB, taps, r, hB, wB, 0, hB, 0, hB));
+      LLIE_LAUNCH(ctx, st, "fir_x_kernel", fir_x_kernel<false><<<gx, 128, sm, st>>>((const float*)dB, (float*)dBt, taps, r, wB, 1, 1.f, 0.f, planes * hB, 0, 0));
+      LLIE_LAUNCH(ctx, st, "fir_y_kernel", fir_y_kernel<<<gy, 128, 0, st>>>((const float*)dBt, (float*)dSB, taps, r, hB, wB, 0, hB, 0, hB, 0, hB));
       dim3 ux(ceil_div((long long)hB * wC, 256), 1, planes), uy(ceil_div((long long)hC * wC, 256), 1, planes);
       LLIE_LAUNCH(ctx, st, "up_bc_x_kernel", up_bc_x_kernel<<<ux, 256, 0, st>>>((const float*)dSB, (float*)dT2, hB, wB, wC, 0, hB, pl->uw));
       LLIE_LAUNCH(ctx, st, "up_bc_y_kernel", up_bc_y_kernel<<<uy, 256, 0, st>>>((const float*)dT2, sc, hB, hC, wC, 0, hC, pl->uw));
