@@ -392,6 +392,65 @@ def _enhancer(device: int) -> Enhancer:
     return e
 
 
+def _tile_enhancer(device: int, slot: int) -> Enhancer:
+    """Extra contexts for row-tiled MSRCR: one per shard, also when several shards share a device."""
+    cache = getattr(_tls, "tile_cache", None)
+    if cache is None:
+        cache = _tls.tile_cache = {}
+    e = cache.get((device, slot))
+    if e is None:
+        e = cache[(device, slot)] = Enhancer(device)
+    return e
+
+
+def tile_rows(h: int, parts: int) -> list[tuple[int, int]]:
+    """Row partition of an h-row image into `parts` shards [(row0, rows), ...] for msrcr_tiled():
+    equal shards with interior boundaries on multiples of 4 (the stride of the first cascade level)."""
+    if parts <= 0 or h <= 0:
+        raise ValueError(f"bad partition {h} rows / {parts} parts")
+    bounds = [0] + [min(h, ((h * i // parts) + 3) // 4 * 4) for i in range(1, parts)] + [h]
+    out = [(bounds[i], bounds[i + 1] - bounds[i]) for i in range(parts)]
+    if any(r <= 0 for _, r in out):
+        raise ValueError(f"image of {h} rows is too small for {parts} shards")
+    return out
+
+
+def msrcr_tiled(shards: Sequence[torch.Tensor], params: dict | None = None, *, outs: Sequence[torch.Tensor] | None = None):
+    """MSRCR of ONE image held as horizontal shards (BASELINE.json configs[4]).
+
+    shards : CUDA float32 tensors of shape (rows_d, W, 3), top to bottom; shard d lives on the device
+             that processes it.  Either every shard is on its own device (halo rows travel as NVLink
+             peer-to-peer copies, no NCCL) or all are on one device ("virtual devices", used by the
+             single-GPU tests).  Interior boundaries must be multiples of 4 rows (see tile_rows()).
+    Returns the enhanced shards (same shapes/devices).  Synchronous: returns when every device is done.
+    """
+    if len(shards) == 0:
+        return []
+    for t in shards:
+        if not (isinstance(t, torch.Tensor) and t.is_cuda and t.dtype == torch.float32 and t.dim() == 3
+                and t.shape[2] == 3 and t.is_contiguous()):
+            raise TypeError("msrcr_tiled shards must be contiguous CUDA float32 tensors of shape (rows, W, 3)")
+    w = int(shards[0].shape[1])
+    if any(int(t.shape[1]) != w for t in shards):
+        raise ValueError("all shards must have the same width")
+    outs = [torch.empty_like(t) for t in shards] if outs is None else list(outs)
+    for y, t in zip(outs, shards):
+        _check_out(y, t)
+    mp = _msrcr_struct(params)
+    n = len(shards)
+    devs = [t.device.index for t in shards]
+    enh = [_tile_enhancer(dv, i if len(set(devs)) == 1 else 0) for i, dv in enumerate(devs)]
+    rows = [int(t.shape[0]) for t in shards]
+    row0 = [sum(rows[:i]) for i in range(n)]
+    for t in shards:  # the library runs on its own streams: order it after the producers of the inputs
+        torch.cuda.current_stream(t.device).synchronize()
+    VP, I = C.c_void_p * n, C.c_int * n
+    _lib.check(_lib.load().llie_msrcr_tiled(VP(*[e._h.value for e in enh]), n, VP(*[t.data_ptr() for t in shards]),
+                                            VP(*[y.data_ptr() for y in outs]), I(*row0), I(*rows), sum(rows), w,
+                                            C.byref(mp)))
+    return outs
+
+
 def enhance(images, method: str, params: dict | None = None, *, out=None, device: int | None = None):
     """Enhance a low-light image batch on a B200.
 

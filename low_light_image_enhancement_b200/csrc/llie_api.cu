@@ -152,6 +152,7 @@ int llie_destroy(llie_ctx* ctx) {
   msrcr_plan_free(ctx->plan);
   dce_weights_free(ctx->dce);
   dce_tc_release(ctx);
+  if (ctx->tile_event) cudaEventDestroy(ctx->tile_event);
   if (ctx->stream) cudaStreamDestroy(ctx->stream);
   delete ctx;
   return LLIE_OK;

@@ -75,6 +75,7 @@ struct llie_ctx {
   struct ProfRec { const char* name; cudaEvent_t e0, e1; };
   std::vector<ProfRec> prof;
   cudaEvent_t prof_pending = nullptr;
+  cudaEvent_t tile_event = nullptr;  // "my level-C rows are ready" (row-tiled MSRCR)
 
   // Returns a device buffer of at least `bytes` under `name`; reallocates only when growing.
   int workspace(const char* name, size_t bytes, void** out);
@@ -122,6 +123,8 @@ int msrcr_pyramid_run(llie_ctx* ctx, const float* in, float* out, int n, int h, 
                       const llie_msrcr_params& p, cudaStream_t st);
 int msrcr_plan_query(float sigma, float truncate, int* stride, double* sigma_low, int* radius_low, double* l1);
 void msrcr_plan_free(MsrcrPlan* p);
+int msrcr_tiled_run(llie_ctx* const* ctxs, int n_dev, const float* const* in, float* const* out, const int* row0,
+                    const int* rows, int H, int W, const llie_msrcr_params& p);
 
 int dce_weights_upload(llie_ctx* ctx, const float* host_packed, size_t count);
 void dce_weights_free(DceWeights* w);

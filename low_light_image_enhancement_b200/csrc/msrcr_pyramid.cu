@@ -17,7 +17,10 @@
 #include <algorithm>
 #include <cmath>
 #include <cstring>
+#include <condition_variable>
 #include <mutex>
+#include <string>
+#include <thread>
 
 namespace llie {
 
@@ -302,6 +305,54 @@ void launch_final(dim3 grid, cudaStream_t st, const float* x, float* out, ImgVie
   msrcr_final_kernel<N6, N4><<<grid, 128, 0, st>>>(x, out, v, io, W, in_row0, row_begin, row_end, rps, fp);
 }
 
+
+// K5 launches: rows [row_begin, row_end) of n images whose pointers start at image row in_row0.
+int final_passes(llie_ctx* ctx, cudaStream_t st, const MsrcrPlan* pl, const llie_msrcr_params& p, const float* in,
+                 float* out, const ImgView& v, bool vec, bool nhwc, int n, int h_view, int w, int in_row0, int row_begin,
+                 int row_end, int hC, int wC, const float* dSC, size_t c_elems, float* dAcc) {
+  (void)h_view;
+  const int io = vec ? (nhwc ? kIoNhwcVec : kIoNchwVec) : kIoScalar;
+  const int cx = ceil_div(w, 4 * kFinalCells);
+  const int rps = pick_strip(row_end - row_begin, (long long)cx * n, 16 * ctx->sm_count, 16, 64, 4);
+  dim3 grid(cx, ceil_div(row_end - row_begin, rps), n);
+  FinalParams fp;
+  memset(&fp, 0, sizeof(fp));
+  fp.hC = hC; fp.wC = wC;
+  const double ln2 = 0.6931471805599453;
+  double wsum = 0;
+  for (int k = 0; k < p.n_scales; ++k) wsum += p.weight[k];
+  fp.wsum2 = (float)(ln2 * wsum);
+  fp.beta_ln_alpha = (float)(p.beta * std::log((double)p.alpha));
+  fp.beta_ln2 = (float)(p.beta * ln2);
+  fp.gain255 = p.gain / 255.f;
+  fp.offset255 = p.offset / 255.f;
+  fp.in_scale = p.in_scale; fp.in_bias = p.in_bias;
+  int n6 = 0;
+  for (auto& sc : pl->scales) n6 += (sc.level == 0);
+  if (p.n_scales == 3 && n6 == 1) {
+    for (int i = 0; i < 3; ++i) {
+      const int k = pl->order[i];
+      fp.map[i] = dSC + (size_t)k * c_elems;
+      fp.w2[i] = (float)(ln2 * p.weight[k]);
+    }
+    LLIE_LAUNCH(ctx, st, "msrcr_final_kernel", (launch_final<1, 2>(grid, st, in, out, v, io, w, in_row0, row_begin, row_end, rps, fp)));
+  } else {
+    for (int k0 = 0; k0 < p.n_scales; k0 += 3) {
+      const int cnt = std::min(3, p.n_scales - k0);
+      for (int i = 0; i < cnt; ++i) {
+        fp.map[i] = dSC + (size_t)(k0 + i) * c_elems;
+        fp.w2[i] = (float)(ln2 * p.weight[k0 + i]);
+      }
+      fp.acc_in = k0 > 0 ? (const float*)dAcc : nullptr;
+      fp.acc_out = k0 + cnt < p.n_scales ? dAcc : nullptr;
+      if (cnt == 1) LLIE_LAUNCH(ctx, st, "msrcr_final_kernel", (launch_final<1, 0>(grid, st, in, out, v, io, w, in_row0, row_begin, row_end, rps, fp)));
+      if (cnt == 2) LLIE_LAUNCH(ctx, st, "msrcr_final_kernel", (launch_final<2, 0>(grid, st, in, out, v, io, w, in_row0, row_begin, row_end, rps, fp)));
+      if (cnt == 3) LLIE_LAUNCH(ctx, st, "msrcr_final_kernel", (launch_final<3, 0>(grid, st, in, out, v, io, w, in_row0, row_begin, row_end, rps, fp)));
+    }
+  }
+  return LLIE_OK;
+}
+
 }  // namespace
 
 int msrcr_pyramid_run(llie_ctx* ctx, const float* in, float* out, int n, int h, int w, int layout,
@@ -383,47 +434,288 @@ int msrcr_pyramid_run(llie_ctx* ctx, const float* in, float* out, int n, int h, 
       LLIE_LAUNCH(ctx, st, "up_bc_y_kernel", up_bc_y_kernel<<<uy, 256, 0, st>>>((const float*)dT2, sc, hB, hC, wC, 0, hC, pl->uw));
     }
   }
-  {  // K5: final pass(es)
-    const int io = vec ? (nhwc ? kIoNhwcVec : kIoNchwVec) : kIoScalar;
-    const int cx = ceil_div(w, 4 * kFinalCells);
-    const int rps = pick_strip(h, (long long)cx * n, 16 * ctx->sm_count, 16, 64, 4);
-    dim3 grid(cx, ceil_div(h, rps), n);
-    FinalParams fp;
-    memset(&fp, 0, sizeof(fp));
-    fp.hC = hC; fp.wC = wC;
-    const double ln2 = 0.6931471805599453;
-    double wsum = 0;
-    for (int k = 0; k < p.n_scales; ++k) wsum += p.weight[k];
-    fp.wsum2 = (float)(ln2 * wsum);
-    fp.beta_ln_alpha = (float)(p.beta * std::log((double)p.alpha));
-    fp.beta_ln2 = (float)(p.beta * ln2);
-    fp.gain255 = p.gain / 255.f;
-    fp.offset255 = p.offset / 255.f;
-    fp.in_scale = p.in_scale; fp.in_bias = p.in_bias;
-    int n6 = 0;
-    for (auto& s : pl->scales) n6 += (s.level == 0);
-    if (p.n_scales == 3 && n6 == 1) {
-      for (int i = 0; i < 3; ++i) {
-        const int k = pl->order[i];
-        fp.map[i] = (const float*)dSC + (size_t)k * c_elems;
-        fp.w2[i] = (float)(ln2 * p.weight[k]);
-      }
-      LLIE_LAUNCH(ctx, st, "msrcr_final_kernel", (launch_final<1, 2>(grid, st, in, out, v, io, w, 0, 0, h, rps, fp)));
+  LLIE_TRY(final_passes(ctx, st, pl, p, in, out, v, vec, nhwc, n, h, w, 0, 0, h, hC, wC, (const float*)dSC, c_elems,
+                        (float*)dAcc));
+  return LLIE_OK;
+}
+
+
+// ---- row-tiled variant (config 5) -----------------------------------------------------------------
+// One image of H x W pixels is split into horizontal shards, one per device.  Every level of the
+// cascade keeps its GLOBAL row indexing on every device (buffers are sized for the whole image; only
+// the rows a device needs are ever touched), so the single-device kernels run unchanged on row
+// ranges.  What crosses devices:
+//   1. 16 raw image rows from each vertical neighbour (the stride-4 prefilter's reach), copied into
+//      small "band" buffers so that the boundary V rows are computed locally;
+//   2. stride-4 level-C rows: every device computes the C rows centred on its own pixels and then
+//      fetches the C rows its large-sigma surrounds reach (about 4*sigma_max/4 rows each way) from
+//      whichever devices own them.  For 16384 x 16384 and sigma = 250 that is ~15 MB per side
+//      instead of the 271 MB of full-resolution row-blurred halos.
+// Everything after the C-level gather (B level, low-resolution FIRs, upsampling, epilogue) is local
+// and recomputed redundantly on the overlap, which is 1/16 .. 1/256 of the pixel count.
+// Copies are cudaMemcpyPeerAsync over NVLink (plain device-to-device copies when the shards are
+// "virtual devices" on one GPU); there is no NCCL and no collective.
+namespace {
+
+struct TileGeom {
+  int R0, R1;            // image rows of the shard
+  int own_lo, own_hi;    // C rows this device computes from its own pixels
+  int s_lo, s_hi;        // C-resolution surround rows the final kernel reads
+  int c0_lo, c0_hi;      // C rows needed by the stride-4 (level C) scales
+  int t_lo, t_hi;        // B-resolution surround rows (SB / T2) needed by the upsampler
+  int bb_lo, bb_hi;      // B rows needed by the stride-16 FIRs
+  int c1_lo, c1_hi;      // C rows needed to build those B rows
+  int cn_lo, cn_hi;      // union: all C rows this device must hold
+};
+
+inline int clampi(int v, int lo, int hi) { return v < lo ? lo : (v > hi ? hi : v); }
+
+int up_bc_j0(int jc) {  // mirrors up_bc_phase()
+  const int d = jc - kPC + 4, ph = d & 3;
+  return (d >> 2) - 1 + kPB + (ph >= 2 ? 1 : 0);
+}
+
+TileGeom tile_geometry(int d, int n_dev, const int* row0, const int* rows, int H, int r0_max, int rb_max, bool any_b) {
+  const int hC = level_c_size(H), hB = level_b_size(H);
+  TileGeom g;
+  g.R0 = row0[d];
+  g.R1 = row0[d] + rows[d];
+  g.own_lo = d == 0 ? 0 : g.R0 / 4 + kPC;
+  g.own_hi = d == n_dev - 1 ? hC : g.R1 / 4 + kPC;
+  g.s_lo = clampi(g.R0 / 4 + kPC - 2, 0, hC);
+  g.s_hi = clampi((g.R1 - 1) / 4 + kPC + 5, 0, hC);
+  g.c0_lo = clampi(g.s_lo - r0_max, 0, hC);
+  g.c0_hi = clampi(g.s_hi + r0_max, 0, hC);
+  g.cn_lo = g.c0_lo;
+  g.cn_hi = g.c0_hi;
+  g.t_lo = g.t_hi = g.bb_lo = g.bb_hi = g.c1_lo = g.c1_hi = 0;
+  if (any_b) {
+    g.t_lo = clampi(up_bc_j0(g.s_lo) - kTU, 0, hB);
+    g.t_hi = clampi(up_bc_j0(g.s_hi - 1) + kTU + 1, 0, hB);
+    g.bb_lo = clampi(g.t_lo - rb_max, 0, hB);
+    g.bb_hi = clampi(g.t_hi + rb_max, 0, hB);
+    g.c1_lo = clampi(4 * (g.bb_lo - kPB) + kPC - kRD, 0, hC - 1);
+    g.c1_hi = clampi(4 * (g.bb_hi - 1 - kPB) + kPC + kRD, 0, hC - 1) + 1;
+    g.cn_lo = std::min(g.cn_lo, g.c1_lo);
+    g.cn_hi = std::max(g.cn_hi, g.c1_hi);
+  }
+  g.cn_lo = std::min(g.cn_lo, g.own_lo);
+  g.cn_hi = std::max(g.cn_hi, g.own_hi);
+  return g;
+}
+
+}  // namespace
+
+
+namespace {
+
+struct TileBufs {
+  float *V, *C, *Ct, *SC, *TB, *B, *Bt, *SB, *T2, *band_top, *band_bot;
+};
+
+constexpr int kBandTopRows = 48, kBandBotRows = 64, kHaloRaw = 16;
+
+int copy_dev(void* dst, int dst_dev, const void* src, int src_dev, size_t bytes, cudaStream_t st) {
+  if (dst_dev == src_dev) LLIE_CUDA_OK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToDevice, st));
+  else LLIE_CUDA_OK(cudaMemcpyPeerAsync(dst, dst_dev, src, src_dev, bytes, st));
+  return LLIE_OK;
+}
+
+// Phase A on device d: raw-row bands from the neighbours, V, and the C rows centred on own pixels.
+int tiled_phase_a(llie_ctx* ctx, int d, int n_dev, llie_ctx* const* ctxs, const float* const* in, const int* rows,
+                  const TileGeom& g, const TileBufs& b, int H, int W, const llie_msrcr_params& p) {
+  cudaStream_t st = ctx->stream;
+  const int RW = 3 * W, hC = level_c_size(H), wC = level_c_size(W);
+  const bool vec = (W % 4 == 0) && (reinterpret_cast<uintptr_t>(in[d]) % 16 == 0);
+  const bool first = d == 0, last = d == n_dev - 1;
+  const size_t row_bytes = (size_t)RW * sizeof(float);
+  if (!first) {  // rows [R0-16, R0) from the device above, [R0, R0+32) own
+    LLIE_TRY(copy_dev(b.band_top, ctx->device, in[d - 1] + (size_t)(rows[d - 1] - kHaloRaw) * RW, ctxs[d - 1]->device,
+                      kHaloRaw * row_bytes, st));
+    LLIE_TRY(copy_dev(b.band_top + (size_t)kHaloRaw * RW, ctx->device, in[d], ctx->device,
+                      (kBandTopRows - kHaloRaw) * row_bytes, st));
+  }
+  if (!last) {  // rows [R1-48, R1) own, [R1, R1+16) from the device below
+    LLIE_TRY(copy_dev(b.band_bot, ctx->device, in[d] + (size_t)(rows[d] - (kBandBotRows - kHaloRaw)) * RW, ctx->device,
+                      (kBandBotRows - kHaloRaw) * row_bytes, st));
+    LLIE_TRY(copy_dev(b.band_bot + (size_t)(kBandBotRows - kHaloRaw) * RW, ctx->device, in[d + 1], ctxs[d + 1]->device,
+                      kHaloRaw * row_bytes, st));
+  }
+  const int vi_lo = first ? 0 : g.R0 / 4 + kPC + 4;                  // V rows whose 33-tap window stays inside the shard
+  const int vi_hi = last ? hC : (g.R1 - 17) / 4 + kPC + 1;           // (or clamps at a true image border)
+  auto rows_launch = [&](const float* x, int in_row0, int in_rows, int v0, int v1, int want) -> int {
+    if (v0 >= v1) return LLIE_OK;
+    if (vec) {
+      const int cx = ceil_div(RW, 512);
+      const int rps = pick_strip(v1 - v0, cx, want, 4, 64, 1);
+      dim3 grid(cx, ceil_div(v1 - v0, rps), 1);
+      LLIE_LAUNCH(ctx, st, "down4_rows_kernel",
+                  down4_rows_kernel<4><<<grid, 128, 0, st>>>(x, 0, RW, H, in_row0, in_rows, b.V, hC, v0, v1, rps));
     } else {
-      for (int k0 = 0; k0 < p.n_scales; k0 += 3) {
-        const int cnt = std::min(3, p.n_scales - k0);
-        for (int i = 0; i < cnt; ++i) {
-          fp.map[i] = (const float*)dSC + (size_t)(k0 + i) * c_elems;
-          fp.w2[i] = (float)(ln2 * p.weight[k0 + i]);
-        }
-        fp.acc_in = k0 > 0 ? (const float*)dAcc : nullptr;
-        fp.acc_out = k0 + cnt < p.n_scales ? (float*)dAcc : nullptr;
-        if (cnt == 1) LLIE_LAUNCH(ctx, st, "msrcr_final_kernel", (launch_final<1, 0>(grid, st, in, out, v, io, w, 0, 0, h, rps, fp)));
-        if (cnt == 2) LLIE_LAUNCH(ctx, st, "msrcr_final_kernel", (launch_final<2, 0>(grid, st, in, out, v, io, w, 0, 0, h, rps, fp)));
-        if (cnt == 3) LLIE_LAUNCH(ctx, st, "msrcr_final_kernel", (launch_final<3, 0>(grid, st, in, out, v, io, w, 0, 0, h, rps, fp)));
-      }
+      const int cx = ceil_div(RW, 128);
+      const int rps = pick_strip(v1 - v0, cx, want, 4, 64, 1);
+      dim3 grid(cx, ceil_div(v1 - v0, rps), 1);
+      LLIE_LAUNCH(ctx, st, "down4_rows_kernel",
+                  down4_rows_kernel<1><<<grid, 128, 0, st>>>(x, 0, RW, H, in_row0, in_rows, b.V, hC, v0, v1, rps));
+    }
+    return LLIE_OK;
+  };
+  if (!first) LLIE_TRY(rows_launch(b.band_top, g.R0 - kHaloRaw, kBandTopRows, g.own_lo, vi_lo, 1));
+  if (!last) LLIE_TRY(rows_launch(b.band_bot, g.R1 - (kBandBotRows - kHaloRaw), kBandBotRows, vi_hi, g.own_hi, 1));
+  LLIE_TRY(rows_launch(in[d], g.R0, rows[d], vi_lo, vi_hi, 8 * ctx->sm_count));
+  dim3 grid(ceil_div(wC, 128), g.own_hi - g.own_lo, 1);
+  LLIE_LAUNCH(ctx, st, "down4_cols_kernel",
+              down4_cols_kernel<3><<<grid, 128, 0, st>>>(b.V, b.C, RW, W, hC, wC, g.own_lo, p.in_scale, p.in_bias));
+  return LLIE_OK;
+}
+
+// Phase B on device d: fetch the foreign C rows, then everything downstream, locally.
+int tiled_phase_b(llie_ctx* ctx, int d, int n_dev, llie_ctx* const* ctxs, const float* const* in, float* const* out,
+                  const std::vector<TileGeom>& geo, const std::vector<TileBufs>& bufs, const std::vector<cudaEvent_t>& ev_c,
+                  int H, int W, const llie_msrcr_params& p) {
+  cudaStream_t st = ctx->stream;
+  const TileGeom& g = geo[d];
+  const TileBufs& b = bufs[d];
+  const MsrcrPlan* pl = ctx->plan;
+  const int hC = level_c_size(H), wC = level_c_size(W), hB = level_b_size(H), wB = level_b_size(W);
+  const size_t c_elems = (size_t)3 * hC * wC;
+  for (int e = 0; e < n_dev; ++e) {
+    if (e == d) continue;
+    const int lo = std::max(g.cn_lo, geo[e].own_lo), hi = std::min(g.cn_hi, geo[e].own_hi);
+    if (lo >= hi) continue;
+    LLIE_CUDA_OK(cudaStreamWaitEvent(st, ev_c[e], 0));
+    for (int pln = 0; pln < 3; ++pln) {
+      const size_t off = ((size_t)pln * hC + lo) * wC;
+      LLIE_TRY(copy_dev(b.C + off, ctx->device, bufs[e].C + off, ctxs[e]->device, (size_t)(hi - lo) * wC * sizeof(float), st));
     }
   }
+  int n_b = 0;
+  for (auto& sp : pl->scales) n_b += sp.level;
+  if (n_b) {
+    dim3 gx(ceil_div((long long)(g.c1_hi - g.c1_lo) * wB, 256), 1, 3), gy(ceil_div((long long)(g.bb_hi - g.bb_lo) * wB, 256), 1, 3);
+    LLIE_LAUNCH(ctx, st, "decim4_x_kernel", decim4_x_kernel<<<gx, 256, 0, st>>>(b.C, b.TB, hC, wC, wB, g.c1_lo, g.c1_hi));
+    LLIE_LAUNCH(ctx, st, "decim4_y_kernel", decim4_y_kernel<<<gy, 256, 0, st>>>(b.TB, b.B, hC, hB, wB, g.bb_lo, g.bb_hi));
+  }
+  for (int k = 0; k < p.n_scales; ++k) {
+    const ScalePlan& sp = pl->scales[k];
+    const float* taps = pl->d_taps + pl->tap_off[k];
+    const int r = sp.radius_low;
+    const size_t sm = (size_t)(128 + 2 * r + 3) * sizeof(float);
+    float* sc = b.SC + (size_t)k * c_elems;
+    if (sp.level == 0) {
+      const int x0 = clampi(g.s_lo - r, 0, hC), x1 = clampi(g.s_hi + r, 0, hC);
+      dim3 gx(3 * (x1 - x0), ceil_div(wC, 128)), gy(ceil_div(wC, 128), ceil_div(g.s_hi - g.s_lo, 4), 3);
+      LLIE_LAUNCH(ctx, st, "fir_x_kernel", fir_x_kernel<false><<<gx, 128, sm, st>>>(b.C, b.Ct, taps, r, wC, 1, 1.f, 0.f, x1 - x0, hC, x0));
+      LLIE_LAUNCH(ctx, st, "fir_y_kernel", fir_y_kernel<<<gy, 128, 0, st>>>(b.Ct, sc, taps, r, hC, wC, 0, hC, g.s_lo, g.s_hi - g.s_lo, g.s_lo, hC));
+    } else {
+      const int x0 = clampi(g.t_lo - r, 0, hB), x1 = clampi(g.t_hi + r, 0, hB);
+      dim3 gx(3 * (x1 - x0), ceil_div(wB, 128)), gy(ceil_div(wB, 128), ceil_div(g.t_hi - g.t_lo, 4), 3);
+      LLIE_LAUNCH(ctx, st, "fir_x_kernel", fir_x_kernel<false><<<gx, 128, sm, st>>>(b.B, b.Bt, taps, r, wB, 1, 1.f, 0.f, x1 - x0, hB, x0));
+      LLIE_LAUNCH(ctx, st, "fir_y_kernel", fir_y_kernel<<<gy, 128, 0, st>>>(b.Bt, b.SB, taps, r, hB, wB, 0, hB, g.t_lo, g.t_hi - g.t_lo, g.t_lo, hB));
+      dim3 ux(ceil_div((long long)(g.t_hi - g.t_lo) * wC, 256), 1, 3), uy(ceil_div((long long)(g.s_hi - g.s_lo) * wC, 256), 1, 3);
+      LLIE_LAUNCH(ctx, st, "up_bc_x_kernel", up_bc_x_kernel<<<ux, 256, 0, st>>>(b.SB, b.T2, hB, wB, wC, g.t_lo, g.t_hi, pl->uw));
+      LLIE_LAUNCH(ctx, st, "up_bc_y_kernel", up_bc_y_kernel<<<uy, 256, 0, st>>>(b.T2, sc, hB, hC, wC, g.s_lo, g.s_hi, pl->uw));
+    }
+  }
+  const ImgView v = make_view(LLIE_NHWC, 3, g.R1 - g.R0, W);
+  const bool vec = (W % 4 == 0) && ((reinterpret_cast<uintptr_t>(in[d]) | reinterpret_cast<uintptr_t>(out[d])) % 16 == 0);
+  return final_passes(ctx, st, pl, p, in[d], out[d], v, vec, true, 1, g.R1 - g.R0, W, g.R0, g.R0, g.R1, hC, wC, b.SC, c_elems,
+                      nullptr);
+}
+
+// Reusable rendezvous of the per-device host threads.
+struct HostBarrier {
+  std::mutex mu;
+  std::condition_variable cv;
+  int n, waiting = 0, generation = 0;
+  explicit HostBarrier(int n_) : n(n_) {}
+  void wait() {
+    std::unique_lock<std::mutex> lk(mu);
+    const int gen = generation;
+    if (++waiting == n) { waiting = 0; ++generation; cv.notify_all(); }
+    else cv.wait(lk, [&] { return gen != generation; });
+  }
+};
+
+}  // namespace
+
+int msrcr_tiled_run(llie_ctx* const* ctxs, int n_dev, const float* const* in, float* const* out, const int* row0,
+                    const int* rows, int H, int W, const llie_msrcr_params& p) {
+  LLIE_REQUIRE(p.n_scales <= 3, LLIE_E_ARG, "row-tiled MSRCR supports at most 3 scales (got %d)", p.n_scales);
+  // plans (pure functions of the params) first, on the calling thread, so that errors surface here
+  int r0_max = 0, rb_max = 0;
+  bool any_b = false;
+  for (int k = 0; k < p.n_scales; ++k) {
+    ScalePlan sp;
+    LLIE_TRY(get_scale_plan(p.sigma[k], p.truncate, &sp));
+    if (sp.level) { rb_max = std::max(rb_max, sp.radius_low); any_b = true; }
+    else r0_max = std::max(r0_max, sp.radius_low);
+  }
+  const int hC = level_c_size(H), wC = level_c_size(W), hB = level_b_size(H), wB = level_b_size(W);
+  const int RW = 3 * W;
+  std::vector<TileGeom> geo(n_dev);
+  for (int d = 0; d < n_dev; ++d) geo[d] = tile_geometry(d, n_dev, row0, rows, H, r0_max, rb_max, any_b);
+  std::vector<TileBufs> bufs(n_dev);
+  std::vector<cudaEvent_t> ev_c(n_dev, nullptr);
+  std::vector<int> rc(n_dev, LLIE_OK);
+  std::vector<std::string> msg(n_dev);
+  HostBarrier bar(n_dev);
+
+  // One host thread per device: launch latency of ~25 operations per device must not serialise.
+  auto worker = [&](int d) {
+    llie_ctx* ctx = ctxs[d];
+    auto body_a = [&]() -> int {
+      LLIE_CUDA_OK(cudaSetDevice(ctx->device));
+      LLIE_TRY(ensure_plan(ctx, p, ctx->stream));
+      TileBufs& b = bufs[d];
+      const size_t c_bytes = (size_t)3 * hC * wC * 4, b_bytes = (size_t)3 * hB * wB * 4;
+      void* q;
+      LLIE_TRY(ctx->workspace("tile.V", (size_t)hC * RW * 4, &q)); b.V = (float*)q;
+      LLIE_TRY(ctx->workspace("tile.C", c_bytes, &q)); b.C = (float*)q;
+      LLIE_TRY(ctx->workspace("tile.Ct", c_bytes, &q)); b.Ct = (float*)q;
+      LLIE_TRY(ctx->workspace("tile.SC", c_bytes * 3, &q)); b.SC = (float*)q;
+      LLIE_TRY(ctx->workspace("tile.TB", (size_t)3 * hC * wB * 4, &q)); b.TB = (float*)q;
+      LLIE_TRY(ctx->workspace("tile.B", b_bytes, &q)); b.B = (float*)q;
+      LLIE_TRY(ctx->workspace("tile.Bt", b_bytes, &q)); b.Bt = (float*)q;
+      LLIE_TRY(ctx->workspace("tile.SB", b_bytes, &q)); b.SB = (float*)q;
+      LLIE_TRY(ctx->workspace("tile.T2", (size_t)3 * hB * wC * 4, &q)); b.T2 = (float*)q;
+      LLIE_TRY(ctx->workspace("tile.band_top", (size_t)kBandTopRows * RW * 4, &q)); b.band_top = (float*)q;
+      LLIE_TRY(ctx->workspace("tile.band_bot", (size_t)kBandBotRows * RW * 4, &q)); b.band_bot = (float*)q;
+      if (!ctx->tile_event) LLIE_CUDA_OK(cudaEventCreateWithFlags(&ctx->tile_event, cudaEventDisableTiming));
+      ev_c[d] = ctx->tile_event;
+      LLIE_TRY(tiled_phase_a(ctx, d, n_dev, ctxs, in, rows, geo[d], b, H, W, p));
+      LLIE_CUDA_OK(cudaEventRecord(ev_c[d], ctx->stream));
+      return LLIE_OK;
+    };
+    rc[d] = body_a();
+    if (rc[d] != LLIE_OK) msg[d] = llie_last_error();
+    bar.wait();  // every device's C-ready event is recorded (or its phase failed)
+    bool all_ok = true;
+    for (int e = 0; e < n_dev; ++e) all_ok = all_ok && rc[e] == LLIE_OK;
+    bar.wait();  // rc[] is read by everyone before anyone writes it again
+    if (all_ok) {
+      rc[d] = tiled_phase_b(ctx, d, n_dev, ctxs, in, out, geo, bufs, ev_c, H, W, p);
+      if (rc[d] != LLIE_OK) msg[d] = llie_last_error();
+    }
+    cudaError_t e = cudaStreamSynchronize(ctx->stream);
+    if (e != cudaSuccess && rc[d] == LLIE_OK) {
+      rc[d] = LLIE_E_CUDA;
+      msg[d] = std::string("tiled MSRCR: device ") + std::to_string(ctx->device) + ": " + cudaGetErrorString(e);
+    }
+    bar.wait();  // nobody frees / reuses a C buffer a neighbour may still be copying from
+  };
+  int prev_dev = 0;
+  cudaGetDevice(&prev_dev);
+  std::vector<std::thread> th;
+  for (int d = 1; d < n_dev; ++d) th.emplace_back(worker, d);
+  worker(0);
+  for (auto& t : th) t.join();
+  cudaSetDevice(prev_dev);
+  for (int d = 0; d < n_dev; ++d)
+    if (rc[d] != LLIE_OK) {
+      set_error("%s", msg[d].c_str());
+      return rc[d];
+    }
   return LLIE_OK;
 }
 

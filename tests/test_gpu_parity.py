@@ -314,3 +314,63 @@ def test_no_allocation_after_warmup(blob):
         before, l0 = e.workspace_bytes(), e.launch_count()
         L.enhance(x, method, p)
         assert e.workspace_bytes() == before and e.launch_count() > l0
+
+
+# ---------------------------------------------------------------- row-tiled MSRCR (config 5) ---
+def _run_tiled(x, parts, params=None):
+    """Split x (H,W,3) into `parts` row shards on cuda:0 ("virtual devices") and run msrcr_tiled."""
+    h = x.shape[0]
+    xd = torch.from_numpy(x).cuda()
+    shards = [xd[r0:r0 + r].contiguous() for r0, r in L.tile_rows(h, parts)]
+    outs = L.msrcr_tiled(shards, params)
+    return torch.cat(outs, 0).cpu().numpy()
+
+
+@pytest.mark.parametrize("parts", [1, 2, 3, 8])
+def test_msrcr_tiled_equals_single_device(parts):
+    """Seam equality: the g-way row-tiled result equals the 1-way result.  The
+    sigma=250 reach (~1200 rows) exceeds the shard height, so C rows are gathered over several hops."""
+    x = oracle.synth_lowlight(1000, 720, 11)
+    ref = L.enhance(torch.from_numpy(x).cuda(), "msrcr").cpu().numpy()
+    y = _run_tiled(x, parts)
+    assert y.shape == ref.shape
+    assert np.abs(y - ref).max() <= 1e-6, (parts, float(np.abs(y - ref).max()))
+
+
+def test_msrcr_tiled_vs_oracle_and_odd_sizes():
+    """Tiled path against the oracle itself, on a size with ragged width / last shard."""
+    x = oracle.synth_lowlight(777, 501, 12)
+    ref = oracle.msrcr(x, mode="fft")
+    for parts in (2, 5):
+        assert np.abs(_run_tiled(x, parts) - ref).max() <= TOL_F32, parts
+    p = dict(sigmas=(20.0, 60.0), weights=(0.4, 0.6), gain=0.5, offset=120.0)
+    ref = oracle.msrcr(x, p, mode="fft")
+    assert np.abs(_run_tiled(x, 3, p) - ref).max() <= TOL_F32
+
+
+def test_msrcr_tiled_large_seams_windowed_oracle():
+    """8 shards of a 4096 x 1024 image: windows straddling every seam row against the windowed oracle."""
+    h, w = 4096, 1024
+    from low_light_image_enhancement_b200.synth import synth_lowlight_batch
+    xd = synth_lowlight_batch(1, h, w, seed=40, device="cuda")[0]
+    x = xd.cpu().numpy()
+    parts = L.tile_rows(h, 8)
+    outs = L.msrcr_tiled([xd[r0:r0 + r].contiguous() for r0, r in parts])
+    y = torch.cat(outs, 0).cpu().numpy()
+    rng = np.random.default_rng(0)
+    for r0, _ in parts[1:]:
+        x0 = int(rng.integers(0, w - 64))
+        ref = oracle.msrcr_window(x, r0 - 32, r0 + 32, x0, x0 + 64)
+        assert np.abs(y[r0 - 32:r0 + 32, x0:x0 + 64] - ref).max() <= TOL_F32, r0
+
+
+def test_msrcr_tiled_rejects_bad_partitions():
+    xd = torch.rand(256, 64, 3, device="cuda")
+    with pytest.raises(L.LlieError):   # interior boundary not a multiple of 4
+        L.msrcr_tiled([xd[:130].contiguous(), xd[130:].contiguous()])
+    with pytest.raises(L.LlieError):   # shard shorter than 64 rows
+        L.msrcr_tiled([xd[:40].contiguous(), xd[40:].contiguous()])
+    with pytest.raises(L.LlieError):   # direct blur is not available row-tiled
+        L.msrcr_tiled([xd[:128].contiguous(), xd[128:].contiguous()], dict(blur="direct"))
+    with pytest.raises(TypeError):
+        L.msrcr_tiled([xd[:128].cpu(), xd[128:].cpu()])
