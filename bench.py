@@ -11,6 +11,9 @@ Rank 0 prints ONE JSON line.  Workloads (BASELINE.json configs[i] -> "ci"):
   c3           MSRCR sigma 15/80/250 on 3840x2160 frames, 32 frames per GPU (weak scaling)
   c1           Zero-DCE fp32, 1 x 1920x1080 (replicas only for N > 1)
   c0           MSRCR on one 600x400 image (the oracle's own CPU-runnable case)
+  c4           MSRCR on ONE 16384x16384 image row-tiled over the N GPUs (strong scaling); rank 0 drives
+               all N devices through llie_msrcr_tiled (peer-to-peer halo copies, no NCCL), the other
+               ranks idle on a host-side wait
 The default line is c2 and carries short c3/c1 measurements under "also".
 
 Keys beyond the base contract: "roofline" (dominant kernel, CUDA-event time per launch measured
@@ -306,6 +309,65 @@ def gpu_workload(dist, name, steps, warmup, peaks, with_e2e=True, with_cpu=True)
     return res
 
 
+def c4_workload(dist, steps, warmup, peaks):
+    """BASELINE configs[4]: one 16384 x 16384 image, rows tiled over the N GPUs of this node, image
+    pre-sharded in HBM, halo exchange inside the timed region.  Time per step = max over devices of
+    the device-side span (CUDA events on each shard's stream after a common host barrier)."""
+    import torch
+    import low_light_image_enhancement_b200 as L
+    from low_light_image_enhancement_b200.api import msrcr_tiled_last_ms, _tile_enhancer
+    from low_light_image_enhancement_b200.synth import synth_lowlight_batch
+    H = W = 16384
+    world, rank = dist.world, dist.rank
+    store = None
+    if world > 1:
+        from torch.distributed.distributed_c10d import _get_default_store
+        store = _get_default_store()
+    res = None
+    if rank == 0:
+        parts = L.tile_rows(H, world)
+        shards, outs = [], []
+        for d, (r0, r) in enumerate(parts):
+            # built in 2048-row bands to bound the generator's temporaries
+            bands = [synth_lowlight_batch(1, min(2048, r - b0), W, seed=4000 + 97 * d + b0, device=torch.device("cuda", d))[0]
+                     for b0 in range(0, r, 2048)]
+            shards.append(torch.cat(bands, 0).contiguous())
+            outs.append(torch.empty_like(shards[-1]))
+        for _ in range(warmup):
+            L.msrcr_tiled(shards, outs=outs)
+        enh = [_tile_enhancer(d, 0) for d in range(world)]
+        l0 = sum(e.launch_count() for e in enh)
+        per_dev, wall = [], []
+        with ClockSampler(0) as clk:
+            for _ in range(steps):
+                t0 = time.perf_counter()
+                L.msrcr_tiled(shards, outs=outs)
+                wall.append((time.perf_counter() - t0) * 1e3)
+                per_dev.append(msrcr_tiled_last_ms(shards))
+        launches = sum(e.launch_count() for e in enh) - l0
+        ms = float(np.mean([max(p) for p in per_dev]))
+        px = H * W
+        ach = MSRCR_NORTH_STAR_BYTES_PER_PX * px / (ms * 1e-3) / 1e9
+        ok = all(bool(torch.isfinite(o[::512, ::64]).all()) and 0.0 <= float(o[::512, ::64].min()) for o in outs)
+        res = {"workload": f"MSRCR sigma=15/80/250, one 16384x16384 image row-tiled over {world} GPU(s) (BASELINE configs[4])",
+               "ms_per_step": round(ms, 4), "value": round(px / ms / 1e3, 1), "scaling": "strong", "dtype": "f32",
+               "frames_total": 1, "frames_this_rank": 1, "clocks": clk.summary(), "gpu_launches": int(launches),
+               "l2": "3.2 GB image per step exceeds the 126 MB L2",
+               "host_wall_ms_per_step": round(float(np.mean(wall)), 3),
+               "per_device_ms": [round(float(np.mean([p[d] for p in per_dev])), 4) for d in range(world)],
+               "output_sane": ok,
+               "roofline": {"bound": "hbm", "kernel": "whole tiled MSRCR (all devices)", "achieved": round(ach, 1),
+                            "peak": round(peaks["hbm"] * world, 1), "unit": "GB/s", "frac": round(ach / (peaks["hbm"] * world), 4),
+                            "traffic": None, "peak_source": f"{peaks['source']} copy x {world} GPUs",
+                            "bytes_per_px": MSRCR_NORTH_STAR_BYTES_PER_PX,
+                            "exchange": "16 raw rows + level-C (stride-4) rows per neighbour via cudaMemcpyPeerAsync"}}
+        if store is not None:
+            store.set("c4_done", "1")
+    elif store is not None:
+        store.wait(["c4_done"])
+    return res
+
+
 # ------------------------------------------------------------------ CPU oracle legs ----------
 def _oracle_step(name, frame_hwc, params, rows):
     """One bounded CPU sample: the NumPy oracle on the top `rows` rows of one frame."""
@@ -323,12 +385,13 @@ def _oracle_step(name, frame_hwc, params, rows):
 
 def _oracle_rows(name):
     # about 10-30 s of CPU work per sample on ~8 cores (measured in the build container)
-    return {"c2": 270, "c1": 270, "c3": 2160, "c0": 400}[name]
+    return {"c2": 270, "c1": 270, "c3": 2160, "c0": 400, "c4": 2160}[name]
 
 
 def _oracle_desc(name):
     return {"c2": "fp64 NumPy im2col+BLAS DCE-Net + curves", "c1": "fp64 NumPy im2col+BLAS DCE-Net + curves",
-            "c3": "fp64 NumPy MSRCR, scipy.fft surround (all cores)", "c0": "fp64 NumPy MSRCR, direct FIR (definition)"}[name]
+            "c3": "fp64 NumPy MSRCR, scipy.fft surround (all cores)", "c0": "fp64 NumPy MSRCR, direct FIR (definition)",
+            "c4": "fp64 NumPy MSRCR, scipy.fft surround (all cores) on a 3840-px-wide crop of the 16384^2 image (extrapolated)"}[name]
 
 
 def cpu_baseline(name, frame_hwc, params):
@@ -351,7 +414,7 @@ def reference_arm(args):
         return
     import oracle
     name = args.workload
-    h, w = {"c2": (H1080, W1080), "c1": (H1080, W1080), "c3": (H4K, W4K), "c0": (400, 600)}[name]
+    h, w = {"c2": (H1080, W1080), "c1": (H1080, W1080), "c3": (H4K, W4K), "c0": (400, 600), "c4": (H4K, W4K)}[name]
     rows = min(_oracle_rows(name), h)
     frame = oracle.synth_lowlight(rows, w, seed=1000 * int(name[1]))
     params = dict(weights=oracle.pack_weights(oracle.init_weights(0))) if name in ("c1", "c2") else None
@@ -373,7 +436,7 @@ def reference_arm(args):
     sample = f"top {rows} rows x {w} px of one synthetic frame per step, {_oracle_desc(name)}"
     line = {"impl": "reference", "metric": "Mpixel/s", "value": val, "unit": "Mpixel/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(dt * 1e3 / args.steps, 2),
-            "higher_is_better": True, "scaling": "strong" if name == "c2" else "weak", "vs_baseline": None,
+            "higher_is_better": True, "scaling": "strong" if name in ("c2", "c4") else "weak", "vs_baseline": None,
             "dtype": "f64", "data": "synthetic", "config": {"workload": workload_label(name, args.gpus)},
             "cpu_baseline": {"value": val, "unit": "Mpixel/s", "cores": os.cpu_count(), "kind": "port", "sample": sample},
             "e2e": {"value": val, "unit": "Mpixel/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -386,7 +449,8 @@ def workload_label(name, world):
     return {"c2": f"Zero-DCE bf16, {C2_TOTAL_FRAMES} x 1920x1080 sharded over {world} GPU(s) (BASELINE configs[2])",
             "c3": f"MSRCR sigma=15/80/250, 3840x2160, {C3_FRAMES_PER_GPU} frames per GPU (BASELINE configs[3])",
             "c1": "Zero-DCE fp32, 1 x 1920x1080 per GPU (BASELINE configs[1]; replicas only)",
-            "c0": "MSRCR sigma=15/80/250, one 600x400 image per GPU (BASELINE configs[0]; replicas only)"}[name]
+            "c0": "MSRCR sigma=15/80/250, one 600x400 image per GPU (BASELINE configs[0]; replicas only)",
+            "c4": f"MSRCR sigma=15/80/250, one 16384x16384 image row-tiled over {world} GPU(s) (BASELINE configs[4])"}[name]
 
 
 def main():
@@ -394,7 +458,7 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--workload", default="c2", choices=["c0", "c1", "c2", "c3"])
+    ap.add_argument("--workload", default="c2", choices=["c0", "c1", "c2", "c3", "c4"])
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-also", action="store_true", help="skip the short secondary workloads")
     ap.add_argument("--no-e2e", action="store_true")
@@ -406,6 +470,19 @@ def main():
         return
     peaks = load_peaks()
     dist = Dist(args.gpus)
+    if args.workload == "c4":
+        main_res = c4_workload(dist, args.steps, args.warmup, peaks)
+        if dist.rank == 0:
+            line = {"metric": "Mpixel/s", "value": main_res["value"], "unit": "Mpixel/s", "n_gpus": dist.world,
+                    "steps": args.steps, "warmup": args.warmup, "ms_per_step": main_res["ms_per_step"],
+                    "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
+                    "data": "synthetic (device-generated low-light image, pre-sharded in HBM)",
+                    "config": {"workload": main_res["workload"], "l2": main_res["l2"], "peaks": peaks},
+                    "roofline": main_res["roofline"], "clocks": main_res["clocks"], "gpu_launches": main_res["gpu_launches"],
+                    "detail": {k: main_res[k] for k in ("host_wall_ms_per_step", "per_device_ms", "output_sane")}}
+            print(json.dumps(line), flush=True)
+        dist.close()
+        return
     main_res = gpu_workload(dist, args.workload, args.steps, args.warmup, peaks, not args.no_e2e, not args.no_cpu)
     also = {}
     if not args.no_also and args.workload == "c2":

@@ -139,6 +139,11 @@ int llie_dce_curves(llie_ctx* ctx, const float* in, const float* maps, float* ou
 int llie_msrcr_tiled(llie_ctx* const* ctxs, int n_dev, const float* const* in_shard, float* const* out_shard,
                      const int* row0, const int* rows, int h_total, int w, const llie_msrcr_params* params);
 
+/* Device-side duration (CUDA events on the shard's stream, first copy to last kernel) of this ctx's
+ * shard in the last successful llie_msrcr_tiled call.  All shards start after a common host barrier,
+ * so the max over the ctxs is the multi-GPU time of the call (SURVEY.md 8(d) "timing method"). */
+int llie_msrcr_tiled_last_ms(llie_ctx* ctx, float* ms);
+
 #ifdef __cplusplus
 }
 #endif

@@ -68,6 +68,7 @@ EXPORTS = {
     "llie_dce_curves": (_I, [_VP, _VP, _VP, _VP, _I, _I, _I, _I, C.POINTER(DceParams), _VP]),
     "llie_msrcr_tiled": (_I, [C.POINTER(_VP), _I, C.POINTER(_VP), C.POINTER(_VP), C.POINTER(_I), C.POINTER(_I),
                               _I, _I, C.POINTER(MsrcrParams)]),
+    "llie_msrcr_tiled_last_ms": (_I, [_VP, C.POINTER(_F)]),
 }
 
 _lib = None

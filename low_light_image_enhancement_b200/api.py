@@ -451,6 +451,17 @@ def msrcr_tiled(shards: Sequence[torch.Tensor], params: dict | None = None, *, o
     return outs
 
 
+def msrcr_tiled_last_ms(shards: Sequence[torch.Tensor]) -> list[float]:
+    """Device-side milliseconds each shard's device spent in the last msrcr_tiled() call on these shards."""
+    devs = [t.device.index for t in shards]
+    ms = []
+    for i, dv in enumerate(devs):
+        v = C.c_float()
+        _lib.check(_lib.load().llie_msrcr_tiled_last_ms(_tile_enhancer(dv, i if len(set(devs)) == 1 else 0)._h, C.byref(v)))
+        ms.append(v.value)
+    return ms
+
+
 def enhance(images, method: str, params: dict | None = None, *, out=None, device: int | None = None):
     """Enhance a low-light image batch on a B200.
 

@@ -152,7 +152,7 @@ int llie_destroy(llie_ctx* ctx) {
   msrcr_plan_free(ctx->plan);
   dce_weights_free(ctx->dce);
   dce_tc_release(ctx);
-  if (ctx->tile_event) cudaEventDestroy(ctx->tile_event);
+  if (ctx->tile_event) { cudaEventDestroy(ctx->tile_event); cudaEventDestroy(ctx->tile_t0); cudaEventDestroy(ctx->tile_t1); }
   if (ctx->stream) cudaStreamDestroy(ctx->stream);
   delete ctx;
   return LLIE_OK;
@@ -174,6 +174,13 @@ int llie_workspace_bytes(llie_ctx* ctx, size_t* bytes) {
 int llie_launch_count(llie_ctx* ctx, uint64_t* count) {
   LLIE_REQUIRE(ctx && count, LLIE_E_ARG, "null argument");
   *count = ctx->launches;
+  return LLIE_OK;
+}
+
+int llie_msrcr_tiled_last_ms(llie_ctx* ctx, float* ms) {
+  LLIE_REQUIRE(ctx && ms, LLIE_E_ARG, "null argument");
+  LLIE_REQUIRE(ctx->tile_ms >= 0.f, LLIE_E_STATE, "no successful llie_msrcr_tiled call has used this ctx");
+  *ms = ctx->tile_ms;
   return LLIE_OK;
 }
 

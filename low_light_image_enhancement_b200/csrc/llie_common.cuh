@@ -76,6 +76,8 @@ struct llie_ctx {
   std::vector<ProfRec> prof;
   cudaEvent_t prof_pending = nullptr;
   cudaEvent_t tile_event = nullptr;  // "my level-C rows are ready" (row-tiled MSRCR)
+  cudaEvent_t tile_t0 = nullptr, tile_t1 = nullptr;  // device-side span of this shard in the last tiled call
+  float tile_ms = -1.f;
 
   // Returns a device buffer of at least `bytes` under `name`; reallocates only when growing.
   int workspace(const char* name, size_t bytes, void** out);
