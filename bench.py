@@ -133,6 +133,8 @@ class Dist:
         if self.world > 1:
             import torch.distributed as dist
             os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+            if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
+                os.environ["NCCL_DEBUG"] = "WARN"   # its banner goes to stdout, which carries the one JSON line
             dist.init_process_group("nccl", device_id=self.device)
             self.dist = dist
 
