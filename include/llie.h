@@ -127,6 +127,11 @@ int llie_dce_forward(llie_ctx* ctx, const float* in, float* out, float* maps_or_
  * SURVEY.md 9.2) of frame `frame` of the last processed chunk to HOST memory as fp32 [32][h][w]. */
 int llie_debug_dce_activation(llie_ctx* ctx, int which, int frame, float* host_out);
 
+/* Test hook for the LLIE_BF16 path: bit 0 = also write the activations that normally never leave the
+ * chip (x4, x6) so that llie_debug_dce_activation can read them; bit 1 = run one launch per layer
+ * instead of the fused conv1-3 / conv4-5 / conv6-7 chains (same kernel, for A/B measurements). */
+int llie_debug_dce_mode(llie_ctx* ctx, int mode);
+
 /* north_star kernel (3) alone: curves from given maps (N,H,W,24)/(N,24,H,W) fp32. */
 int llie_dce_curves(llie_ctx* ctx, const float* in, const float* maps, float* out, int n, int h, int w,
                     int layout, const llie_dce_params* params, void* stream);

@@ -65,6 +65,7 @@ EXPORTS = {
     "llie_dce_set_weights": (_I, [_VP, C.POINTER(_F), C.c_size_t]),
     "llie_dce_forward": (_I, [_VP, _VP, _VP, _VP, _I, _I, _I, _I, C.POINTER(DceParams), _VP]),
     "llie_debug_dce_activation": (_I, [_VP, _I, _I, C.POINTER(_F)]),
+    "llie_debug_dce_mode": (_I, [_VP, _I]),
     "llie_dce_curves": (_I, [_VP, _VP, _VP, _VP, _I, _I, _I, _I, C.POINTER(DceParams), _VP]),
     "llie_msrcr_tiled": (_I, [C.POINTER(_VP), _I, C.POINTER(_VP), C.POINTER(_VP), C.POINTER(_I), C.POINTER(_I),
                               _I, _I, C.POINTER(MsrcrParams)]),

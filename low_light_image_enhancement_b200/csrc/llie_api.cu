@@ -293,6 +293,12 @@ int llie_debug_dce_activation(llie_ctx* ctx, int which, int frame, float* host_o
   return dce_debug_activation(ctx, which, frame, host_out);
 }
 
+int llie_debug_dce_mode(llie_ctx* ctx, int mode) {
+  LLIE_REQUIRE(ctx, LLIE_E_ARG, "null ctx");
+  LLIE_REQUIRE(mode >= 0 && mode <= 3, LLIE_E_ARG, "mode %d out of range [0,3]", mode);
+  return dce_debug_mode(ctx, mode);
+}
+
 int llie_dce_curves(llie_ctx* ctx, const float* in, const float* maps, float* out, int n, int h, int w, int layout,
                     const llie_dce_params* params, void* stream) {
   LLIE_REQUIRE(ctx, LLIE_E_ARG, "null ctx");

@@ -136,6 +136,7 @@ int dce_forward_bf16(llie_ctx* ctx, const float* in, float* out, float* maps, in
                      const llie_dce_params& p, cudaStream_t st);
 void dce_tc_release(llie_ctx* ctx);
 int dce_debug_activation(llie_ctx* ctx, int which, int frame, float* host_out);
+int dce_debug_mode(llie_ctx* ctx, int mode);
 int dce_curves_run(llie_ctx* ctx, const float* in, const float* maps, ImgView maps_view, float* out, float* maps_out,
                    int n, int h, int w, int layout, const llie_dce_params& p, cudaStream_t st);
 

@@ -187,23 +187,52 @@ def test_dce_bf16_psnr(case):
         assert y.min() >= 0.0 and y.max() <= 1.0
 
 
-def test_dce_bf16_activations_match_bf16_emulation(blob):
-    """Layer-by-layer check of the tensor-core path against a NumPy emulation of bf16 storage."""
+@pytest.mark.parametrize("unfused", [False, True])
+def test_dce_bf16_activations_match_bf16_emulation(blob, unfused):
+    """Layer-by-layer check of the tensor-core path against a NumPy emulation of bf16 storage, for the
+    fused chains (conv1-3 / conv4-5 / conv6-7, x4 and x6 stored only through the test hook) and for
+    one launch per layer."""
     from bf16_emulation import dce_activations_bf16
     from low_light_image_enhancement_b200.api import _enhancer
     ws = oracle.init_weights(0)
     x = (oracle.synth_lowlight(70, 200, 5) * 6).astype(np.float32)
     acts, A = dce_activations_bf16(x, ws)
     xd = torch.from_numpy(x).cuda()
-    y, m = L.enhance(xd, "zero_dce", dict(weights=blob, precision="bf16", return_maps=True))
     e = _enhancer(xd.device.index)
-    for i in range(6):
-        g = e.debug_dce_activation(i + 1, 0, 70, 200)
-        scale = max(1.0, float(np.abs(acts[i]).max()))
-        # one bf16 ulp of disagreement where fp32 accumulation order flips a rounding
-        assert np.abs(g - acts[i]).max() <= scale * 2.0 ** -7, i
-        assert (np.abs(g - acts[i]) > scale * 2.0 ** -9).mean() < 0.02, i
-    assert np.abs(m.cpu().numpy() - A.transpose(1, 2, 0)).max() <= 2e-2
+    e.debug_dce_mode(keep_all=True, unfused=unfused)
+    try:
+        y, m = L.enhance(xd, "zero_dce", dict(weights=blob, precision="bf16", return_maps=True))
+        for i in range(6):
+            g = e.debug_dce_activation(i + 1, 0, 70, 200)
+            scale = max(1.0, float(np.abs(acts[i]).max()))
+            # one bf16 ulp of disagreement where fp32 accumulation order flips a rounding
+            assert np.abs(g - acts[i]).max() <= scale * 2.0 ** -7, i
+            assert (np.abs(g - acts[i]) > scale * 2.0 ** -9).mean() < 0.02, i
+        assert np.abs(m.cpu().numpy() - A.transpose(1, 2, 0)).max() <= 2e-2
+    finally:
+        e.debug_dce_mode()
+
+
+@pytest.mark.parametrize("shape", [(70, 200), (300, 251), (33, 700), (5, 124), (129, 125), (2, 127)])
+def test_dce_bf16_fused_equals_per_layer(blob, shape):
+    """The fused chains and the one-launch-per-layer schedule run the same arithmetic per pixel:
+    identical outputs, across strip seams (124 / 126-pixel strips) and row segments."""
+    from low_light_image_enhancement_b200.api import _enhancer
+    h, w = shape
+    x = torch.from_numpy((oracle.synth_lowlight(h, w, 21) * 4).astype(np.float32)).cuda()
+    xb = torch.stack([x, x.flip(0), x.flip(1)])
+    e = _enhancer(x.device.index)
+    p = dict(weights=blob, precision="bf16", return_maps=True)
+    try:
+        e.debug_dce_mode(unfused=True)
+        y0, m0 = L.enhance(xb, "zero_dce", p)
+        e.debug_dce_mode()
+        y1, m1 = L.enhance(xb, "zero_dce", p)
+    finally:
+        e.debug_dce_mode()
+    assert torch.equal(m0, m1) and torch.equal(y0, y1)
+    ref = oracle.zero_dce(x.cpu().numpy(), oracle.init_weights(0))
+    assert psnr(y1[0].cpu().numpy(), ref) >= PSNR_BF16
 
 
 @pytest.mark.parametrize("prec", ["fp32", "bf16"])

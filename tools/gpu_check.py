@@ -61,8 +61,9 @@ def main():
             for (h, w, seed) in ((20, 40, 4), (70, 200, 5)):
                 x = oracle.synth_lowlight(h, w, seed) * 6
                 acts, Aem = dce_activations_bf16(x, ws)
-                y, m = L.enhance(torch.from_numpy(x).cuda(), "zero_dce", dict(weights=blob, precision="bf16", return_maps=True))
                 e = _enhancer(0)
+                e.debug_dce_mode(keep_all=True, unfused="unfused" in which)
+                y, m = L.enhance(torch.from_numpy(x).cuda(), "zero_dce", dict(weights=blob, precision="bf16", return_maps=True))
                 for i in range(6):
                     g = e.debug_dce_activation(i + 1, 0, h, w)
                     d = np.abs(g - acts[i]); k = np.unravel_index(d.argmax(), d.shape)
