@@ -43,8 +43,10 @@ C2_TOTAL_FRAMES = 64
 C3_FRAMES_PER_GPU = 32
 
 # algorithmic work per pixel (DESIGN.md "Kernels")
-FLOP_PER_PX = {"dce_conv_tc_k32_kernel": 2 * 32 * 32 * 9, "dce_conv_tc_k64_kernel": 2 * 64 * 32 * 9,
-               "dce_conv_tc_last_kernel": 2 * 64 * 24 * 9}
+# algorithmic tensor-pipe FLOPs per pixel of each fused launch (conv1's padded 3->32 MMAs are not counted)
+FLOP_PER_PX = {"dce_chain_c123_kernel": 2 * (2 * 32 * 32 * 9),                       # conv2 + conv3
+               "dce_chain_c45_kernel": 2 * 32 * 32 * 9 + 2 * 64 * 32 * 9,             # conv4 + conv5
+               "dce_chain_c67_kernel": 2 * 64 * 32 * 9 + 2 * 64 * 24 * 9}             # conv6 + conv7
 DCE_TENSOR_FLOP_PER_PX = 156672          # conv2..conv7
 MSRCR_NORTH_STAR_BYTES_PER_PX = 108      # two-pass separable data flow
 # per-kernel algorithmic HBM bytes per full-resolution pixel of the decimated cascade (DESIGN.md "Kernels"):
@@ -215,8 +217,7 @@ def tc_roofline(prof, px_per_step, steps, peaks):
     if not tc:
         return None
     dom = max(tc, key=lambda k: tc[k][1])
-    n_dom = {"dce_conv_tc_k32_kernel": 3, "dce_conv_tc_k64_kernel": 2, "dce_conv_tc_last_kernel": 1}[dom]
-    flops_dom = FLOP_PER_PX[dom] * n_dom * px_per_step * steps          # all launches of that kernel
+    flops_dom = FLOP_PER_PX[dom] * px_per_step * steps                  # all launches of that kernel
     ach = flops_dom / (tc[dom][1] * 1e-3) / 1e12
     chain_ms = sum(v[1] for v in tc.values())
     chain = DCE_TENSOR_FLOP_PER_PX * px_per_step * steps / (chain_ms * 1e-3) / 1e12

@@ -13,9 +13,10 @@
 // of the last stage's output.  Rows outside the image are skipped, columns outside are written as
 // zeros (the convolution's zero padding applies to every layer's INPUT).
 //
-// Warps: s < S = MMA issuer of stage s (a single thread issuing for three stages was the bottleneck:
-// ~7 cycles per instruction on one warp), S..3 = bulk-copy producers (one per external input ring),
-// 4.. = one epilogue group of four warps per stage (warp & 3 = TMEM lane quadrant).  Stages are
+// Warps: s < S = the MMA issuer of stage s (one issuing thread per stage: the accumulation order,
+// hence the result, is deterministic), S..3 = bulk-copy producers (one per external input ring),
+// 4.. = two epilogue groups of four warps per stage, alternating output rows (warp & 3 = TMEM lane
+// quadrant).  Stages are
 // ordered against each other only through the ring / accumulator mbarriers.
 #pragma once
 #include "llie_common.cuh"
@@ -111,12 +112,13 @@ __host__ __device__ constexpr int producer_index(const Group& g, int s, int j) {
   return o;
 }
 __host__ __device__ constexpr int valid_px(const Group& g) { return kTileX - 2 * (g.S - 1); }
-__host__ __device__ constexpr int n_threads(const Group& g) { return (kFirstEpiWarp + 4 * g.S) * 32; }
+constexpr int kEpiGroups = 2;             // epilogue groups per stage; they alternate output rows
+__host__ __device__ constexpr int n_threads(const Group& g) { return (kFirstEpiWarp + 4 * kEpiGroups * g.S) * 32; }
 
 struct ChainArgs {
   const __nv_bfloat16* ext[kMaxStages][2][2];  // [stage][src][tensor]: HBM inputs of external rings
   const __nv_bfloat16* wpk[kMaxStages];        // weight tiles of each stage
-  const float* bias[kMaxStages];               // 32 floats each
+  float bias[kMaxStages][32];                  // per stage; read as constant-bank operands by the epilogues
   __nv_bfloat16* out[kMaxStages];              // HBM destination of a stage's activation, or nullptr
   const float* x;                              // last stage: the caller's image / output / optional maps
   float* y;
@@ -267,7 +269,7 @@ __device__ __forceinline__ void producer_loop(const ChainArgs& a, const Smem<GID
 struct IssueState { uint32_t ocnt[kMaxStages]; uint32_t rcnt[kMaxStages]; };
 
 template <int GID, int S_>
-__device__ __forceinline__ void issue_row(const Smem<GID>& sm, uint32_t tmem, uint32_t ocnt, uint32_t rcnt,
+__device__ __forceinline__ void issue_row(const Smem<GID>& sm, uint32_t tmem, uint32_t ocnt, uint32_t rc,
                                           const StageRows& sr, int r) {
   constexpr Group G = group_cfg(GID);
   constexpr Stage T = G.st[S_];
@@ -283,12 +285,11 @@ __device__ __forceinline__ void issue_row(const Smem<GID>& sm, uint32_t tmem, ui
   const int lo = max(rr - 1, 0), hi = min(rr + 1, rows - 1);     // relative output rows it contributes to
   uint64_t* acc_free = sm.template acc_free<S_>();
   uint64_t* acc_ready = sm.template acc_ready<S_>();
-  // slots touched for the first time must have been drained and re-initialised with the bias
+  // slots touched for the first time must have been drained and re-zeroed since their previous use
   for (int o = (r == sr.in_lo) ? lo : rr + 1; o <= hi; ++o) {
     const uint32_t og = ocnt + o;
     mbar_wait(&acc_free[og % NS], (og / NS) & 1);
   }
-  const uint32_t rc = rcnt + (uint32_t)(r - sr.in_lo);
   const uint32_t slot0 = rc % kD0, slot1 = rc % kD1;
   mbar_wait(&sm.template ring_full<S_, 0>()[slot0], (rc / kD0) & 1);
   if constexpr (kNsrc > 1) mbar_wait(&sm.template ring_full<S_, (kNsrc > 1 ? 1 : 0)>()[slot1], (rc / kD1) & 1);
@@ -337,7 +338,7 @@ __device__ __forceinline__ void issue_row(const Smem<GID>& sm, uint32_t tmem, ui
 
 // ---- epilogue of stage S_: four warps, one TMEM lane quadrant each ---------------------------------
 template <int GID, int S_>
-__device__ __forceinline__ void epilogue_loop(const ChainArgs& a, const Smem<GID>& sm, uint32_t tmem, int q, int lane) {
+__device__ __forceinline__ void epilogue_loop(const ChainArgs& a, const Smem<GID>& sm, uint32_t tmem, int g, int q, int lane) {
   constexpr Group G = group_cfg(GID);
   constexpr int L = G.S - 1, NS = G.slots;
   constexpr bool kLast = G.st[S_].last != 0;
@@ -350,15 +351,16 @@ __device__ __forceinline__ void epilogue_loop(const ChainArgs& a, const Smem<GID
   uint64_t* acc_free = sm.template acc_free<S_>();
   const uint32_t lane_base = (uint32_t)(q * 32) << 16;
   const uint32_t tcol = tmem + lane_base + S_ * NS * 32;
-  uint32_t bias_u[32];
-#pragma unroll
-  for (int j = 0; j < 32; ++j) bias_u[j] = __float_as_uint(__ldg(a.bias[S_] + j));
-  for (int s = 0; s < NS; ++s) tmem_st32(tcol + s * 32, bias_u);
-  tmem_wait_st();
-  tc_fence_before();
-  __syncwarp();
-  if (lane == 0)
-    for (int s = 0; s < NS; ++s) mbar_arrive(&acc_free[s]);
+  // Accumulator slots start from zero (the bias is added below, from the constant bank); a drained
+  // slot is re-zeroed with a single-register tcgen05.st.  Group 0 initialises every slot once.
+  if (g == 0) {
+    for (int s = 0; s < NS; ++s) tmem_fill32(tcol + s * 32, 0u);
+    tmem_wait_st();
+    tc_fence_before();
+    __syncwarp();
+    if (lane == 0)
+      for (int s = 0; s < NS; ++s) mbar_arrive(&acc_free[s]);
+  }
   const int m = q * 32 + lane;  // this thread's pixel of the 128-pixel tile
   uint32_t ocnt = 0;            // running output-row counter (same sequence as the issuer's)
   for (int u = blockIdx.x; u < a.units; u += gridDim.x) {
@@ -369,7 +371,7 @@ __device__ __forceinline__ void epilogue_loop(const ChainArgs& a, const Smem<GID
     // the strip owns kValid columns of the last stage's output; earlier stages own the same columns
     const bool owned = in_img && m >= (L - S_) && m < (L - S_) + kValid;
     const int rows = sr.ye - sr.ys;
-    for (int i = 0; i < rows; ++i) {
+    for (int i = (g ^ ocnt) & 1; i < rows; i += 2) {  // group g owns the output rows with (counter & 1) == g
       const uint32_t og = ocnt + i;
       const int y = sr.ys + i, s = og % NS;
       mbar_wait(&acc_ready[s], (og / NS) & 1);
@@ -377,11 +379,13 @@ __device__ __forceinline__ void epilogue_loop(const ChainArgs& a, const Smem<GID
       uint32_t v[32];
       tmem_ld32(tcol + s * 32, v);
       tmem_wait_ld();
-      tmem_st32(tcol + s * 32, bias_u);
+      tmem_fill32(tcol + s * 32, 0u);
       tmem_wait_st();
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&acc_free[s]);
+#pragma unroll
+      for (int j = 0; j < 32; ++j) v[j] = __float_as_uint(__uint_as_float(v[j]) + a.bias[S_][j]);
       if constexpr (!kLast) {
         uint4 o[4];
 #pragma unroll
@@ -483,7 +487,8 @@ __global__ void __launch_bounds__(n_threads(group_cfg(GID)), 1) dce_chain_kernel
   const uint32_t tmem = *sm.tmem_ptr();
 
   if (warp < kS) {
-    // ---------------- MMA issuers: warp s issues stage s (its own barriers order it against the others) --------
+    // ---------------- MMA issuers: warp s issues stage s; stages are ordered only through the mbarriers -------
+    // (ONE issuing thread per stage keeps the fp32 accumulation order, hence the result, deterministic)
     if (warp == 0) {
       if (elect_one()) {
         constexpr uint32_t wbytes = w_offset(group_cfg(GID), group_cfg(GID).S);
@@ -503,9 +508,8 @@ __global__ void __launch_bounds__(n_threads(group_cfg(GID)), 1) dce_chain_kernel
         for (int u = blockIdx.x; u < a.units; u += gridDim.x) {
           const Unit un = decode_unit(a, u);
           const StageRows sr = stage_rows(un.ys, un.ye, a.H, L, s);
-          for (int r = sr.in_lo; r < sr.in_hi; ++r) issue_row<GID, s>(sm, tmem, oc, rc, sr, r);
+          for (int r = sr.in_lo; r < sr.in_hi; ++r, ++rc) issue_row<GID, s>(sm, tmem, oc, rc, sr, r);
           oc += sr.ye - sr.ys;
-          rc += sr.in_hi - sr.in_lo;
         }
       }
     });
@@ -525,7 +529,7 @@ __global__ void __launch_bounds__(n_threads(group_cfg(GID)), 1) dce_chain_kernel
     const int grp = (warp - kFirstEpiWarp) >> 2, q = warp & 3;
     for_each_stage<GID>([&](auto S) {
       constexpr int s = decltype(S)::value;
-      if (grp == s) epilogue_loop<GID, s>(a, sm, tmem, q, lane);
+      if (grp / kEpiGroups == s) epilogue_loop<GID, s>(a, sm, tmem, grp % kEpiGroups, q, lane);
     });
   }
   tc_fence_before();

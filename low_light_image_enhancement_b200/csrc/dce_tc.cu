@@ -75,7 +75,7 @@ int launch_chain(llie_ctx* ctx, cudaStream_t st, ChainArgs a, const char* name) 
 // dx=1), tile 1 = (dx=2 | zeros) -- each half holding the 3 input channels + 5 zero channels.
 struct DceTcPack {
   size_t tile_off[7];  // element offsets into d_bf16 (layers 0..6)
-  float* d_bias = nullptr;  // 7 x 32
+  float h_bias[7 * 32] = {0};  // per layer, host copy (passed to the kernels by value)
   // geometry of the activation workspace of the last forward (for the debug hook / pad zeroing)
   int n = 0, h = 0, w = 0, wp = 0;
   __nv_bfloat16* xin = nullptr;  // packed input [n][h][wp][8]
@@ -87,11 +87,10 @@ static std::map<llie_ctx*, DceTcPack> g_packs;  // keyed by ctx (ctx is single-t
 
 int dce_pack_bf16(llie_ctx* ctx, DceWeights* dw) {
   DceTcPack& pk = g_packs[ctx];
-  cudaFree(pk.d_bias);
-  pk.d_bias = nullptr;
   const float* raw = dw->host_raw.data();
   std::vector<__nv_bfloat16> tiles;
-  std::vector<float> biases(7 * 32, 0.f);
+  float* biases = pk.h_bias;
+  memset(biases, 0, sizeof(pk.h_bias));
   size_t src = 0;
   for (int l = 0; l < 7; ++l) {
     const int co = kCout[l], ci = kCin[l];
@@ -130,15 +129,12 @@ int dce_pack_bf16(llie_ctx* ctx, DceWeights* dw) {
   }
   LLIE_CUDA_OK(cudaMalloc(&dw->d_bf16, tiles.size() * sizeof(__nv_bfloat16)));
   LLIE_CUDA_OK(cudaMemcpy(dw->d_bf16, tiles.data(), tiles.size() * sizeof(__nv_bfloat16), cudaMemcpyHostToDevice));
-  LLIE_CUDA_OK(cudaMalloc(&pk.d_bias, biases.size() * sizeof(float)));
-  LLIE_CUDA_OK(cudaMemcpy(pk.d_bias, biases.data(), biases.size() * sizeof(float), cudaMemcpyHostToDevice));
   return LLIE_OK;
 }
 
 void dce_tc_release(llie_ctx* ctx) {
   auto it = g_packs.find(ctx);
   if (it == g_packs.end()) return;
-  cudaFree(it->second.d_bias);
   g_packs.erase(it);
 }
 
@@ -185,7 +181,7 @@ int dce_forward_bf16(llie_ctx* ctx, const float* in, float* out, float* maps, in
     // stage slot <- layer l (0..6): weights, bias, HBM destination (nullptr = keep on chip)
     auto stage = [&](int slot, int l, __nv_bfloat16* o) {
       a.wpk[slot] = dw->d_bf16 + pk.tile_off[l];
-      a.bias[slot] = pk.d_bias + l * 32;
+      memcpy(a.bias[slot], pk.h_bias + l * 32, 32 * sizeof(float));
       a.out[slot] = o;
     };
     __nv_bfloat16 *x1 = pk.act[0], *x2 = pk.act[1], *x3 = pk.act[2], *x4 = pk.act[3], *x5 = pk.act[4], *x6 = pk.act[5];

@@ -1,0 +1,71 @@
+// Micro-probe (B200): cycles per tcgen05.mma (M=128, K=16, bf16, SS) as a function of N, of whether
+// consecutive MMAs accumulate into the same TMEM columns, and of the shared-memory layout.
+// Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -o tools/probes/mma_probe.bin tools/probes/mma_probe.cu
+#include <cstdio>
+#include <cstdint>
+#include <cuda_runtime.h>
+#include "../../low_light_image_enhancement_b200/csrc/sm100_ptx.cuh"
+using namespace llie::ptx;
+
+// mode bit0: alternate between two accumulators; bit1: 4 accumulators round-robin
+__global__ void probe(int n, int iters, int mode, int a_stride16, int b_bytes_step, long long* out) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  __shared__ uint64_t bar;
+  __shared__ uint32_t tm;
+  for (int i = threadIdx.x; i < 160 * 1024 / 4; i += blockDim.x) reinterpret_cast<uint32_t*>(smem)[i] = 0;
+  if (threadIdx.x == 0) { mbar_init(&bar, 1); fence_barrier_init(); }
+  if (threadIdx.x < 32) { tmem_alloc(&tm, 512); tmem_relinquish(); }
+  asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");
+  tc_fence_before(); __syncthreads(); tc_fence_after();
+  const uint32_t tmem = tm;
+  if (threadIdx.x < 32) {
+    long long t0 = 0, t1 = 0;
+    if (elect_one()) {
+      const uint64_t a0 = smem_desc(smem_u32(smem), 2112, 128);
+      const uint64_t b0 = smem_desc(smem_u32(smem + 96 * 1024), 1536, 128);
+      const uint32_t idesc = idesc_bf16_m128(n);
+      const int nacc = (mode & 2) ? 4 : ((mode & 1) ? 2 : 1);
+      t0 = clock64();
+      for (int i = 0; i < iters; ++i) {
+        const uint32_t d = tmem + (i % nacc) * 128;
+        const uint64_t ad = a0 + (uint64_t)((i % 6) * a_stride16);
+        const uint64_t bd = b0 + (uint64_t)(((i % 6) * b_bytes_step) >> 4);
+        mma_bf16_ss(d, ad, bd, idesc, 1u);
+      }
+      mma_commit(&bar);
+    }
+    __syncwarp();
+    mbar_wait(&bar, 0);
+    t1 = clock64();
+    if (threadIdx.x == 0) out[blockIdx.x] = t1 - t0;
+  }
+  tc_fence_before(); __syncthreads();
+  if (threadIdx.x < 32) tmem_dealloc(tmem, 512);
+}
+
+int main() {
+  long long* d; cudaMalloc(&d, 148 * 8);
+  cudaFuncSetAttribute(probe, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
+  const int iters = 4096;
+  struct Cfg { int n, mode, a16, bstep; const char* what; };
+  Cfg cfgs[] = {
+      {96, 0, 1, 3072, "N=96 same D (as the conv kernel)"}, {96, 1, 1, 3072, "N=96 two D alternating"},
+      {96, 2, 1, 3072, "N=96 four D round-robin"},          {32, 0, 1, 3072, "N=32 same D"},
+      {32, 2, 1, 3072, "N=32 four D"},                      {128, 0, 1, 3072, "N=128 same D"},
+      {128, 2, 1, 3072, "N=128 four D"},                    {256, 0, 1, 0, "N=256 same D"},
+      {256, 1, 1, 0, "N=256 two D"},                        {96, 0, 0, 0, "N=96 same D, same operands"},
+      {96, 2, 0, 0, "N=96 four D, same operands"},          {64, 0, 1, 3072, "N=64 same D"},
+      {192, 0, 1, 3072, "N=192 same D"},                    {192, 1, 1, 3072, "N=192 two D"},
+  };
+  for (auto& c : cfgs) {
+    for (int grid : {1, 148}) {
+      probe<<<grid, 128, 160 * 1024>>>(c.n, iters, c.mode, c.a16, c.bstep, d);
+      cudaError_t e = cudaDeviceSynchronize();
+      if (e != cudaSuccess) { printf("%s: %s\n", c.what, cudaGetErrorString(e)); return 1; }
+      long long h[148]; cudaMemcpy(h, d, grid * 8, cudaMemcpyDeviceToHost);
+      long long mx = 0; for (int i = 0; i < grid; ++i) mx = h[i] > mx ? h[i] : mx;
+      printf("%-40s grid %3d: %7.1f cycles / MMA  (floor 128*N/256 = %5.1f)\n", c.what, grid, (double)mx / iters, 128.0 * c.n / 256);
+    }
+  }
+  return 0;
+}
