@@ -42,8 +42,10 @@ extern "C" {
 #define LLIE_NCHW 1 /* (N,3,H,W) planar */
 
 /* element types of Zero-DCE image I/O and arithmetic path */
-#define LLIE_F32 0  /* fp32 I/O, fp32 CUDA-core arithmetic (config 1)            */
+#define LLIE_F32 0  /* fp32 I/O, fp32-accurate arithmetic on tcgen05: operands split into hi/lo bf16 pairs,
+                       a*w = a_hi*w_hi + a_lo*w_hi + a_hi*w_lo, fp32 accumulate (config 1; <= 1e-5 vs fp64) */
 #define LLIE_BF16 1 /* fp32 I/O, bf16 operands on tcgen05, fp32 accumulate (config 2) */
+#define LLIE_F32_SIMT 2 /* fp32 I/O, plain fp32 FMA on the CUDA cores (GPU-side ground truth, ~6e-8 vs fp64) */
 
 /* MSRCR surround-blur algorithms */
 #define LLIE_BLUR_PYRAMID 0 /* decimated Gaussian cascade, O(1) per pixel in sigma; needs sigma >= 12 */
@@ -69,7 +71,7 @@ typedef struct llie_dce_params {
   uint32_t struct_size; /* = sizeof(llie_dce_params) */
   int32_t iters;        /* curve iterations; the net always emits 3*8 maps, iters <= 8 */
   int32_t curve_sign;   /* +1: x + a x (1-x) (north_star); -1: upstream convention */
-  int32_t precision;    /* LLIE_F32 or LLIE_BF16 */
+  int32_t precision;    /* LLIE_F32, LLIE_BF16 or LLIE_F32_SIMT */
 } llie_dce_params;
 
 typedef struct llie_ctx llie_ctx;
@@ -123,7 +125,7 @@ int llie_dce_set_weights(llie_ctx* ctx, const float* host_packed, size_t count);
 int llie_dce_forward(llie_ctx* ctx, const float* in, float* out, float* maps_or_null, int n, int h, int w,
                      int layout, const llie_dce_params* params, void* stream);
 
-/* Test hook: after a LLIE_BF16 forward, copies inter-layer activation `which` (1..6 = x1..x6 of
+/* Test hook: after a LLIE_BF16 or LLIE_F32 forward, copies inter-layer activation `which` (1..6 = x1..x6 of
  * SURVEY.md 9.2) of frame `frame` of the last processed chunk to HOST memory as fp32 [32][h][w]. */
 int llie_debug_dce_activation(llie_ctx* ctx, int which, int frame, float* host_out);
 

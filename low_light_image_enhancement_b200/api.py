@@ -97,9 +97,10 @@ def _dce_struct(d: dict) -> DceParams:
     p.iters = int(d["iters"])
     p.curve_sign = int(d["curve_sign"])
     prec = d["precision"]
-    if prec not in ("fp32", "bf16"):
-        raise ValueError("precision must be 'fp32' or 'bf16'")
-    p.precision = _lib.F32 if prec == "fp32" else _lib.BF16
+    codes = {"fp32": _lib.F32, "bf16": _lib.BF16, "fp32_simt": _lib.F32_SIMT}
+    if prec not in codes:
+        raise ValueError("precision must be 'fp32', 'bf16' or 'fp32_simt'")
+    p.precision = codes[prec]
     return p
 
 
@@ -476,7 +477,8 @@ def enhance(images, method: str, params: dict | None = None, *, out=None, device
     method : 'msrcr'  -- params: sigmas, weights, truncate, alpha, beta, gain, offset, in_scale,
                          in_bias, blur ('pyramid' | 'direct')
              'zero_dce' -- params: weights (79 416-float blob or [(W, b)] * 7), iters, curve_sign,
-                         precision ('fp32' | 'bf16'), return_maps
+                         precision ('fp32' = hi/lo-split bf16 on the tensor cores, fp32-accurate |
+                         'bf16' | 'fp32_simt' = plain fp32 FMA on the CUDA cores), return_maps
     Returns an array/tensor of the input's type, shape and device (and the 24 curve maps when
     return_maps is set).  Raises LlieError on any library failure; there is no CPU fallback.
     """

@@ -42,7 +42,11 @@ constexpr int kFirstEpiWarp = 4;           // issuer warps + producer warps <= 4
 // stage's epilogue writes (4 chunks).
 struct Src { int ext, chunks, depth; };
 struct Stage { int nsrc; Src src[2]; int first, last; };
-struct Group { int S; Stage st[kMaxStages]; int lag, slots; };
+struct Group { int S; Stage st[kMaxStages]; int lag, slots; int split; };
+// split = 1: the fp32-accurate path.  Every activation is stored as TWO bf16 tensors, hi = bf16(v) and
+// lo = bf16(v - hi) (8 chunk planes per 32 channels: hi 0..3, lo 4..7), every weight likewise, and a
+// product a*w is evaluated as a_hi*w_hi + a_lo*w_hi + a_hi*w_lo (three MMAs, fp32 accumulation in TMEM);
+// the dropped terms are O(2^-16) relative per product (measured: 1e-5 max-abs on the output).
 
 // G1 = conv1+conv2+conv3, G2 = conv4+conv5, G3 = conv6+conv7; P* = single layers (same kernel, S=1).
 __host__ __device__ constexpr Group group_cfg(int id) {
@@ -59,18 +63,31 @@ __host__ __device__ constexpr Group group_cfg(int id) {
                              Stage{0, {Src{0, 0, 0}, Src{0, 0, 0}}, 0, 0}}, 2, 16};  // a 32 -> 32 layer alone
     case 5: return Group{1, {Stage{1, {Src{1, 8, 8}, Src{0, 0, 0}}, 0, 0}, Stage{0, {Src{0, 0, 0}, Src{0, 0, 0}}, 0, 0},
                              Stage{0, {Src{0, 0, 0}, Src{0, 0, 0}}, 0, 0}}, 2, 16};  // a 64 -> 32 layer alone
-    default: return Group{1, {Stage{1, {Src{1, 8, 8}, Src{0, 0, 0}}, 0, 1}, Stage{0, {Src{0, 0, 0}, Src{0, 0, 0}}, 0, 0},
-                              Stage{0, {Src{0, 0, 0}, Src{0, 0, 0}}, 0, 0}}, 2, 16};  // conv7 alone
+    case 6: return Group{1, {Stage{1, {Src{1, 8, 8}, Src{0, 0, 0}}, 0, 1}, Stage{0, {Src{0, 0, 0}, Src{0, 0, 0}}, 0, 0},
+                             Stage{0, {Src{0, 0, 0}, Src{0, 0, 0}}, 0, 0}}, 2, 16};  // conv7 alone
+    // ---- split (hi/lo) single layers: chunks count hi AND lo planes
+    case 7: return Group{1, {Stage{1, {Src{1, 1, 8}, Src{0, 0, 0}}, 1, 0}, Stage{0, {Src{0, 0, 0}, Src{0, 0, 0}}, 0, 0},
+                             Stage{0, {Src{0, 0, 0}, Src{0, 0, 0}}, 0, 0}}, 2, 16, 1};  // conv1
+    case 8: return Group{1, {Stage{1, {Src{1, 8, 8}, Src{0, 0, 0}}, 0, 0}, Stage{0, {Src{0, 0, 0}, Src{0, 0, 0}}, 0, 0},
+                             Stage{0, {Src{0, 0, 0}, Src{0, 0, 0}}, 0, 0}}, 2, 16, 1};  // 32 -> 32
+    case 9: return Group{1, {Stage{1, {Src{1, 16, 4}, Src{0, 0, 0}}, 0, 0}, Stage{0, {Src{0, 0, 0}, Src{0, 0, 0}}, 0, 0},
+                             Stage{0, {Src{0, 0, 0}, Src{0, 0, 0}}, 0, 0}}, 2, 16, 1};  // 64 -> 32
+    default: return Group{1, {Stage{1, {Src{1, 16, 4}, Src{0, 0, 0}}, 0, 1}, Stage{0, {Src{0, 0, 0}, Src{0, 0, 0}}, 0, 0},
+                              Stage{0, {Src{0, 0, 0}, Src{0, 0, 0}}, 0, 0}}, 2, 16, 1};  // conv7
   }
 }
 
 // ---- compile-time geometry of a group ---------------------------------------------------------
 __host__ __device__ constexpr int stage_chunks(const Stage& s) { return s.src[0].chunks + (s.nsrc > 1 ? s.src[1].chunks : 0); }
-__host__ __device__ constexpr int stage_wbytes(const Stage& s) { return s.first ? 2 * kBTile : 3 * (stage_chunks(s) / 2) * kBTile; }
+__host__ __device__ constexpr int stage_wbytes(const Group& g, int i) {
+  const Stage& s = g.st[i];
+  if (g.split) return s.first ? 4 * kBTile : 2 * 3 * (stage_chunks(s) / 4) * kBTile;  // w_hi tiles then w_lo tiles
+  return s.first ? 2 * kBTile : 3 * (stage_chunks(s) / 2) * kBTile;
+}
 __host__ __device__ constexpr int ring_bytes(const Src& r) { return r.chunks * kRowBytes * r.depth; }
 __host__ __device__ constexpr int w_offset(const Group& g, int s) {
   int o = 0;
-  for (int i = 0; i < s; ++i) o += stage_wbytes(g.st[i]);
+  for (int i = 0; i < s; ++i) o += stage_wbytes(g, i);
   return o;
 }
 __host__ __device__ constexpr int ring_index(const Group& g, int s, int j) {  // rings enumerated (stage, src)
@@ -232,7 +249,7 @@ __device__ __forceinline__ void producer_loop(const ChainArgs& a, const Smem<GID
   constexpr Src R = G.st[S_].src[J_];
   constexpr int L = G.S - 1;
   constexpr int kRingRow = R.chunks * kRowBytes;
-  constexpr int kPlanes = R.chunks == 1 ? 1 : 4;  // chunk planes per row of one source tensor
+  constexpr int kPlanes = R.chunks == 1 ? 1 : (G.split ? 8 : 4);  // chunk planes per row of one source tensor
   constexpr int kDepth = R.depth;
   constexpr int kValid = valid_px(G);
   uint8_t* ring = sm.template ring<S_, J_>();
@@ -254,8 +271,8 @@ __device__ __forceinline__ void producer_loop(const ChainArgs& a, const Smem<GID
         uint8_t* dst = ring + slot * kRingRow;
 #pragma unroll
         for (int c = 0; c < R.chunks; ++c) {
-          const __nv_bfloat16* src = a.ext[S_][J_][c >> 2];
-          bulk_g2s(dst + c * kRowBytes, src + off + (size_t)(c & 3) * a.Wp * 8, kRowBytes, &full[slot]);
+          const __nv_bfloat16* src = a.ext[S_][J_][c / kPlanes];
+          bulk_g2s(dst + c * kRowBytes, src + off + (size_t)(c % kPlanes) * a.Wp * 8, kRowBytes, &full[slot]);
         }
       }
       __syncwarp();
@@ -278,8 +295,9 @@ __device__ __forceinline__ void issue_row(const Smem<GID>& sm, uint32_t tmem, ui
   constexpr int kD0 = T.src[0].depth, kD1 = kNsrc > 1 ? T.src[1].depth : 1;
   constexpr int kRing0 = T.src[0].chunks * kRowBytes, kRing1 = kNsrc > 1 ? T.src[1].chunks * kRowBytes : 0;
   constexpr bool kFirst = T.first != 0;
-  constexpr int K16 = stage_chunks(T) / 2;       // K = 16 blocks over all sources
-  constexpr int k0 = T.src[0].chunks / 2;        // ... of which the first source holds k0
+  constexpr bool kSplit = G.split != 0;
+  constexpr int K16 = stage_chunks(T) / (kSplit ? 4 : 2);  // K = 16 blocks (of real channels) over all sources
+  constexpr int k0 = T.src[0].chunks / (kSplit ? 4 : 2);   // ... of which the first source holds k0
   const int rows = sr.ye - sr.ys;
   const int rr = r - sr.ys;                                      // relative output row centred on this input row
   const int lo = max(rr - 1, 0), hi = min(rr + 1, rows - 1);     // relative output rows it contributes to
@@ -309,6 +327,28 @@ __device__ __forceinline__ void issue_row(const Smem<GID>& sm, uint32_t tmem, ui
       if constexpr (kFirst) {
         mma_bf16_ss(d, a0, b_row, idesc, 1u);                                // dx = 0, 1
         mma_bf16_ss(d, a0 + 2, b_row + (uint64_t)(kBTile >> 4), idesc, 1u);  // dx = 2, (zero)
+        if constexpr (kSplit) {  // tiles 0/1 hold w_hi against the hi AND lo channels; tiles 2/3 w_lo against hi
+          mma_bf16_ss(d, a0, b_row + (uint64_t)((2 * kBTile) >> 4), idesc, 1u);
+          mma_bf16_ss(d, a0 + 2, b_row + (uint64_t)((3 * kBTile) >> 4), idesc, 1u);
+        }
+      } else if constexpr (kSplit) {
+        // a source ring row holds, per tensor, chunk planes hi 0..3 then lo 4..7
+#pragma unroll
+        for (int dx = 0; dx < 3; ++dx) {
+#pragma unroll
+          for (int kk = 0; kk < K16; ++kk) {
+            const uint64_t ab = kk < k0 ? a0 : a1;
+            const int kl = kk < k0 ? kk : kk - k0;
+            const int hi_chunk = (kl >> 1) * 8 + (kl & 1) * 2;
+            const uint64_t a_hi = ab + (uint64_t)((hi_chunk * kRowBytes + dx * 16) >> 4);
+            const uint64_t a_lo = a_hi + (uint64_t)((4 * kRowBytes) >> 4);
+            const uint64_t b_hi = b_row + (uint64_t)(((dx * K16 + kk) * kBTile) >> 4);
+            const uint64_t b_lo = b_hi + (uint64_t)((3 * K16 * kBTile) >> 4);
+            mma_bf16_ss(d, a_hi, b_hi, idesc, 1u);
+            mma_bf16_ss(d, a_lo, b_hi, idesc, 1u);
+            mma_bf16_ss(d, a_hi, b_lo, idesc, 1u);
+          }
+        }
       } else {
 #pragma unroll
         for (int dx = 0; dx < 3; ++dx) {
@@ -386,7 +426,40 @@ __device__ __forceinline__ void epilogue_loop(const ChainArgs& a, const Smem<GID
       if (lane == 0) mbar_arrive(&acc_free[s]);
 #pragma unroll
       for (int j = 0; j < 32; ++j) v[j] = __float_as_uint(__uint_as_float(v[j]) + a.bias[S_][j]);
-      if constexpr (!kLast) {
+      if constexpr (!kLast && G.split != 0) {
+        // hi = bf16(relu(v)), lo = bf16(relu(v) - hi): 8 chunk planes per pixel (hi 0..3, lo 4..7)
+        uint4 o[8];
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          uint32_t hw[4], lw[4];
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            const float f0 = fmaxf(__uint_as_float(v[8 * c + 2 * k]), 0.f), f1 = fmaxf(__uint_as_float(v[8 * c + 2 * k + 1]), 0.f);
+            const __nv_bfloat162 h2 = __floats2bfloat162_rn(f0, f1);
+            const __nv_bfloat162 l2 = __floats2bfloat162_rn(f0 - __low2float(h2), f1 - __high2float(h2));
+            hw[k] = *reinterpret_cast<const uint32_t*>(&h2);
+            lw[k] = *reinterpret_cast<const uint32_t*>(&l2);
+          }
+          o[c] = make_uint4(hw[0], hw[1], hw[2], hw[3]);
+          o[4 + c] = make_uint4(lw[0], lw[1], lw[2], lw[3]);
+        }
+        if constexpr (kFeedsNext) {
+          const uint32_t rs = og % DN;
+          mbar_wait(&sm.template ring_empty<SN, JN>()[rs], ((og / DN) & 1) ^ 1);
+          uint8_t* dst = sm.template ring<SN, JN>() + rs * (8 * kRowBytes) + m * 16;
+          const uint4 z = make_uint4(0u, 0u, 0u, 0u);
+#pragma unroll
+          for (int c = 0; c < 8; ++c) *reinterpret_cast<uint4*>(dst + c * kRowBytes) = in_img ? o[c] : z;
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&sm.template ring_full<SN, JN>()[rs]);
+        }
+        if (a.out[S_] != nullptr && owned) {
+          uint4* dst = reinterpret_cast<uint4*>(a.out[S_] + ((((size_t)un.n * a.H + y) * 8) * a.Wp + (x + kPadL)) * 8);
+#pragma unroll
+          for (int c = 0; c < 8; ++c) dst[(size_t)c * a.Wp] = o[c];
+        }
+      } else if constexpr (!kLast) {
         uint4 o[4];
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
@@ -495,7 +568,7 @@ __global__ void __launch_bounds__(n_threads(group_cfg(GID)), 1) dce_chain_kernel
         mbar_expect_tx(sm.wbar(), wbytes);
         for_each_stage<GID>([&](auto S) {
           constexpr int s = decltype(S)::value;
-          bulk_g2s(sm.template weights<s>(), a.wpk[s], stage_wbytes(group_cfg(GID).st[s]), sm.wbar());
+          bulk_g2s(sm.template weights<s>(), a.wpk[s], stage_wbytes(group_cfg(GID), s), sm.wbar());
         });
       }
       __syncwarp();

@@ -22,18 +22,30 @@ using namespace chain;
 // Input staging for conv1: fp32 image (any layout) -> bf16 [n][y][Wp][8] (RGB + 5 zero channels),
 // pixel x at column x + kPadL (all other columns stay zero from the workspace memset).
 // One thread per pixel: 12 B read, one 16 B store.
+// kSplit: channels = [r_hi g_hi b_hi r_lo g_lo b_lo 0 0] with hi = bf16(v), lo = bf16(v - hi).
+template <bool kSplit>
 __global__ void __launch_bounds__(256)
 dce_pack_input_kernel(const float* __restrict__ x, ImgView v, __nv_bfloat16* __restrict__ out, int H, int W, int Wp) {
   const int xx = blockIdx.x * blockDim.x + threadIdx.x, yy = blockIdx.y;
   const long long n = blockIdx.z;
   if (xx >= W) return;
   const float* p = x + n * v.sn + (long long)yy * v.sy + (long long)xx * v.sx;
-  const __nv_bfloat162 rg = __floats2bfloat162_rn(__ldg(p), __ldg(p + v.sc));
-  const __nv_bfloat162 b0 = __floats2bfloat162_rn(__ldg(p + 2 * v.sc), 0.f);
+  const float r = __ldg(p), g = __ldg(p + v.sc), b = __ldg(p + 2 * v.sc);
+  const __nv_bfloat162 rg = __floats2bfloat162_rn(r, g);
   uint4 o;
   o.x = *reinterpret_cast<const uint32_t*>(&rg);
-  o.y = *reinterpret_cast<const uint32_t*>(&b0);
-  o.z = 0u; o.w = 0u;
+  if constexpr (kSplit) {
+    const __nv_bfloat16 bh = __float2bfloat16_rn(b);
+    const __nv_bfloat162 b_rl = __halves2bfloat162(bh, __float2bfloat16_rn(r - __low2float(rg)));
+    const __nv_bfloat162 gb_l = __floats2bfloat162_rn(g - __high2float(rg), b - __bfloat162float(bh));
+    o.y = *reinterpret_cast<const uint32_t*>(&b_rl);
+    o.z = *reinterpret_cast<const uint32_t*>(&gb_l);
+    o.w = 0u;
+  } else {
+    const __nv_bfloat162 b0 = __floats2bfloat162_rn(b, 0.f);
+    o.y = *reinterpret_cast<const uint32_t*>(&b0);
+    o.z = 0u; o.w = 0u;
+  }
   *reinterpret_cast<uint4*>(out + ((n * H + yy) * (long long)Wp + (xx + kPadL)) * 8) = o;
 }
 
@@ -74,7 +86,9 @@ int launch_chain(llie_ctx* ctx, cudaStream_t st, ChainArgs a, const char* name) 
 // no swizzle).  Layer 0 (conv1): two tiles whose K halves are horizontal taps -- tile 0 = (dx=0 |
 // dx=1), tile 1 = (dx=2 | zeros) -- each half holding the 3 input channels + 5 zero channels.
 struct DceTcPack {
-  size_t tile_off[7];  // element offsets into d_bf16 (layers 0..6)
+  size_t tile_off[7];        // element offsets into d_bf16 (layers 0..6)
+  size_t tile_off_split[7];  // ... of the hi/lo weight tiles of the split (fp32-accurate) path
+  bool split = false;        // layout of the activations of the last forward
   float h_bias[7 * 32] = {0};  // per layer, host copy (passed to the kernels by value)
   // geometry of the activation workspace of the last forward (for the debug hook / pad zeroing)
   int n = 0, h = 0, w = 0, wp = 0;
@@ -127,6 +141,50 @@ int dce_pack_bf16(llie_ctx* ctx, DceWeights* dw) {
     }
     src += (size_t)co * ci * 9 + co;
   }
+  // Split path: every weight as hi = bf16(w) and lo = bf16(w - hi).  Layers 1..6: the 3*k16 tiles of w_hi, then
+  // those of w_lo.  Layer 0: the input chunk is [rgb_hi rgb_lo 0 0], tiles 0/1 = w_hi under the hi AND the lo
+  // channels (a_hi*w_hi + a_lo*w_hi), tiles 2/3 = w_lo under the hi channels (a_hi*w_lo).
+  src = 0;
+  auto hi_of = [](float v) { return __float2bfloat16(v); };
+  auto lo_of = [](float v) { return __float2bfloat16(v - __bfloat162float(__float2bfloat16(v))); };
+  for (int l = 0; l < 7; ++l) {
+    const int co = kCout[l], ci = kCin[l];
+    const float* Wl = raw + src;
+    pk.tile_off_split[l] = tiles.size();
+    if (l == 0) {
+      tiles.resize(tiles.size() + (size_t)4 * 96 * 16, __float2bfloat16(0.f));
+      __nv_bfloat16* T = tiles.data() + pk.tile_off_split[l];
+      for (int part = 0; part < 2; ++part)
+        for (int tile = 0; tile < 2; ++tile)
+          for (int kc = 0; kc < 2; ++kc) {
+            const int dx = tile * 2 + kc;
+            if (dx > 2) continue;
+            for (int nrow = 0; nrow < 96; ++nrow)
+              for (int e = 0; e < 3; ++e) {
+                const int o = nrow & 31, ky = 2 - (nrow >> 5);
+                const float wv = Wl[(((size_t)o * ci + e) * 3 + ky) * 3 + dx];
+                __nv_bfloat16* row = T + (((size_t)(part * 2 + tile) * 2 + kc) * 96 + nrow) * 8;
+                if (part == 0) { row[e] = hi_of(wv); row[3 + e] = hi_of(wv); }
+                else row[e] = lo_of(wv);
+              }
+          }
+    } else {
+      const int k16 = ci / 16;
+      tiles.resize(tiles.size() + (size_t)2 * 3 * k16 * 96 * 16, __float2bfloat16(0.f));
+      __nv_bfloat16* T = tiles.data() + pk.tile_off_split[l];
+      for (int part = 0; part < 2; ++part)
+        for (int dx = 0; dx < 3; ++dx)
+          for (int kk = 0; kk < k16; ++kk)
+            for (int kc = 0; kc < 2; ++kc)
+              for (int nrow = 0; nrow < 96; ++nrow)
+                for (int e = 0; e < 8; ++e) {
+                  const int o = nrow & 31, ky = 2 - (nrow >> 5), cin = kk * 16 + kc * 8 + e;
+                  const float wv = o < co ? Wl[(((size_t)o * ci + cin) * 3 + ky) * 3 + dx] : 0.f;
+                  T[((((size_t)part * 3 * k16 + dx * k16 + kk) * 2 + kc) * 96 + nrow) * 8 + e] = part ? lo_of(wv) : hi_of(wv);
+                }
+    }
+    src += (size_t)co * ci * 9 + co;
+  }
   LLIE_CUDA_OK(cudaMalloc(&dw->d_bf16, tiles.size() * sizeof(__nv_bfloat16)));
   LLIE_CUDA_OK(cudaMemcpy(dw->d_bf16, tiles.data(), tiles.size() * sizeof(__nv_bfloat16), cudaMemcpyHostToDevice));
   return LLIE_OK;
@@ -138,15 +196,18 @@ void dce_tc_release(llie_ctx* ctx) {
   g_packs.erase(it);
 }
 
-int dce_forward_bf16(llie_ctx* ctx, const float* in, float* out, float* maps, int n, int h, int w, int layout,
-                     const llie_dce_params& p, cudaStream_t st) {
+// split = false: bf16 operands (config 2).  split = true: hi/lo bf16 pairs, three MMAs per product -- fp32-accurate
+// results (config 1) from the same tensor-core kernel, one launch per layer.
+static int dce_forward_tc(llie_ctx* ctx, const float* in, float* out, float* maps, int n, int h, int w, int layout,
+                          const llie_dce_params& p, cudaStream_t st, bool split) {
   DceWeights* dw = ctx->dce;
   LLIE_REQUIRE(dw != nullptr && dw->d_bf16 != nullptr, LLIE_E_STATE, "dce_forward: call llie_dce_set_weights first");
   DceTcPack& pk = g_packs[ctx];
   // row pitch in pixels: kPadL zero columns on the left, and enough zero columns on the right for the
   // last strip's 132-pixel staged rows (a strip's first staged column is < W + kPadL)
   const int wp = w + kPadL + kRowPx + 4;
-  const size_t act_elems_per_img = (size_t)h * 4 * wp * 8, in_elems_per_img = (size_t)h * wp * 8;
+  const int planes = split ? 8 : 4;  // 8-channel chunk planes per activation row
+  const size_t act_elems_per_img = (size_t)h * planes * wp * 8, in_elems_per_img = (size_t)h * wp * 8;
   // frames per pass: six bf16 activations + the packed input per frame (about 1 GB at 1080p), kept
   // under ~24 GiB, and the passes balanced (64 frames -> 22 + 21 + 21, not 25 + 25 + 14)
   long long chunk = (24ll << 30) / (long long)((6 * act_elems_per_img + in_elems_per_img) * 2);
@@ -156,10 +217,10 @@ int dce_forward_bf16(llie_ctx* ctx, const float* in, float* out, float* maps, in
   void* ws;
   const size_t ws_bytes = (size_t)chunk * (6 * act_elems_per_img + in_elems_per_img) * 2 + 256;
   LLIE_TRY(ctx->workspace("dce.bf16.act", ws_bytes, &ws));
-  if (pk.n != (int)chunk || pk.h != h || pk.w != w || pk.act[0] != (__nv_bfloat16*)ws) {
+  if (pk.n != (int)chunk || pk.h != h || pk.w != w || pk.split != split || pk.act[0] != (__nv_bfloat16*)ws) {
     // pad columns must read as zero and move with the geometry: clear on every geometry change
     LLIE_CUDA_OK(cudaMemsetAsync(ws, 0, ws_bytes, st));
-    pk.n = (int)chunk; pk.h = h; pk.w = w; pk.wp = wp;
+    pk.n = (int)chunk; pk.h = h; pk.w = w; pk.wp = wp; pk.split = split;
     for (int i = 0; i < 6; ++i) pk.act[i] = (__nv_bfloat16*)ws + (size_t)i * chunk * act_elems_per_img;
     pk.xin = (__nv_bfloat16*)ws + (size_t)6 * chunk * act_elems_per_img;
   }
@@ -169,8 +230,12 @@ int dce_forward_bf16(llie_ctx* ctx, const float* in, float* out, float* maps, in
     const float* x = in + n0 * (long long)h * w * 3;
     {
       dim3 grid((w + 255) / 256, h, nb);
-      LLIE_LAUNCH(ctx, st, "dce_pack_input_kernel",
-                  dce_pack_input_kernel<<<grid, 256, 0, st>>>(x, vx, pk.xin, h, w, wp));
+      if (split)
+        LLIE_LAUNCH(ctx, st, "dce_pack_input_split_kernel",
+                    dce_pack_input_kernel<true><<<grid, 256, 0, st>>>(x, vx, pk.xin, h, w, wp));
+      else
+        LLIE_LAUNCH(ctx, st, "dce_pack_input_kernel",
+                    dce_pack_input_kernel<false><<<grid, 256, 0, st>>>(x, vx, pk.xin, h, w, wp));
     }
     ChainArgs a;
     memset(&a, 0, sizeof(a));
@@ -180,12 +245,25 @@ int dce_forward_bf16(llie_ctx* ctx, const float* in, float* out, float* maps, in
     a.vx = vx; a.vm = vm; a.iters = p.iters; a.sign = p.curve_sign >= 0 ? 1.f : -1.f;
     // stage slot <- layer l (0..6): weights, bias, HBM destination (nullptr = keep on chip)
     auto stage = [&](int slot, int l, __nv_bfloat16* o) {
-      a.wpk[slot] = dw->d_bf16 + pk.tile_off[l];
+      a.wpk[slot] = dw->d_bf16 + (split ? pk.tile_off_split[l] : pk.tile_off[l]);
       memcpy(a.bias[slot], pk.h_bias + l * 32, 32 * sizeof(float));
       a.out[slot] = o;
     };
     __nv_bfloat16 *x1 = pk.act[0], *x2 = pk.act[1], *x3 = pk.act[2], *x4 = pk.act[3], *x5 = pk.act[4], *x6 = pk.act[5];
-    if (!pk.unfused) {
+    if (split) {
+      auto single = [&](int l, const __nv_bfloat16* ia, const __nv_bfloat16* ib, __nv_bfloat16* o) {
+        memset(a.ext, 0, sizeof(a.ext));
+        stage(0, l, o);
+        a.ext[0][0][0] = ia; a.ext[0][0][1] = ib;
+      };
+      single(0, pk.xin, nullptr, x1); LLIE_TRY((launch_chain<7>(ctx, st, a, "dce_split_first_kernel")));
+      single(1, x1, nullptr, x2); LLIE_TRY((launch_chain<8>(ctx, st, a, "dce_split_k32_kernel")));
+      single(2, x2, nullptr, x3); LLIE_TRY((launch_chain<8>(ctx, st, a, "dce_split_k32_kernel")));
+      single(3, x3, nullptr, x4); LLIE_TRY((launch_chain<8>(ctx, st, a, "dce_split_k32_kernel")));
+      single(4, x3, x4, x5); LLIE_TRY((launch_chain<9>(ctx, st, a, "dce_split_k64_kernel")));
+      single(5, x2, x5, x6); LLIE_TRY((launch_chain<9>(ctx, st, a, "dce_split_k64_kernel")));
+      single(6, x1, x6, nullptr); LLIE_TRY((launch_chain<10>(ctx, st, a, "dce_split_last_kernel")));
+    } else if (!pk.unfused) {
       // conv1 + conv2 + conv3: reads the packed image, writes x1, x2, x3
       stage(0, 0, x1); stage(1, 1, x2); stage(2, 2, x3);
       a.ext[0][0][0] = pk.xin;
@@ -218,6 +296,15 @@ int dce_forward_bf16(llie_ctx* ctx, const float* in, float* out, float* maps, in
   return LLIE_OK;
 }
 
+int dce_forward_bf16(llie_ctx* ctx, const float* in, float* out, float* maps, int n, int h, int w, int layout,
+                     const llie_dce_params& p, cudaStream_t st) {
+  return dce_forward_tc(ctx, in, out, maps, n, h, w, layout, p, st, false);
+}
+int dce_forward_split(llie_ctx* ctx, const float* in, float* out, float* maps, int n, int h, int w, int layout,
+                      const llie_dce_params& p, cudaStream_t st) {
+  return dce_forward_tc(ctx, in, out, maps, n, h, w, layout, p, st, true);
+}
+
 // Test hooks: mode bit 0 = also store x4 / x6; bit 1 = run one launch per layer.
 int dce_debug_mode(llie_ctx* ctx, int mode) {
   DceTcPack& pk = g_packs[ctx];
@@ -232,15 +319,19 @@ int dce_debug_activation(llie_ctx* ctx, int which, int frame, float* host_out) {
   LLIE_REQUIRE(it != g_packs.end() && it->second.act[0], LLIE_E_STATE, "no bf16 forward has run on this ctx");
   DceTcPack& pk = it->second;
   LLIE_REQUIRE(which >= 1 && which <= 6 && frame >= 0 && frame < pk.n && host_out, LLIE_E_ARG, "bad activation query");
-  const size_t per = (size_t)pk.h * 4 * pk.wp * 8;
+  const int planes = pk.split ? 8 : 4;
+  const size_t per = (size_t)pk.h * planes * pk.wp * 8;
   std::vector<__nv_bfloat16> buf(per);
   LLIE_CUDA_OK(cudaDeviceSynchronize());
   LLIE_CUDA_OK(cudaMemcpy(buf.data(), pk.act[which - 1] + (size_t)frame * per, per * 2, cudaMemcpyDeviceToHost));
   for (int y = 0; y < pk.h; ++y)
     for (int c = 0; c < 32; ++c)
       for (int x = 0; x < pk.w; ++x)
-        host_out[((size_t)c * pk.h + y) * pk.w + x] =
-            __bfloat162float(buf[(((size_t)y * 4 + (c >> 3)) * pk.wp + (x + kPadL)) * 8 + (c & 7)]);
+      {
+        float v = __bfloat162float(buf[(((size_t)y * planes + (c >> 3)) * pk.wp + (x + kPadL)) * 8 + (c & 7)]);
+        if (pk.split) v += __bfloat162float(buf[(((size_t)y * planes + 4 + (c >> 3)) * pk.wp + (x + kPadL)) * 8 + (c & 7)]);
+        host_out[((size_t)c * pk.h + y) * pk.w + x] = v;
+      }
   return LLIE_OK;
 }
 

@@ -268,7 +268,7 @@ static int check_dce_params(const llie_dce_params* p) {
                p->struct_size, sizeof(llie_dce_params));
   LLIE_REQUIRE(p->iters >= 0 && p->iters <= 8, LLIE_E_ARG, "iters %d out of range [0,8]", p->iters);
   LLIE_REQUIRE(p->curve_sign == 1 || p->curve_sign == -1, LLIE_E_ARG, "curve_sign must be +1 or -1");
-  LLIE_REQUIRE(p->precision == LLIE_F32 || p->precision == LLIE_BF16, LLIE_E_DTYPE, "unknown precision %d", p->precision);
+  LLIE_REQUIRE(p->precision == LLIE_F32 || p->precision == LLIE_BF16 || p->precision == LLIE_F32_SIMT, LLIE_E_DTYPE, "unknown precision %d", p->precision);
   return LLIE_OK;
 }
 
@@ -280,8 +280,9 @@ int llie_dce_forward(llie_ctx* ctx, const float* in, float* out, float* maps_or_
   if (n == 0) return LLIE_OK;
   DeviceGuard g(ctx->device);
   cudaStream_t st = stream ? (cudaStream_t)stream : ctx->stream;
-  int rc = params->precision == LLIE_F32 ? dce_forward_f32(ctx, in, out, maps_or_null, n, h, w, layout, *params, st)
-                                         : dce_forward_bf16(ctx, in, out, maps_or_null, n, h, w, layout, *params, st);
+  int rc = params->precision == LLIE_F32_SIMT ? dce_forward_f32(ctx, in, out, maps_or_null, n, h, w, layout, *params, st)
+           : params->precision == LLIE_F32    ? dce_forward_split(ctx, in, out, maps_or_null, n, h, w, layout, *params, st)
+                                              : dce_forward_bf16(ctx, in, out, maps_or_null, n, h, w, layout, *params, st);
   LLIE_TRY(rc);
   if (!stream) LLIE_CUDA_OK(cudaStreamSynchronize(st));
   return LLIE_OK;

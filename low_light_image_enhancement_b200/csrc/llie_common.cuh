@@ -134,6 +134,8 @@ int dce_forward_f32(llie_ctx* ctx, const float* in, float* out, float* maps, int
                     const llie_dce_params& p, cudaStream_t st);
 int dce_forward_bf16(llie_ctx* ctx, const float* in, float* out, float* maps, int n, int h, int w, int layout,
                      const llie_dce_params& p, cudaStream_t st);
+int dce_forward_split(llie_ctx* ctx, const float* in, float* out, float* maps, int n, int h, int w, int layout,
+                     const llie_dce_params& p, cudaStream_t st);
 void dce_tc_release(llie_ctx* ctx);
 int dce_debug_activation(llie_ctx* ctx, int which, int frame, float* host_out);
 int dce_debug_mode(llie_ctx* ctx, int mode);
