@@ -280,14 +280,62 @@ __device__ __forceinline__ void producer_loop(const ChainArgs& a, const Smem<GID
   }
 }
 
-// ---- MMA issue for one input row of stage S_ ------------------------------------------------------
-// ocnt = output rows of this stage started before the current unit; rcnt = ring rows consumed before
-// the current unit (the same for every source of a stage); r = absolute input row.
-struct IssueState { uint32_t ocnt[kMaxStages]; uint32_t rcnt[kMaxStages]; };
+// ---- MMA issue of stage S_: a software-pipelined walk over (unit, input row) -----------------------
+// oc = output rows of this stage started before the current unit (position in the TMEM slot ring);
+// rc = ring rows consumed so far (the same for every source of a stage); r = absolute input row.
+struct RowIt { int u; StageRows sr; int r; uint32_t oc, rc; bool valid; };
 
 template <int GID, int S_>
-__device__ __forceinline__ void issue_row(const Smem<GID>& sm, uint32_t tmem, uint32_t ocnt, uint32_t rc,
-                                          const StageRows& sr, int r) {
+__device__ __forceinline__ void row_begin_unit(const ChainArgs& a, RowIt& it) {
+  constexpr int L = group_cfg(GID).S - 1;
+  it.valid = it.u < a.units;
+  if (it.valid) {
+    const Unit un = decode_unit(a, it.u);
+    it.sr = stage_rows(un.ys, un.ye, a.H, L, S_);
+    it.r = it.sr.in_lo;
+  }
+}
+template <int GID, int S_>
+__device__ __forceinline__ void row_advance(const ChainArgs& a, RowIt& it) {
+  ++it.rc;
+  if (++it.r == it.sr.in_hi) {
+    it.oc += it.sr.ye - it.sr.ys;
+    it.u += gridDim.x;
+    row_begin_unit<GID, S_>(a, it);
+  }
+}
+
+// What input row `it` needs before its MMAs may be issued: the accumulator slots it touches for the first time
+// drained and re-zeroed since their previous use, and its ring row(s) landed.  kBlock: spin; else probe once.
+template <int GID, int S_, bool kBlock>
+__device__ __forceinline__ bool row_ready(const Smem<GID>& sm, const RowIt& it) {
+  constexpr Group G = group_cfg(GID);
+  constexpr Stage T = G.st[S_];
+  constexpr int NS = G.slots;
+  constexpr int kD0 = T.src[0].depth, kD1 = T.nsrc > 1 ? T.src[1].depth : 1;
+  auto check = [](uint64_t* bar, uint32_t parity) -> bool {
+    if constexpr (kBlock) { mbar_wait(bar, parity); return true; }
+    else return mbar_try_wait(bar, parity);
+  };
+  const int rows = it.sr.ye - it.sr.ys, rr = it.r - it.sr.ys;
+  const int lo = max(rr - 1, 0), hi = min(rr + 1, rows - 1);
+  uint64_t* acc_free = sm.template acc_free<S_>();
+  bool ok = true;
+  for (int o = (it.r == it.sr.in_lo) ? lo : rr + 1; o <= hi; ++o) {
+    const uint32_t og = it.oc + o;
+    ok = check(&acc_free[og % NS], (og / NS) & 1) && ok;
+  }
+  ok = check(&sm.template ring_full<S_, 0>()[it.rc % kD0], (it.rc / kD0) & 1) && ok;
+  if constexpr (T.nsrc > 1) ok = check(&sm.template ring_full<S_, (T.nsrc > 1 ? 1 : 0)>()[it.rc % kD1], (it.rc / kD1) & 1) && ok;
+  return ok;
+}
+
+// Issues the MMAs of input row `cur` (whose barriers have been waited on).  Between the first third of the
+// MMAs and the rest, the barriers of the NEXT row are probed (and waited on after the last MMA if they were
+// not ready): the mbarrier round trips and the address arithmetic run while the tensor pipe drains its
+// queue, instead of between rows with the pipe idle (ncu: the issuing warp spent ~40 % of a row on this).
+template <int GID, int S_>
+__device__ __forceinline__ void issue_row(const Smem<GID>& sm, uint32_t tmem, const RowIt& cur, const RowIt& nxt) {
   constexpr Group G = group_cfg(GID);
   constexpr Stage T = G.st[S_];
   constexpr int NS = G.slots;
@@ -298,19 +346,14 @@ __device__ __forceinline__ void issue_row(const Smem<GID>& sm, uint32_t tmem, ui
   constexpr bool kSplit = G.split != 0;
   constexpr int K16 = stage_chunks(T) / (kSplit ? 4 : 2);  // K = 16 blocks (of real channels) over all sources
   constexpr int k0 = T.src[0].chunks / (kSplit ? 4 : 2);   // ... of which the first source holds k0
+  const StageRows& sr = cur.sr;
+  const int r = cur.r;
+  const uint32_t ocnt = cur.oc, rc = cur.rc;
   const int rows = sr.ye - sr.ys;
   const int rr = r - sr.ys;                                      // relative output row centred on this input row
   const int lo = max(rr - 1, 0), hi = min(rr + 1, rows - 1);     // relative output rows it contributes to
-  uint64_t* acc_free = sm.template acc_free<S_>();
   uint64_t* acc_ready = sm.template acc_ready<S_>();
-  // slots touched for the first time must have been drained and re-zeroed since their previous use
-  for (int o = (r == sr.in_lo) ? lo : rr + 1; o <= hi; ++o) {
-    const uint32_t og = ocnt + o;
-    mbar_wait(&acc_free[og % NS], (og / NS) & 1);
-  }
   const uint32_t slot0 = rc % kD0, slot1 = rc % kD1;
-  mbar_wait(&sm.template ring_full<S_, 0>()[slot0], (rc / kD0) & 1);
-  if constexpr (kNsrc > 1) mbar_wait(&sm.template ring_full<S_, (kNsrc > 1 ? 1 : 0)>()[slot1], (rc / kD1) & 1);
   tc_fence_after();
   if (elect_one()) {
     const uint64_t b_desc0 = smem_desc(smem_u32(sm.template weights<S_>()), kBPlane, 128);
@@ -319,59 +362,62 @@ __device__ __forceinline__ void issue_row(const Smem<GID>& sm, uint32_t tmem, ui
     uint64_t a1 = 0;
     if constexpr (kNsrc > 1)
       a1 = smem_desc(smem_u32(sm.template ring<S_, (kNsrc > 1 ? 1 : 0)>()), kRowBytes, 128) + (uint64_t)(slot1 * (kRing1 >> 4));
-    // cnt output rows starting at slot s0; dyslot of the first: 0 = dy+1 (output above), 1 = dy 0, 2 = dy-1
-    auto issue = [&](uint32_t s0, int cnt, int dyslot) {
+    // cnt output rows starting at slot s0; dyslot of the first: 0 = dy+1 (output above), 1 = dy 0, 2 = dy-1.
+    // part 0 = the horizontal tap dx = 0, part 1 = dx = 1, 2 (conv1: its first / remaining MMAs).
+    auto issue = [&](uint32_t s0, int cnt, int dyslot, int part) {
       const uint32_t idesc = idesc_bf16_m128(32 * cnt);
       const uint32_t d = tmem + (S_ * NS + s0) * 32;
       const uint64_t b_row = b_desc0 + (uint64_t)(dyslot * (512 >> 4));
       if constexpr (kFirst) {
-        mma_bf16_ss(d, a0, b_row, idesc, 1u);                                // dx = 0, 1
-        mma_bf16_ss(d, a0 + 2, b_row + (uint64_t)(kBTile >> 4), idesc, 1u);  // dx = 2, (zero)
-        if constexpr (kSplit) {  // tiles 0/1 hold w_hi against the hi AND lo channels; tiles 2/3 w_lo against hi
-          mma_bf16_ss(d, a0, b_row + (uint64_t)((2 * kBTile) >> 4), idesc, 1u);
-          mma_bf16_ss(d, a0 + 2, b_row + (uint64_t)((3 * kBTile) >> 4), idesc, 1u);
-        }
-      } else if constexpr (kSplit) {
-        // a source ring row holds, per tensor, chunk planes hi 0..3 then lo 4..7
-#pragma unroll
-        for (int dx = 0; dx < 3; ++dx) {
-#pragma unroll
-          for (int kk = 0; kk < K16; ++kk) {
-            const uint64_t ab = kk < k0 ? a0 : a1;
-            const int kl = kk < k0 ? kk : kk - k0;
-            const int hi_chunk = (kl >> 1) * 8 + (kl & 1) * 2;
-            const uint64_t a_hi = ab + (uint64_t)((hi_chunk * kRowBytes + dx * 16) >> 4);
-            const uint64_t a_lo = a_hi + (uint64_t)((4 * kRowBytes) >> 4);
-            const uint64_t b_hi = b_row + (uint64_t)(((dx * K16 + kk) * kBTile) >> 4);
-            const uint64_t b_lo = b_hi + (uint64_t)((3 * K16 * kBTile) >> 4);
-            mma_bf16_ss(d, a_hi, b_hi, idesc, 1u);
-            mma_bf16_ss(d, a_lo, b_hi, idesc, 1u);
-            mma_bf16_ss(d, a_hi, b_lo, idesc, 1u);
+        if (part == 0) {
+          mma_bf16_ss(d, a0, b_row, idesc, 1u);                                // dx = 0, 1
+        } else {
+          mma_bf16_ss(d, a0 + 2, b_row + (uint64_t)(kBTile >> 4), idesc, 1u);  // dx = 2, (zero)
+          if constexpr (kSplit) {  // tiles 0/1 hold w_hi against the hi AND lo channels; tiles 2/3 w_lo against hi
+            mma_bf16_ss(d, a0, b_row + (uint64_t)((2 * kBTile) >> 4), idesc, 1u);
+            mma_bf16_ss(d, a0 + 2, b_row + (uint64_t)((3 * kBTile) >> 4), idesc, 1u);
           }
         }
       } else {
 #pragma unroll
         for (int dx = 0; dx < 3; ++dx) {
+          if ((dx == 0) != (part == 0)) continue;
 #pragma unroll
           for (int kk = 0; kk < K16; ++kk) {
             const uint64_t ab = kk < k0 ? a0 : a1;
             const int kl = kk < k0 ? kk : kk - k0;
-            const uint64_t ad = ab + (uint64_t)((kl * 2 * kRowBytes + dx * 16) >> 4);
-            const uint64_t bd = b_row + (uint64_t)(((dx * K16 + kk) * kBTile) >> 4);
-            mma_bf16_ss(d, ad, bd, idesc, 1u);
+            if constexpr (kSplit) {
+              // a source ring row holds, per tensor, chunk planes hi 0..3 then lo 4..7
+              const int hi_chunk = (kl >> 1) * 8 + (kl & 1) * 2;
+              const uint64_t a_hi = ab + (uint64_t)((hi_chunk * kRowBytes + dx * 16) >> 4);
+              const uint64_t a_lo = a_hi + (uint64_t)((4 * kRowBytes) >> 4);
+              const uint64_t b_hi = b_row + (uint64_t)(((dx * K16 + kk) * kBTile) >> 4);
+              const uint64_t b_lo = b_hi + (uint64_t)((3 * K16 * kBTile) >> 4);
+              mma_bf16_ss(d, a_hi, b_hi, idesc, 1u);
+              mma_bf16_ss(d, a_lo, b_hi, idesc, 1u);
+              mma_bf16_ss(d, a_hi, b_lo, idesc, 1u);
+            } else {
+              const uint64_t ad = ab + (uint64_t)((kl * 2 * kRowBytes + dx * 16) >> 4);
+              const uint64_t bd = b_row + (uint64_t)(((dx * K16 + kk) * kBTile) >> 4);
+              mma_bf16_ss(d, ad, bd, idesc, 1u);
+            }
           }
         }
       }
     };
     const uint32_t s0 = (ocnt + lo) % NS;
     const int cnt = hi - lo + 1, c1 = min(cnt, NS - (int)s0), dyslot = lo - (rr - 1);
-    issue(s0, c1, dyslot);
-    if (c1 < cnt) issue(0, cnt - c1, dyslot + c1);  // the slot ring wrapped
+    issue(s0, c1, dyslot, 0);
+    if (c1 < cnt) issue(0, cnt - c1, dyslot + c1, 0);  // the slot ring wrapped
+    const bool nxt_ready = nxt.valid ? row_ready<GID, S_, false>(sm, nxt) : true;
+    issue(s0, c1, dyslot, 1);
+    if (c1 < cnt) issue(0, cnt - c1, dyslot + c1, 1);
     mma_commit(&sm.template ring_empty<S_, 0>()[slot0]);
     if constexpr (kNsrc > 1) mma_commit(&sm.template ring_empty<S_, (kNsrc > 1 ? 1 : 0)>()[slot1]);
     // output row rr-1 has now received its last tap; at the bottom image border so has row rr
     if (rr >= 1) mma_commit(&acc_ready[(ocnt + rr - 1) % NS]);
     if (r == sr.in_hi - 1 && rr == rows - 1) mma_commit(&acc_ready[(ocnt + rr) % NS]);
+    if (!nxt_ready) row_ready<GID, S_, true>(sm, nxt);
   }
   __syncwarp();
 }
@@ -518,7 +564,7 @@ __device__ __forceinline__ void epilogue_loop(const ChainArgs& a, const Smem<GID
 template <int GID>
 __global__ void __launch_bounds__(n_threads(group_cfg(GID)), 1) dce_chain_kernel(const __grid_constant__ ChainArgs a) {
   constexpr Group G = group_cfg(GID);
-  constexpr int L = G.S - 1, kS = G.S;
+  constexpr int kS = G.S;
   constexpr int kRingLo = w_offset(G, G.S), kRingHi = bar_offset(G);
   static_assert(G.S * G.slots * 32 <= 512, "TMEM: stages x slots x 32 columns must fit 512");
   static_assert(smem_bytes(G) <= 227 * 1024, "shared memory budget");
@@ -577,12 +623,15 @@ __global__ void __launch_bounds__(n_threads(group_cfg(GID)), 1) dce_chain_kernel
     for_each_stage<GID>([&](auto S) {
       constexpr int s = decltype(S)::value;
       if (warp == s) {
-        uint32_t oc = 0, rc = 0;  // running positions in the TMEM slot ring / the input rings
-        for (int u = blockIdx.x; u < a.units; u += gridDim.x) {
-          const Unit un = decode_unit(a, u);
-          const StageRows sr = stage_rows(un.ys, un.ye, a.H, L, s);
-          for (int r = sr.in_lo; r < sr.in_hi; ++r, ++rc) issue_row<GID, s>(sm, tmem, oc, rc, sr, r);
-          oc += sr.ye - sr.ys;
+        RowIt cur;
+        cur.u = blockIdx.x; cur.oc = 0; cur.rc = 0; cur.r = 0;
+        row_begin_unit<GID, s>(a, cur);
+        if (cur.valid) row_ready<GID, s, true>(sm, cur);
+        while (cur.valid) {
+          RowIt nxt = cur;
+          row_advance<GID, s>(a, nxt);
+          issue_row<GID, s>(sm, tmem, cur, nxt);
+          cur = nxt;
         }
       }
     });

@@ -8,7 +8,7 @@
 using namespace llie::ptx;
 
 // mode bit0: alternate between two accumulators; bit1: 4 accumulators round-robin
-__global__ void probe(int n, int iters, int mode, int a_stride16, int b_bytes_step, long long* out) {
+__global__ void probe(int n, int iters, int mode, int a_stride16, int b_bytes_step, long long* out, int a_base = 0) {
   extern __shared__ __align__(1024) uint8_t smem[];
   __shared__ uint64_t bar;
   __shared__ uint32_t tm;
@@ -21,7 +21,7 @@ __global__ void probe(int n, int iters, int mode, int a_stride16, int b_bytes_st
   if (threadIdx.x < 32) {
     long long t0 = 0, t1 = 0;
     if (elect_one()) {
-      const uint64_t a0 = smem_desc(smem_u32(smem), 2112, 128);
+      const uint64_t a0 = smem_desc(smem_u32(smem) + a_base, 2112, 128);
       const uint64_t b0 = smem_desc(smem_u32(smem + 96 * 1024), 1536, 128);
       const uint32_t idesc = idesc_bf16_m128(n);
       const int nacc = (mode & 2) ? 4 : ((mode & 1) ? 2 : 1);
@@ -47,7 +47,7 @@ int main() {
   long long* d; cudaMalloc(&d, 148 * 8);
   cudaFuncSetAttribute(probe, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
   const int iters = 4096;
-  struct Cfg { int n, mode, a16, bstep; const char* what; };
+  struct Cfg { int n, mode, a16, bstep; const char* what; int abase = 0; };
   Cfg cfgs[] = {
       {96, 0, 1, 3072, "N=96 same D (as the conv kernel)"}, {96, 1, 1, 3072, "N=96 two D alternating"},
       {96, 2, 1, 3072, "N=96 four D round-robin"},          {32, 0, 1, 3072, "N=32 same D"},
@@ -56,10 +56,14 @@ int main() {
       {256, 1, 1, 0, "N=256 two D"},                        {96, 0, 0, 0, "N=96 same D, same operands"},
       {96, 2, 0, 0, "N=96 four D, same operands"},          {64, 0, 1, 3072, "N=64 same D"},
       {192, 0, 1, 3072, "N=192 same D"},                    {192, 1, 1, 3072, "N=192 two D"},
+      {96, 0, 0, 3072, "N=96 A fixed, 128B-aligned"},        {96, 0, 8, 3072, "N=96 A steps of 128 B (aligned)"},
+      {96, 0, 1, 3072, "N=96 A steps of 16 B (the conv)"},   {96, 0, 8, 3072, "N=96 A steps 128 B, base +64 B", 64},
+      {96, 0, 8, 3072, "N=96 A steps 128 B, base +16 B", 16}, {96, 0, 0, 3072, "N=96 A fixed, base +16 B", 16},
+      {96, 0, 0, 3072, "N=96 A fixed, base +64 B", 64},      {96, 0, 0, 3072, "N=96 A fixed, base +32 B", 32},
   };
   for (auto& c : cfgs) {
     for (int grid : {1, 148}) {
-      probe<<<grid, 128, 160 * 1024>>>(c.n, iters, c.mode, c.a16, c.bstep, d);
+      probe<<<grid, 128, 160 * 1024>>>(c.n, iters, c.mode, c.a16, c.bstep, d, c.abase);
       cudaError_t e = cudaDeviceSynchronize();
       if (e != cudaSuccess) { printf("%s: %s\n", c.what, cudaGetErrorString(e)); return 1; }
       long long h[148]; cudaMemcpy(h, d, grid * 8, cudaMemcpyDeviceToHost);
