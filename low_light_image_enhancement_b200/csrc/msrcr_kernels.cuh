@@ -215,40 +215,72 @@ __device__ __forceinline__ void up_bc_phase(int jc, int& j0, int& ph) {
   ph = d & 3;
   j0 = (d >> 2) - 1 + kPB + (ph >= 2 ? 1 : 0);
 }
-// x pass on B rows [b0, b1): T2[plane][jb][jc] (hB x wC)
+// The four C samples jc = 4q + ph + kPC - 4 (ph = 0..3) of group q share the ten B samples q + kPB - 5 .. q + kPB + 4:
+// phases 0, 1 are centred on j0 = q + kPB - 1, phases 2, 3 on j0 + 1.  Both passes therefore load a window of ten
+// values once and produce four outputs with compile-time phase (weights become constant-bank FFMA operands).
+__device__ __forceinline__ void up_bc_group(const float (&win)[10], const UpWeights& uw, float (&o)[4]) {
+#pragma unroll
+  for (int ph = 0; ph < 4; ++ph) {
+    float acc = 0.f;
+#pragma unroll
+    for (int t = 0; t <= 2 * kTU; ++t) acc = fmaf(uw.w[ph][t], win[t + (ph >= 2 ? 1 : 0)], acc);
+    o[ph] = acc;
+  }
+}
+__host__ __device__ inline int up_bc_x_groups(int wC) { return ((wC - 1 + 4 - kPC) >> 2) + 1; }  // q of the last column + 1
+// x pass on B rows [b0, b1): T2[plane][jb][jc] (hB x wC).  One thread per (row, group of 4 output columns).
 __global__ void __launch_bounds__(256)
 up_bc_x_kernel(const float* __restrict__ SB, float* __restrict__ T2, int hB, int wB, int wC, int b0, int b1,
                const __grid_constant__ UpWeights uw) {
   const long long plane = blockIdx.z;
+  const int groups = up_bc_x_groups(wC);
   const int i = blockIdx.x * 256 + threadIdx.x;
-  const int n = (b1 - b0) * wC;
-  if (i >= n) return;
-  const int jb = b0 + i / wC, jc = i % wC;
-  int j0, ph;
-  up_bc_phase(jc, j0, ph);
+  if (i >= (b1 - b0) * groups) return;
+  const int jb = b0 + i / groups, q = i % groups;
   const float* src = SB + (plane * hB + jb) * (long long)wB;
-  float acc = 0.f;
+  float win[10], o[4];
 #pragma unroll
-  for (int t = 0; t <= 2 * kTU; ++t) acc = fmaf(uw.w[ph][t], __ldg(src + min(max(j0 - kTU + t, 0), wB - 1)), acc);
-  T2[(plane * hB + jb) * (long long)wC + jc] = acc;
+  for (int t = 0; t < 10; ++t) win[t] = __ldg(src + min(max(q + kPB - 5 + t, 0), wB - 1));
+  up_bc_group(win, uw, o);
+  float* dst = T2 + (plane * hB + jb) * (long long)wC;
+#pragma unroll
+  for (int ph = 0; ph < 4; ++ph) {
+    const int jc = 4 * q + ph + kPC - 4;
+    if (jc >= 0 && jc < wC) dst[jc] = o[ph];
+  }
 }
-// y pass for C rows [c0, c1): SC[plane][jc][x] (hC x wC)
-__global__ void __launch_bounds__(256)
+// y pass for C rows [c0, c1): SC[plane][jc][x] (hC x wC).  One thread per column walks down kUpGroups groups of
+// four C rows with the ten-row window in registers: one new T2 sample per four outputs.
+constexpr int kUpGroups = 16;
+__host__ __device__ inline int up_bc_y_chunks(int c0, int c1) {
+  return (((c1 - 1 - kPC + 4) >> 2) - ((c0 - kPC + 4) >> 2)) / kUpGroups + 1;
+}
+__global__ void __launch_bounds__(128)
 up_bc_y_kernel(const float* __restrict__ T2, float* __restrict__ SC, int hB, int hC, int wC, int c0, int c1,
                const __grid_constant__ UpWeights uw) {
   const long long plane = blockIdx.z;
-  const int i = blockIdx.x * 256 + threadIdx.x;
-  const int n = (c1 - c0) * wC;
-  if (i >= n) return;
-  const int jc = c0 + i / wC, xx = i % wC;
-  int j0, ph;
-  up_bc_phase(jc, j0, ph);
+  const int xx = blockIdx.x * 128 + threadIdx.x;
+  if (xx >= wC) return;
+  const int q_lo = (c0 - kPC + 4) >> 2, q_hi = (c1 - 1 - kPC + 4) >> 2;  // c0 - kPC + 4 >= 0 (kPC = 4)
+  const int q0 = q_lo + blockIdx.y * kUpGroups;
+  if (q0 > q_hi) return;
+  const int q1 = min(q0 + kUpGroups - 1, q_hi);
   const float* src = T2 + plane * (long long)hB * wC + xx;
-  float acc = 0.f;
+  float* dst = SC + plane * (long long)hC * wC + xx;
+  float win[10], o[4];
 #pragma unroll
-  for (int t = 0; t <= 2 * kTU; ++t)
-    acc = fmaf(uw.w[ph][t], __ldg(src + (long long)min(max(j0 - kTU + t, 0), hB - 1) * wC), acc);
-  SC[(plane * hC + jc) * (long long)wC + xx] = acc;
+  for (int t = 1; t < 10; ++t) win[t] = __ldg(src + (long long)min(max(q0 + kPB - 6 + t, 0), hB - 1) * wC);
+  for (int q = q0; q <= q1; ++q) {
+#pragma unroll
+    for (int t = 0; t < 9; ++t) win[t] = win[t + 1];
+    win[9] = __ldg(src + (long long)min(max(q + kPB + 4, 0), hB - 1) * wC);
+    up_bc_group(win, uw, o);
+#pragma unroll
+    for (int ph = 0; ph < 4; ++ph) {
+      const int jc = 4 * q + ph + kPC - 4;
+      if (jc >= c0 && jc < c1) dst[(long long)jc * wC] = o[ph];
+    }
+  }
 }
 
 // ---- K5: x4 Lagrange upsample of every scale's surround + MSRCR epilogue -------------------------

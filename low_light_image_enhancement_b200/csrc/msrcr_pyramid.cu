@@ -429,9 +429,9 @@ int msrcr_pyramid_run(llie_ctx* ctx, const float* in, float* out, int n, int h, 
       dim3 gx((unsigned)((long long)planes * hB), ceil_div(wB, 128)), gy(ceil_div(wB, 128), ceil_div(hB, 4), planes);
       LLIE_LAUNCH(ctx, st, "fir_x_kernel", fir_x_kernel<false><<<gx, 128, sm, st>>>((const float*)dB, (float*)dBt, taps, r, wB, 1, 1.f, 0.f, planes * hB, 0, 0));
       LLIE_LAUNCH(ctx, st, "fir_y_kernel", fir_y_kernel<<<gy, 128, 0, st>>>((const float*)dBt, (float*)dSB, taps, r, hB, wB, 0, hB, 0, hB, 0, hB));
-      dim3 ux(ceil_div((long long)hB * wC, 256), 1, planes), uy(ceil_div((long long)hC * wC, 256), 1, planes);
+      dim3 ux(ceil_div((long long)hB * up_bc_x_groups(wC), 256), 1, planes), uy(ceil_div(wC, 128), up_bc_y_chunks(0, hC), planes);
       LLIE_LAUNCH(ctx, st, "up_bc_x_kernel", up_bc_x_kernel<<<ux, 256, 0, st>>>((const float*)dSB, (float*)dT2, hB, wB, wC, 0, hB, pl->uw));
-      LLIE_LAUNCH(ctx, st, "up_bc_y_kernel", up_bc_y_kernel<<<uy, 256, 0, st>>>((const float*)dT2, sc, hB, hC, wC, 0, hC, pl->uw));
+      LLIE_LAUNCH(ctx, st, "up_bc_y_kernel", up_bc_y_kernel<<<uy, 128, 0, st>>>((const float*)dT2, sc, hB, hC, wC, 0, hC, pl->uw));
     }
   }
   LLIE_TRY(final_passes(ctx, st, pl, p, in, out, v, vec, nhwc, n, h, w, 0, 0, h, hC, wC, (const float*)dSC, c_elems,
@@ -612,9 +612,9 @@ int tiled_phase_b(llie_ctx* ctx, int d, int n_dev, llie_ctx* const* ctxs, const 
       dim3 gx(3 * (x1 - x0), ceil_div(wB, 128)), gy(ceil_div(wB, 128), ceil_div(g.t_hi - g.t_lo, 4), 3);
       LLIE_LAUNCH(ctx, st, "fir_x_kernel", fir_x_kernel<false><<<gx, 128, sm, st>>>(b.B, b.Bt, taps, r, wB, 1, 1.f, 0.f, x1 - x0, hB, x0));
       LLIE_LAUNCH(ctx, st, "fir_y_kernel", fir_y_kernel<<<gy, 128, 0, st>>>(b.Bt, b.SB, taps, r, hB, wB, 0, hB, g.t_lo, g.t_hi - g.t_lo, g.t_lo, hB));
-      dim3 ux(ceil_div((long long)(g.t_hi - g.t_lo) * wC, 256), 1, 3), uy(ceil_div((long long)(g.s_hi - g.s_lo) * wC, 256), 1, 3);
+      dim3 ux(ceil_div((long long)(g.t_hi - g.t_lo) * up_bc_x_groups(wC), 256), 1, 3), uy(ceil_div(wC, 128), up_bc_y_chunks(g.s_lo, g.s_hi), 3);
       LLIE_LAUNCH(ctx, st, "up_bc_x_kernel", up_bc_x_kernel<<<ux, 256, 0, st>>>(b.SB, b.T2, hB, wB, wC, g.t_lo, g.t_hi, pl->uw));
-      LLIE_LAUNCH(ctx, st, "up_bc_y_kernel", up_bc_y_kernel<<<uy, 256, 0, st>>>(b.T2, sc, hB, hC, wC, g.s_lo, g.s_hi, pl->uw));
+      LLIE_LAUNCH(ctx, st, "up_bc_y_kernel", up_bc_y_kernel<<<uy, 128, 0, st>>>(b.T2, sc, hB, hC, wC, g.s_lo, g.s_hi, pl->uw));
     }
   }
   const ImgView v = make_view(LLIE_NHWC, 3, g.R1 - g.R0, W);
