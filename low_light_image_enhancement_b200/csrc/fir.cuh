@@ -103,5 +103,92 @@ __global__ void __launch_bounds__(128) fir_y_kernel(const float* __restrict__ in
     if (yb + q < out_rows) dst[(long long)(yb + q) * RW] = acc[q];
 }
 
+// ---- planar (C = 1) variants for the low-resolution levels of the cascade ------------------------
+// Eight outputs per thread and the tap loop unrolled by eight, so that the sliding taps sit in eight registers
+// whose roles rotate at compile time: per eight input samples 8 loads + 8 tap loads + 64 FFMA (the generic
+// kernels above spend 3 in 4 instructions on bookkeeping, and fir_x_kernel keeps only 32 of 128 threads busy at
+// C = 1).  Every output accumulates its taps strictly in order t = 0 .. 2r, whatever its position in the
+// thread's group of eight, so results do not depend on how rows / columns are grouped (row-tiled == whole).
+constexpr int kFir8 = 8;
+constexpr int kFirX8Tile = 128 * kFir8;  // pixels per CTA of fir_x8_kernel
+__host__ __device__ inline int fir8_steps(int r) { return (2 * r + kFir8 + 7) & ~7; }
+__host__ __device__ inline size_t fir_x8_smem(int r) {
+  const int seg = kFirX8Tile + fir8_steps(r);
+  return (size_t)(seg + (seg >> 3) + 1 + fir8_steps(r)) * sizeof(float);
+}
+
+// Row addressing as fir_x_kernel.  Shared memory: the clamped input segment, one pad float after every
+// eight (thread g reads element 8 g + u: bank 9 g + ..., conflict-free), then the zero-padded taps.
+__global__ void __launch_bounds__(128) fir_x8_kernel(const float* __restrict__ in, float* __restrict__ out,
+                                                     const float* __restrict__ taps, int r, int W,
+                                                     int rows_per_plane, int plane_rows, int row_lo) {
+  extern __shared__ float seg[];
+  const int x0 = blockIdx.y * kFirX8Tile;
+  const int pl = blockIdx.x / rows_per_plane;
+  const long long row = (long long)pl * plane_rows + row_lo + (blockIdx.x - pl * rows_per_plane);
+  const float* src = in + row * (long long)W;
+  const int n_steps = fir8_steps(r);
+  const int tile = min(kFirX8Tile, (W - x0 + 7) & ~7);
+  const int seg_px = tile + n_steps;
+  float* stap = seg + seg_px + (seg_px >> 3) + 1;
+  for (int i = threadIdx.x; i < seg_px; i += blockDim.x) seg[i + (i >> 3)] = __ldg(src + min(max(x0 - r + i, 0), W - 1));
+  for (int i = threadIdx.x; i < n_steps; i += blockDim.x) stap[i] = (i <= 2 * r) ? __ldg(taps + i) : 0.f;
+  __syncthreads();
+  const int g = threadIdx.x;
+  if (g * kFir8 >= tile) return;
+  float acc[kFir8], k[kFir8];
+#pragma unroll
+  for (int q = 0; q < kFir8; ++q) acc[q] = 0.f, k[q] = 0.f;
+  const float* sg = seg + g * 9;  // element 8 g of the padded segment
+  for (int u0 = 0; u0 < n_steps; u0 += 8) {
+    const float* sb = sg + u0 + (u0 >> 3);
+#pragma unroll
+    for (int s = 0; s < 8; ++s) {
+      const float v = sb[s];
+      k[s] = stap[u0 + s];
+#pragma unroll
+      for (int q = 0; q < kFir8; ++q) acc[q] = fmaf(k[(s - q) & 7], v, acc[q]);
+    }
+  }
+  float* dst = out + row * (long long)W + x0 + g * kFir8;
+#pragma unroll
+  for (int q = 0; q < kFir8; ++q)
+    if (x0 + g * kFir8 + q < W) dst[q] = acc[q];
+}
+
+// Row addressing as fir_y_kernel; 8 consecutive rows per thread, one column per lane (coalesced).
+__global__ void __launch_bounds__(128) fir_y8_kernel(const float* __restrict__ in, float* __restrict__ out,
+                                                     const float* __restrict__ taps, int r, int H, int RW,
+                                                     int in_row0, int in_rows, int out_row0, int out_rows,
+                                                     int out_buf_row0, int out_plane_rows) {
+  extern __shared__ float stap[];
+  const int n_steps = fir8_steps(r);
+  for (int i = threadIdx.x; i < n_steps; i += blockDim.x) stap[i] = (i <= 2 * r) ? __ldg(taps + i) : 0.f;
+  __syncthreads();
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= RW) return;
+  const int yb = blockIdx.y * kFir8;       // first output buffer row of this thread
+  const int y0 = out_row0 + yb;            // its level row
+  const long long plane = blockIdx.z;
+  const float* src = in + plane * (long long)in_rows * RW + j;
+  float acc[kFir8], k[kFir8];
+#pragma unroll
+  for (int q = 0; q < kFir8; ++q) acc[q] = 0.f, k[q] = 0.f;
+  for (int u0 = 0; u0 < n_steps; u0 += 8) {
+#pragma unroll
+    for (int s = 0; s < 8; ++s) {
+      const int y = min(max(y0 - r + u0 + s, 0), H - 1) - in_row0;
+      const float v = __ldg(src + (long long)y * RW);
+      k[s] = stap[u0 + s];
+#pragma unroll
+      for (int q = 0; q < kFir8; ++q) acc[q] = fmaf(k[(s - q) & 7], v, acc[q]);
+    }
+  }
+  float* dst = out + (plane * (long long)out_plane_rows + out_buf_row0) * RW + j;
+#pragma unroll
+  for (int q = 0; q < kFir8; ++q)
+    if (yb + q < out_rows) dst[(long long)(yb + q) * RW] = acc[q];
+}
+
 }  // namespace
 }  // namespace llie

@@ -419,16 +419,16 @@ int msrcr_pyramid_run(llie_ctx* ctx, const float* in, float* out, int n, int h, 
     const ScalePlan& sp = pl->scales[k];
     const float* taps = pl->d_taps + pl->tap_off[k];
     const int r = sp.radius_low;
-    const size_t sm = (size_t)(128 + 2 * r + 3) * sizeof(float);
+    const size_t smx = fir_x8_smem(r), smy = (size_t)fir8_steps(r) * sizeof(float);
     float* sc = (float*)dSC + (size_t)k * c_elems;
     if (sp.level == 0) {
-      dim3 gx((unsigned)((long long)planes * hC), ceil_div(wC, 128)), gy(ceil_div(wC, 128), ceil_div(hC, 4), planes);
-      LLIE_LAUNCH(ctx, st, "fir_x_kernel", fir_x_kernel<false><<<gx, 128, sm, st>>>((const float*)dC, (float*)dCt, taps, r, wC, 1, 1.f, 0.f, planes * hC, 0, 0));
-      LLIE_LAUNCH(ctx, st, "fir_y_kernel", fir_y_kernel<<<gy, 128, 0, st>>>((const float*)dCt, sc, taps, r, hC, wC, 0, hC, 0, hC, 0, hC));
+      dim3 gx((unsigned)((long long)planes * hC), ceil_div(wC, kFirX8Tile)), gy(ceil_div(wC, 128), ceil_div(hC, kFir8), planes);
+      LLIE_LAUNCH(ctx, st, "fir_x_kernel", fir_x8_kernel<<<gx, 128, smx, st>>>((const float*)dC, (float*)dCt, taps, r, wC, planes * hC, 0, 0));
+      LLIE_LAUNCH(ctx, st, "fir_y_kernel", fir_y8_kernel<<<gy, 128, smy, st>>>((const float*)dCt, sc, taps, r, hC, wC, 0, hC, 0, hC, 0, hC));
     } else {
-      dim3 gx((unsigned)((long long)planes * hB), ceil_div(wB, 128)), gy(ceil_div(wB, 128), ceil_div(hB, 4), planes);
-      LLIE_LAUNCH(ctx, st, "fir_x_kernel", fir_x_kernel<false><<<gx, 128, sm, st>>>((const float*)dB, (float*)dBt, taps, r, wB, 1, 1.f, 0.f, planes * hB, 0, 0));
-      LLIE_LAUNCH(ctx, st, "fir_y_kernel", fir_y_kernel<<<gy, 128, 0, st>>>((const float*)dBt, (float*)dSB, taps, r, hB, wB, 0, hB, 0, hB, 0, hB));
+      dim3 gx((unsigned)((long long)planes * hB), ceil_div(wB, kFirX8Tile)), gy(ceil_div(wB, 128), ceil_div(hB, kFir8), planes);
+      LLIE_LAUNCH(ctx, st, "fir_x_kernel", fir_x8_kernel<<<gx, 128, smx, st>>>((const float*)dB, (float*)dBt, taps, r, wB, planes * hB, 0, 0));
+      LLIE_LAUNCH(ctx, st, "fir_y_kernel", fir_y8_kernel<<<gy, 128, smy, st>>>((const float*)dBt, (float*)dSB, taps, r, hB, wB, 0, hB, 0, hB, 0, hB));
       dim3 ux(ceil_div((long long)hB * up_bc_x_groups(wC), 256), 1, planes), uy(ceil_div(wC, 128), up_bc_y_chunks(0, hC), planes);
       LLIE_LAUNCH(ctx, st, "up_bc_x_kernel", up_bc_x_kernel<<<ux, 256, 0, st>>>((const float*)dSB, (float*)dT2, hB, wB, wC, 0, hB, pl->uw));
       LLIE_LAUNCH(ctx, st, "up_bc_y_kernel", up_bc_y_kernel<<<uy, 128, 0, st>>>((const float*)dT2, sc, hB, hC, wC, 0, hC, pl->uw));
@@ -600,18 +600,18 @@ int tiled_phase_b(llie_ctx* ctx, int d, int n_dev, llie_ctx* const* ctxs, const 
     const ScalePlan& sp = pl->scales[k];
     const float* taps = pl->d_taps + pl->tap_off[k];
     const int r = sp.radius_low;
-    const size_t sm = (size_t)(128 + 2 * r + 3) * sizeof(float);
+    const size_t smx = fir_x8_smem(r), smy = (size_t)fir8_steps(r) * sizeof(float);
     float* sc = b.SC + (size_t)k * c_elems;
     if (sp.level == 0) {
       const int x0 = clampi(g.s_lo - r, 0, hC), x1 = clampi(g.s_hi + r, 0, hC);
-      dim3 gx(3 * (x1 - x0), ceil_div(wC, 128)), gy(ceil_div(wC, 128), ceil_div(g.s_hi - g.s_lo, 4), 3);
-      LLIE_LAUNCH(ctx, st, "fir_x_kernel", fir_x_kernel<false><<<gx, 128, sm, st>>>(b.C, b.Ct, taps, r, wC, 1, 1.f, 0.f, x1 - x0, hC, x0));
-      LLIE_LAUNCH(ctx, st, "fir_y_kernel", fir_y_kernel<<<gy, 128, 0, st>>>(b.Ct, sc, taps, r, hC, wC, 0, hC, g.s_lo, g.s_hi - g.s_lo, g.s_lo, hC));
+      dim3 gx(3 * (x1 - x0), ceil_div(wC, kFirX8Tile)), gy(ceil_div(wC, 128), ceil_div(g.s_hi - g.s_lo, kFir8), 3);
+      LLIE_LAUNCH(ctx, st, "fir_x_kernel", fir_x8_kernel<<<gx, 128, smx, st>>>(b.C, b.Ct, taps, r, wC, x1 - x0, hC, x0));
+      LLIE_LAUNCH(ctx, st, "fir_y_kernel", fir_y8_kernel<<<gy, 128, smy, st>>>(b.Ct, sc, taps, r, hC, wC, 0, hC, g.s_lo, g.s_hi - g.s_lo, g.s_lo, hC));
     } else {
       const int x0 = clampi(g.t_lo - r, 0, hB), x1 = clampi(g.t_hi + r, 0, hB);
-      dim3 gx(3 * (x1 - x0), ceil_div(wB, 128)), gy(ceil_div(wB, 128), ceil_div(g.t_hi - g.t_lo, 4), 3);
-      LLIE_LAUNCH(ctx, st, "fir_x_kernel", fir_x_kernel<false><<<gx, 128, sm, st>>>(b.B, b.Bt, taps, r, wB, 1, 1.f, 0.f, x1 - x0, hB, x0));
-      LLIE_LAUNCH(ctx, st, "fir_y_kernel", fir_y_kernel<<<gy, 128, 0, st>>>(b.Bt, b.SB, taps, r, hB, wB, 0, hB, g.t_lo, g.t_hi - g.t_lo, g.t_lo, hB));
+      dim3 gx(3 * (x1 - x0), ceil_div(wB, kFirX8Tile)), gy(ceil_div(wB, 128), ceil_div(g.t_hi - g.t_lo, kFir8), 3);
+      LLIE_LAUNCH(ctx, st, "fir_x_kernel", fir_x8_kernel<<<gx, 128, smx, st>>>(b.B, b.Bt, taps, r, wB, x1 - x0, hB, x0));
+      LLIE_LAUNCH(ctx, st, "fir_y_kernel", fir_y8_kernel<<<gy, 128, smy, st>>>(b.Bt, b.SB, taps, r, hB, wB, 0, hB, g.t_lo, g.t_hi - g.t_lo, g.t_lo, hB));
       dim3 ux(ceil_div((long long)(g.t_hi - g.t_lo) * up_bc_x_groups(wC), 256), 1, 3), uy(ceil_div(wC, 128), up_bc_y_chunks(g.s_lo, g.s_hi), 3);
       LLIE_LAUNCH(ctx, st, "up_bc_x_kernel", up_bc_x_kernel<<<ux, 256, 0, st>>>(b.SB, b.T2, hB, wB, wC, g.t_lo, g.t_hi, pl->uw));
       LLIE_LAUNCH(ctx, st, "up_bc_y_kernel", up_bc_y_kernel<<<uy, 128, 0, st>>>(b.T2, sc, hB, hC, wC, g.s_lo, g.s_hi, pl->uw));
