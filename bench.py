@@ -58,6 +58,9 @@ MSRCR_NORTH_STAR_BYTES_PER_PX = 108      # two-pass separable data flow (SURVEY.
 #   down4_rows_kernel : reads x (12 B), writes the stride-4 (vertical) partial V (12/4 B)
 #   msrcr_final_kernel: reads x (12 B), writes out (12 B), reads 3 scales x 3 ch of stride-4 surround (36/16 B)
 MSRCR_KERNEL_BYTES_PER_PX = {"down4_rows_kernel": 12 + 3.0, "msrcr_final_kernel": 12 + 12 + 36 / 16.0}
+# the same kernels on 8-bit images: the image costs 1 byte per sample
+MSRCR_KERNEL_BYTES_PER_PX_U8 = {"down4_rows_kernel": 3 + 3.0, "msrcr_final_kernel": 3 + 3 + 36 / 16.0}
+MSRCR_NORTH_STAR_BYTES_PER_PX_U8 = 3 + 36 + 36 + 3 + 3   # the same two-pass data flow with uint8 image I/O
 
 
 def load_peaks():
@@ -238,23 +241,25 @@ def tc_roofline(prof, px_per_step, steps, peaks, split=False):
             "kernel_ms_per_step": {k: round(v[1] / steps, 4) for k, v in sorted(prof.items())}}
 
 
-def hbm_roofline(prof, px_per_step, steps, peaks, total_ms_per_step):
-    cand = {k: v for k, v in prof.items() if k in MSRCR_KERNEL_BYTES_PER_PX}
+def hbm_roofline(prof, px_per_step, steps, peaks, total_ms_per_step, u8=False):
+    kbytes = MSRCR_KERNEL_BYTES_PER_PX_U8 if u8 else MSRCR_KERNEL_BYTES_PER_PX
+    ns_bytes = MSRCR_NORTH_STAR_BYTES_PER_PX_U8 if u8 else MSRCR_NORTH_STAR_BYTES_PER_PX
+    cand = {k: v for k, v in prof.items() if k in kbytes}
     if not cand:
         return None
     dom = max(cand, key=lambda k: cand[k][1])
     cnt, ms = cand[dom]
-    ach = MSRCR_KERNEL_BYTES_PER_PX[dom] * px_per_step * steps / (ms * 1e-3) / 1e9
-    ns = MSRCR_NORTH_STAR_BYTES_PER_PX * px_per_step / (total_ms_per_step * 1e-3) / 1e9
+    ach = kbytes[dom] * px_per_step * steps / (ms * 1e-3) / 1e9
+    ns = ns_bytes * px_per_step / (total_ms_per_step * 1e-3) / 1e9
     return {"bound": "hbm", "kernel": dom, "achieved": round(ach, 1), "peak": peaks["hbm"], "unit": "GB/s",
             "frac": round(ach / peaks["hbm"], 4), "traffic": None, "peak_source": f"{peaks['source']} copy",
-            "kernel_bytes_per_px": MSRCR_KERNEL_BYTES_PER_PX[dom],
+            "kernel_bytes_per_px": kbytes[dom],
             "launches": cnt, "avg_launch_ms": round(ms / cnt, 4),
-            "whole_msrcr_at_108B_per_px": {"achieved": round(ns, 1), "frac": round(ns / peaks["hbm"], 4)},
+            f"whole_msrcr_at_{ns_bytes}B_per_px": {"achieved": round(ns, 1), "frac": round(ns / peaks["hbm"], 4)},
             "kernel_ms_per_step": {k: round(v[1] / steps, 4) for k, v in sorted(prof.items())}}
 
 
-def gpu_workload(dist, name, steps, warmup, peaks, with_e2e=True, with_cpu=True):
+def gpu_workload(dist, name, steps, warmup, peaks, with_e2e=True, with_cpu=True, io="f32"):
     import torch
     import low_light_image_enhancement_b200 as L
     from low_light_image_enhancement_b200.api import _enhancer
@@ -285,6 +290,9 @@ def gpu_workload(dist, name, steps, warmup, peaks, with_e2e=True, with_cpu=True)
         flush = torch.empty(64 << 20, dtype=torch.float32, device=dev)      # 256 MiB > 126 MB L2
     distinct = min(n_local, 8)
     x = synth_lowlight_batch(distinct, h, w, seed=1000 * int(name[1]) + rank, device=dev)
+    if io == "u8":   # 8-bit images: a byte b means b / 255
+        x = (x * 255.0).round().clamp(0, 255).to(torch.uint8)
+        label += "; uint8 image I/O"
     if distinct < n_local:
         x = x.repeat((n_local + distinct - 1) // distinct, 1, 1, 1)[:n_local].contiguous()
     y = torch.empty_like(x)
@@ -295,24 +303,26 @@ def gpu_workload(dist, name, steps, warmup, peaks, with_e2e=True, with_cpu=True)
 
     ms, prof, launches, clocks = run_timed(dist, enh, step, steps, warmup, flush)
     res = {"workload": label, "ms_per_step": round(ms, 4), "value": round(px_total / ms / 1e3, 1), "scaling": scaling,
-           "dtype": dtype, "frames_total": total_frames, "frames_this_rank": n_local, "clocks": clocks,
+           "dtype": dtype, "io": io, "frames_total": total_frames, "frames_this_rank": n_local, "clocks": clocks,
            "gpu_launches": int(dist.reduce(launches, "sum")),
            "l2": "inputs+activations per step exceed the 126 MB L2" if flush is None else "256 MiB flush between timed steps"}
     res["roofline"] = (tc_roofline(prof, px_local, steps, peaks, split=(dtype != "bf16")) if method == "zero_dce"
-                       else hbm_roofline(prof, px_local, steps, peaks, ms))
+                       else hbm_roofline(prof, px_local, steps, peaks, ms, u8=(io == "u8")))
     if with_e2e:
-        xh = torch.empty(x.shape, dtype=torch.float32, pin_memory=True)
+        xh = torch.empty(x.shape, dtype=x.dtype, pin_memory=True)
         xh.copy_(x)
-        yh = torch.empty(x.shape, dtype=torch.float32, pin_memory=True)
+        yh = torch.empty(x.shape, dtype=x.dtype, pin_memory=True)
         e2e_steps = max(1, min(steps, 5))
         ms_e = run_e2e(dist, lambda: enh.enhance(xh, method, params, out=yh), e2e_steps, warmup)
         res["e2e"] = {"value": round(px_total / ms_e / 1e3, 1), "unit": "Mpixel/s", "ms_per_step": round(ms_e, 3),
-                      "h2d_bytes_per_step": int(xh.numel() * 4 * world), "d2h_bytes_per_step": int(yh.numel() * 4 * world),
+                      "h2d_bytes_per_step": int(xh.numel() * xh.element_size() * world),
+                      "d2h_bytes_per_step": int(yh.numel() * yh.element_size() * world),
                       "steps": e2e_steps, "api": "enhance(pinned torch CPU tensor, out=pinned) -> staged 3-stream pipeline"}
         if not torch.equal(yh, y.cpu()):
             res["e2e"]["warning"] = "host-path result differs from device-path result"
     if with_cpu and rank == 0:
-        res["cpu_baseline"] = cpu_baseline(name, x[0].cpu().numpy(), params)
+        x0 = x[0].cpu().numpy()
+        res["cpu_baseline"] = cpu_baseline(name, x0 if io == "f32" else x0.astype(np.float32) / np.float32(255), params)
     return res
 
 
@@ -470,6 +480,7 @@ def main():
     ap.add_argument("--no-also", action="store_true", help="skip the short secondary workloads")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--io", default="f32", choices=["f32", "u8"], help="image I/O type of the c2 / c3 workloads")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     if args.impl == "reference":
@@ -490,18 +501,21 @@ def main():
             print(json.dumps(line), flush=True)
         dist.close()
         return
-    main_res = gpu_workload(dist, args.workload, args.steps, args.warmup, peaks, not args.no_e2e, not args.no_cpu)
+    main_res = gpu_workload(dist, args.workload, args.steps, args.warmup, peaks, not args.no_e2e, not args.no_cpu, io=args.io)
     also = {}
     if not args.no_also and args.workload == "c2":
         for other in ("c3", "c1"):
             r = gpu_workload(dist, other, max(3, args.steps // 2), 3, peaks, with_e2e=False, with_cpu=(dist.world == 1))
             also[other] = r
+        # the same two workloads on 8-bit images, end to end from pinned host memory
+        for other in ("c2", "c3"):
+            also[other + "_u8"] = gpu_workload(dist, other, 3, 3, peaks, with_e2e=True, with_cpu=False, io="u8")
     if dist.rank == 0:
         line = {"metric": "Mpixel/s", "value": main_res["value"], "unit": "Mpixel/s", "n_gpus": dist.world,
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": main_res["ms_per_step"],
                 "higher_is_better": True, "scaling": main_res["scaling"], "vs_baseline": None,
                 "dtype": main_res["dtype"], "data": "synthetic (device-generated low-light frames, random-init He weights)",
-                "config": {"workload": main_res["workload"], "frames_total": main_res["frames_total"],
+                "config": {"workload": main_res["workload"], "image_io": main_res["io"], "frames_total": main_res["frames_total"],
                            "l2": main_res["l2"], "peaks": peaks},
                 "roofline": main_res["roofline"], "cpu_baseline": main_res.get("cpu_baseline"),
                 "e2e": main_res.get("e2e"), "clocks": main_res["clocks"], "gpu_launches": main_res["gpu_launches"]}

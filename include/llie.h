@@ -108,6 +108,13 @@ int llie_profile_end(llie_ctx* ctx, char* buf, size_t buflen);
 int llie_msrcr_f32(llie_ctx* ctx, const float* in, float* out, int n, int h, int w, int layout,
                    const llie_msrcr_params* params, void* stream);
 
+/* SURVEY.md 8(f) rank 1 -- 8-bit images: in/out are n*h*w*3 uint8 device arrays in `layout`; a byte b means the
+ * value b/255 and the result is stored as rint(255 * value).  The conversions happen inside the first and last
+ * kernels of the path (no extra pass over the image), so the image costs 1 byte per sample on HBM and on PCIe.
+ * LLIE_BLUR_PYRAMID only. */
+int llie_msrcr_u8(llie_ctx* ctx, const uint8_t* in, uint8_t* out, int n, int h, int w, int layout,
+                  const llie_msrcr_params* params, void* stream);
+
 /* Host-side planner of the pyramid blur, exposed so that CPU tests can check it without a
  * GPU: for `sigma`/`truncate` returns the cascade level's stride (4 or 16), the low-res
  * Gaussian's sigma and radius, and the L1 distance between the cascade's effective kernel
@@ -124,6 +131,11 @@ int llie_dce_set_weights(llie_ctx* ctx, const float* host_packed, size_t count);
  * layout family: NHWC -> (N,H,W,24), NCHW -> (N,24,H,W)). */
 int llie_dce_forward(llie_ctx* ctx, const float* in, float* out, float* maps_or_null, int n, int h, int w,
                      int layout, const llie_dce_params* params, void* stream);
+
+/* 8-bit variant of llie_dce_forward (same conventions as llie_msrcr_u8; LLIE_BF16 precision only; the curve
+ * maps, if requested, stay fp32). */
+int llie_dce_forward_u8(llie_ctx* ctx, const uint8_t* in, uint8_t* out, float* maps_or_null, int n, int h, int w,
+                        int layout, const llie_dce_params* params, void* stream);
 
 /* Test hook: after a LLIE_BF16 or LLIE_F32 forward, copies inter-layer activation `which` (1..6 = x1..x6 of
  * SURVEY.md 9.2) of frame `frame` of the last processed chunk to HOST memory as fp32 [32][h][w]. */

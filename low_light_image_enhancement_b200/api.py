@@ -202,13 +202,13 @@ class Enhancer:
 
     # -- device-pointer entry points (zero-copy for torch CUDA tensors) -----------------------
     def msrcr_device(self, x: torch.Tensor, out: torch.Tensor, n, h, w, layout, p: MsrcrParams, stream_ptr):
-        _lib.check(self._lib.llie_msrcr_f32(self._h, x.data_ptr(), out.data_ptr(), n, h, w, layout, C.byref(p),
-                                            stream_ptr))
+        fn = self._lib.llie_msrcr_u8 if x.dtype == torch.uint8 else self._lib.llie_msrcr_f32
+        _lib.check(fn(self._h, x.data_ptr(), out.data_ptr(), n, h, w, layout, C.byref(p), stream_ptr))
 
     def dce_device(self, x, out, maps, n, h, w, layout, p: DceParams, stream_ptr):
-        _lib.check(self._lib.llie_dce_forward(self._h, x.data_ptr(), out.data_ptr(),
-                                              maps.data_ptr() if maps is not None else None, n, h, w, layout,
-                                              C.byref(p), stream_ptr))
+        fn = self._lib.llie_dce_forward_u8 if x.dtype == torch.uint8 else self._lib.llie_dce_forward
+        _lib.check(fn(self._h, x.data_ptr(), out.data_ptr(), maps.data_ptr() if maps is not None else None,
+                      n, h, w, layout, C.byref(p), stream_ptr))
 
     def dce_curves_device(self, x, maps, out, n, h, w, layout, p: DceParams, stream_ptr):
         _lib.check(self._lib.llie_dce_curves(self._h, x.data_ptr(), maps.data_ptr(), out.data_ptr(), n, h, w,
@@ -223,8 +223,8 @@ class Enhancer:
         if not is_np and not isinstance(images, torch.Tensor):
             raise TypeError("images must be a numpy.ndarray or a torch.Tensor")
         t = torch.from_numpy(images) if is_np else images
-        if t.dtype != torch.float32:
-            raise TypeError(f"images must be float32, got {t.dtype}")
+        if t.dtype not in (torch.float32, torch.uint8):
+            raise TypeError(f"images must be float32 (values in [0,1]) or uint8 (byte / 255), got {t.dtype}")
         if not t.is_contiguous():
             raise ValueError("images must be contiguous")
         n, h, w, layout, batched = _resolve_layout(t.shape, params.get("layout"))
@@ -261,17 +261,19 @@ class Enhancer:
         y_t = self._host_pipeline(t, n, h, w, layout, mp, dp, want_maps, out, is_np)
         return y_t
 
-    def _pinned(self, name: str, nelem: int) -> torch.Tensor:
+    def _pinned(self, name: str, nelem: int, dtype=torch.float32) -> torch.Tensor:
+        name = f"{name}.{dtype}"
         buf = self._stage.get(name)
         if buf is None or buf.numel() < nelem:
-            buf = torch.empty(nelem, dtype=torch.float32, pin_memory=True)
+            buf = torch.empty(nelem, dtype=dtype, pin_memory=True)
             self._stage[name] = buf
         return buf[:nelem]
 
-    def _devbuf(self, name: str, nelem: int) -> torch.Tensor:
+    def _devbuf(self, name: str, nelem: int, dtype=torch.float32) -> torch.Tensor:
+        name = f"{name}.{dtype}"
         buf = self._stage.get(name)
         if buf is None or buf.numel() < nelem:
-            buf = torch.empty(nelem, dtype=torch.float32, device=f"cuda:{self.device}")
+            buf = torch.empty(nelem, dtype=dtype, device=f"cuda:{self.device}")
             self._stage[name] = buf
         return buf[:nelem]
 
@@ -279,8 +281,9 @@ class Enhancer:
         dev = torch.device("cuda", self.device)
         frame = h * w * 3
         x_flat = t.reshape(-1)
+        dt = t.dtype
         if out is None:
-            y_host = torch.empty(t.shape, dtype=torch.float32)
+            y_host = torch.empty(t.shape, dtype=dt)
         else:
             y_host = torch.from_numpy(out) if isinstance(out, np.ndarray) else out
             _check_out(y_host, t)
@@ -291,17 +294,17 @@ class Enhancer:
             maps_host = torch.empty(mshape if t.dim() == 4 else mshape[1:], dtype=torch.float32)
         in_pinned, out_pinned = x_flat.is_pinned(), y_flat.is_pinned()
         # chunk: about 64 MiB of input per stage, at least one frame
-        per = max(1, min(n, (64 << 20) // (frame * 4)))
+        per = max(1, min(n, (64 << 20) // (frame * t.element_size())))
         n_chunks = math.ceil(n / per)
         if self._copy_stream is None:
             self._copy_stream = [torch.cuda.Stream(dev) for _ in range(2)]
         h2d, d2h = self._copy_stream
         comp = torch.cuda.current_stream(dev)
-        xd = [self._devbuf(f"x{i}", per * frame) for i in range(2)]
-        yd = [self._devbuf(f"y{i}", per * frame) for i in range(2)]
+        xd = [self._devbuf(f"x{i}", per * frame, dt) for i in range(2)]
+        yd = [self._devbuf(f"y{i}", per * frame, dt) for i in range(2)]
         md = [self._devbuf(f"m{i}", per * frame * 8) for i in range(2)] if want_maps else [None, None]
-        xp = None if in_pinned else [self._pinned(f"xp{i}", per * frame) for i in range(2)]
-        yp = None if out_pinned else [self._pinned(f"yp{i}", per * frame) for i in range(2)]
+        xp = None if in_pinned else [self._pinned(f"xp{i}", per * frame, dt) for i in range(2)]
+        yp = None if out_pinned else [self._pinned(f"yp{i}", per * frame, dt) for i in range(2)]
         ev_in = [torch.cuda.Event() for _ in range(2)]
         ev_comp = [torch.cuda.Event() for _ in range(2)]
         ev_out = [torch.cuda.Event() for _ in range(2)]
@@ -365,8 +368,8 @@ def _stream_ptr(stream: torch.cuda.Stream) -> int:
 
 
 def _check_out(y: torch.Tensor, t: torch.Tensor) -> None:
-    if y.shape != t.shape or y.dtype != torch.float32 or not y.is_contiguous() or y.device != t.device:
-        raise ValueError("out must match images in shape, dtype (float32), device and be contiguous")
+    if y.shape != t.shape or y.dtype != t.dtype or not y.is_contiguous() or y.device != t.device:
+        raise ValueError("out must match images in shape, dtype, device and be contiguous")
     if y.data_ptr() == t.data_ptr():
         raise ValueError("out must not alias images")
 
@@ -470,7 +473,8 @@ def msrcr_tiled_last_ms(shards: Sequence[torch.Tensor]) -> list[float]:
 def enhance(images, method: str, params: dict | None = None, *, out=None, device: int | None = None):
     """Enhance a low-light image batch on a B200.
 
-    images : numpy.ndarray or torch.Tensor, float32 in [0, 1], shape (H,W,3), (N,H,W,3) or
+    images : numpy.ndarray or torch.Tensor, float32 in [0, 1] or uint8 (a byte b means b / 255; the result is
+             rint(255 * value) as uint8, converted inside the first / last kernel), shape (H,W,3), (N,H,W,3) or
              (N,3,H,W) (params['layout'] = 'NHWC' | 'NCHW' when the shape is ambiguous).
              CUDA tensors are processed in place on their device and stream (zero copy); NumPy
              arrays and CPU tensors are staged through pinned memory.

@@ -143,6 +143,7 @@ struct ChainArgs {
   ImgView vx, vm;
   int iters;
   float sign;
+  int u8;  // x / y are uint8_t images (value = byte / 255; stored as rint(255 * value))
   int N, H, W, Wp, strips, segs, seg_rows, units;
 };
 
@@ -535,8 +536,13 @@ __device__ __forceinline__ void epilogue_loop(const ChainArgs& a, const Smem<GID
         if (owned) {
           const long long bx = un.n * a.vx.sn + (long long)y * a.vx.sy + (long long)x * a.vx.sx;
           float p[3];
+          if (a.u8) {
 #pragma unroll
-          for (int c = 0; c < 3; ++c) p[c] = __ldg(a.x + bx + c * a.vx.sc);
+            for (int c = 0; c < 3; ++c) p[c] = (float)__ldg(reinterpret_cast<const uint8_t*>(a.x) + bx + c * a.vx.sc) * (1.f / 255.f);
+          } else {
+#pragma unroll
+            for (int c = 0; c < 3; ++c) p[c] = __ldg(a.x + bx + c * a.vx.sc);
+          }
           float A[24];
 #pragma unroll
           for (int j = 0; j < 24; ++j) A[j] = fast_tanh(__uint_as_float(v[j]));
@@ -546,8 +552,14 @@ __device__ __forceinline__ void epilogue_loop(const ChainArgs& a, const Smem<GID
 #pragma unroll
               for (int c = 0; c < 3; ++c) p[c] = fmaf(a.sign * A[3 * it + c] * p[c], 1.f - p[c], p[c]);
             }
+          if (a.u8) {
 #pragma unroll
-          for (int c = 0; c < 3; ++c) a.y[bx + c * a.vx.sc] = p[c];
+            for (int c = 0; c < 3; ++c)
+              reinterpret_cast<uint8_t*>(a.y)[bx + c * a.vx.sc] = (uint8_t)__float2uint_rn(255.f * __saturatef(p[c]));
+          } else {
+#pragma unroll
+            for (int c = 0; c < 3; ++c) a.y[bx + c * a.vx.sc] = p[c];
+          }
           if (a.maps) {
             const long long bm = un.n * a.vm.sn + (long long)y * a.vm.sy + (long long)x * a.vm.sx;
 #pragma unroll

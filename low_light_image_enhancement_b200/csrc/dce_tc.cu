@@ -23,14 +23,15 @@ using namespace chain;
 // pixel x at column x + kPadL (all other columns stay zero from the workspace memset).
 // One thread per pixel: 12 B read, one 16 B store.
 // kSplit: channels = [r_hi g_hi b_hi r_lo g_lo b_lo 0 0] with hi = bf16(v), lo = bf16(v - hi).
-template <bool kSplit>
+template <bool kSplit, typename TIn>
 __global__ void __launch_bounds__(256)
-dce_pack_input_kernel(const float* __restrict__ x, ImgView v, __nv_bfloat16* __restrict__ out, int H, int W, int Wp) {
+dce_pack_input_kernel(const TIn* __restrict__ x, ImgView v, __nv_bfloat16* __restrict__ out, int H, int W, int Wp) {
   const int xx = blockIdx.x * blockDim.x + threadIdx.x, yy = blockIdx.y;
   const long long n = blockIdx.z;
   if (xx >= W) return;
-  const float* p = x + n * v.sn + (long long)yy * v.sy + (long long)xx * v.sx;
-  const float r = __ldg(p), g = __ldg(p + v.sc), b = __ldg(p + 2 * v.sc);
+  const TIn* p = x + n * v.sn + (long long)yy * v.sy + (long long)xx * v.sx;
+  constexpr float kIn = sizeof(TIn) == 1 ? 1.f / 255.f : 1.f;  // a byte b means b / 255
+  const float r = kIn * (float)__ldg(p), g = kIn * (float)__ldg(p + v.sc), b = kIn * (float)__ldg(p + 2 * v.sc);
   const __nv_bfloat162 rg = __floats2bfloat162_rn(r, g);
   uint4 o;
   o.x = *reinterpret_cast<const uint32_t*>(&rg);
@@ -198,8 +199,9 @@ void dce_tc_release(llie_ctx* ctx) {
 
 // split = false: bf16 operands (config 2).  split = true: hi/lo bf16 pairs, three MMAs per product -- fp32-accurate
 // results (config 1) from the same tensor-core kernel, one launch per layer.
-static int dce_forward_tc(llie_ctx* ctx, const float* in, float* out, float* maps, int n, int h, int w, int layout,
-                          const llie_dce_params& p, cudaStream_t st, bool split) {
+static int dce_forward_tc(llie_ctx* ctx, const void* in_v, void* out_v, float* maps, int n, int h, int w, int layout,
+                          const llie_dce_params& p, cudaStream_t st, bool split, bool u8 = false) {
+  const size_t esz = u8 ? 1 : 4;  // bytes per image sample
   DceWeights* dw = ctx->dce;
   LLIE_REQUIRE(dw != nullptr && dw->d_bf16 != nullptr, LLIE_E_STATE, "dce_forward: call llie_dce_set_weights first");
   DceTcPack& pk = g_packs[ctx];
@@ -227,20 +229,24 @@ static int dce_forward_tc(llie_ctx* ctx, const float* in, float* out, float* map
   const ImgView vx = make_view(layout, 3, h, w), vm = make_view(layout, 24, h, w);
   for (long long n0 = 0; n0 < n; n0 += chunk) {
     const int nb = (int)((n - n0 < chunk) ? (n - n0) : chunk);
-    const float* x = in + n0 * (long long)h * w * 3;
+    const float* x = reinterpret_cast<const float*>(static_cast<const char*>(in_v) + (size_t)n0 * h * w * 3 * esz);
     {
       dim3 grid((w + 255) / 256, h, nb);
       if (split)
         LLIE_LAUNCH(ctx, st, "dce_pack_input_split_kernel",
-                    dce_pack_input_kernel<true><<<grid, 256, 0, st>>>(x, vx, pk.xin, h, w, wp));
+                    (dce_pack_input_kernel<true, float><<<grid, 256, 0, st>>>(x, vx, pk.xin, h, w, wp)));
+      else if (u8)
+        LLIE_LAUNCH(ctx, st, "dce_pack_input_kernel",
+                    (dce_pack_input_kernel<false, uint8_t><<<grid, 256, 0, st>>>(reinterpret_cast<const uint8_t*>(x), vx, pk.xin, h, w, wp)));
       else
         LLIE_LAUNCH(ctx, st, "dce_pack_input_kernel",
-                    dce_pack_input_kernel<false><<<grid, 256, 0, st>>>(x, vx, pk.xin, h, w, wp));
+                    (dce_pack_input_kernel<false, float><<<grid, 256, 0, st>>>(x, vx, pk.xin, h, w, wp)));
     }
     ChainArgs a;
     memset(&a, 0, sizeof(a));
     a.N = nb; a.H = h; a.W = w; a.Wp = wp;
-    a.x = x; a.y = out + n0 * (long long)h * w * 3;
+    a.x = x; a.y = reinterpret_cast<float*>(static_cast<char*>(out_v) + (size_t)n0 * h * w * 3 * esz);
+    a.u8 = u8 ? 1 : 0;
     a.maps = maps ? maps + n0 * (long long)h * w * 24 : nullptr;
     a.vx = vx; a.vm = vm; a.iters = p.iters; a.sign = p.curve_sign >= 0 ? 1.f : -1.f;
     // stage slot <- layer l (0..6): weights, bias, HBM destination (nullptr = keep on chip)
@@ -299,6 +305,10 @@ static int dce_forward_tc(llie_ctx* ctx, const float* in, float* out, float* map
 int dce_forward_bf16(llie_ctx* ctx, const float* in, float* out, float* maps, int n, int h, int w, int layout,
                      const llie_dce_params& p, cudaStream_t st) {
   return dce_forward_tc(ctx, in, out, maps, n, h, w, layout, p, st, false);
+}
+int dce_forward_u8(llie_ctx* ctx, const uint8_t* in, uint8_t* out, float* maps, int n, int h, int w, int layout,
+                   const llie_dce_params& p, cudaStream_t st) {
+  return dce_forward_tc(ctx, in, out, maps, n, h, w, layout, p, st, false, true);
 }
 int dce_forward_split(llie_ctx* ctx, const float* in, float* out, float* maps, int n, int h, int w, int layout,
                       const llie_dce_params& p, cudaStream_t st) {

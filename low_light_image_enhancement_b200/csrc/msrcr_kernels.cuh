@@ -51,9 +51,11 @@ __device__ constexpr float kL4[3][4] = {{-5.4687500000e-02f, 8.2031250000e-01f, 
 // rows once, scattering each loaded value into the 8-9 output rows whose windows contain it; the
 // 9 live accumulators rotate through a 9-group (36-row) unrolled body so every index is static.
 // `x` points at image row in_row0 and holds in_rows rows (row-tiled shards); rows outside [0, H) clamp.
-template <int VEC>
+// TIn = float, or uint8_t (8-bit images; raw 0..255 values are filtered as they are and
+// the 1/255 is folded into K1b's affine map).
+template <int VEC, typename TIn>
 __global__ void __launch_bounds__(128)
-down4_rows_kernel(const float* __restrict__ x, long long plane_stride, int RW, int H, int in_row0, int in_rows,
+down4_rows_kernel(const TIn* __restrict__ x, long long plane_stride, int RW, int H, int in_row0, int in_rows,
                   float* __restrict__ V, int hC, int v_row_begin, int v_row_end, int rows_per_strip) {
   const int e0 = (blockIdx.x * 128 + threadIdx.x) * VEC;
   if (e0 >= RW) return;
@@ -61,7 +63,7 @@ down4_rows_kernel(const float* __restrict__ x, long long plane_stride, int RW, i
   const int j1 = min(j0 + rows_per_strip, v_row_end);
   if (j0 >= j1) return;
   const long long plane = blockIdx.z;
-  const float* src = x + plane * plane_stride + e0;
+  const TIn* src = x + plane * plane_stride + e0;
   float* dst = V + plane * (long long)hC * RW + e0;
   const int ngroups = (j1 - j0) + 8;
   const int ybase = 4 * (j0 - kPC - 4);  // raw row of group 0, phase 0
@@ -79,13 +81,16 @@ down4_rows_kernel(const float* __restrict__ x, long long plane_stride, int RW, i
       // clamp to the image, then to the rows this pointer holds (the latter only ever bites on
       // taps of output rows outside [j0, j1), which are never stored)
       const int y = min(max(min(max(ybase + 4 * g + p, 0), H - 1) - in_row0, 0), in_rows - 1);
-      const float* q = src + (long long)y * RW;
-      if constexpr (VEC == 4) {
+      const TIn* q = src + (long long)y * RW;
+      if constexpr (VEC == 4 && sizeof(TIn) == 1) {
+        const uchar4 t = __ldg(reinterpret_cast<const uchar4*>(q));
+        buf[p][0] = (float)t.x; buf[p][1] = (float)t.y; buf[p][2] = (float)t.z; buf[p][3] = (float)t.w;
+      } else if constexpr (VEC == 4) {
         const float4 t = __ldg(reinterpret_cast<const float4*>(q));
         buf[p][0] = t.x; buf[p][1] = t.y; buf[p][2] = t.z; buf[p][3] = t.w;
       } else {
 #pragma unroll
-        for (int i = 0; i < VEC; ++i) buf[p][i] = __ldg(q + i);
+        for (int i = 0; i < VEC; ++i) buf[p][i] = (float)__ldg(q + i);
       }
     }
   };
@@ -305,13 +310,14 @@ constexpr int kFinalCells = 123;
 
 enum { kIoNhwcVec = 0, kIoNchwVec = 1, kIoScalar = 2 };
 
-// Pull the 48 bytes final_load will read for (row yl, cell X0) into L1 ahead of time: the row loop of the
+// Pull the bytes final_load will read for (row yl, cell X0) into L1 ahead of time: the row loop of the
 // final kernel runs at 16 warps/SM (register-bound), too few to hide an HBM round trip per row, and a
 // register double buffer would cost 12 more registers (ncu: 34 % of the samples sat on this load).
-__device__ __forceinline__ void final_prefetch(const float* __restrict__ x, const ImgView& v, int io, long long img,
+template <typename T>
+__device__ __forceinline__ void final_prefetch(const T* __restrict__ x, const ImgView& v, int io, long long img,
                                                int yl, int X0) {
   if (io == kIoNhwcVec) {
-    const float* p = x + img * v.sn + (long long)yl * v.sy + (long long)X0 * 3;
+    const T* p = x + img * v.sn + (long long)yl * v.sy + (long long)X0 * 3;
     asm volatile("prefetch.global.L1 [%0];" ::"l"(p));
     asm volatile("prefetch.global.L1 [%0];" ::"l"(p + 8));
   } else if (io == kIoNchwVec) {
@@ -321,7 +327,8 @@ __device__ __forceinline__ void final_prefetch(const float* __restrict__ x, cons
   }
 }
 
-// 4 pixels x 3 channels of one row of the cell: f[px][c]
+// 4 pixels x 3 channels of one row of the cell: f[px][c].  uint8_t images are read as raw 0..255 values
+// (FinalParams.in_scale carries the 1/255) and written as rint(255 * value).
 __device__ __forceinline__ void final_load(const float* __restrict__ x, const ImgView& v, int io, long long img,
                                            int yl, int X0, int W, float (&f)[4][3]) {
   if (io == kIoNhwcVec) {
@@ -341,6 +348,27 @@ __device__ __forceinline__ void final_load(const float* __restrict__ x, const Im
 #pragma unroll
       for (int c = 0; c < 3; ++c)
         f[i][c] = (X0 + i < W) ? __ldg(x + img * v.sn + c * v.sc + (long long)yl * v.sy + (long long)(X0 + i) * v.sx) : 0.f;
+  }
+}
+__device__ __forceinline__ void final_load(const uint8_t* __restrict__ x, const ImgView& v, int io, long long img,
+                                           int yl, int X0, int W, float (&f)[4][3]) {
+  if (io == kIoNhwcVec) {
+    const uchar4* p = reinterpret_cast<const uchar4*>(x + img * v.sn + (long long)yl * v.sy + (long long)X0 * 3);
+    const uchar4 a = __ldg(p), b = __ldg(p + 1), c = __ldg(p + 2);
+    f[0][0] = a.x; f[0][1] = a.y; f[0][2] = a.z; f[1][0] = a.w; f[1][1] = b.x; f[1][2] = b.y;
+    f[2][0] = b.z; f[2][1] = b.w; f[2][2] = c.x; f[3][0] = c.y; f[3][1] = c.z; f[3][2] = c.w;
+  } else if (io == kIoNchwVec) {
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      const uchar4 a = __ldg(reinterpret_cast<const uchar4*>(x + img * v.sn + c * v.sc + (long long)yl * v.sy + X0));
+      f[0][c] = a.x; f[1][c] = a.y; f[2][c] = a.z; f[3][c] = a.w;
+    }
+  } else {
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int c = 0; c < 3; ++c)
+        f[i][c] = (X0 + i < W) ? (float)__ldg(x + img * v.sn + c * v.sc + (long long)yl * v.sy + (long long)(X0 + i) * v.sx) : 0.f;
   }
 }
 __device__ __forceinline__ void final_store(float* __restrict__ o, const ImgView& v, int io, long long img, int yl,
@@ -363,12 +391,33 @@ __device__ __forceinline__ void final_store(float* __restrict__ o, const ImgView
         if (X0 + i < W) o[img * v.sn + c * v.sc + (long long)yl * v.sy + (long long)(X0 + i) * v.sx] = f[i][c];
   }
 }
+__device__ __forceinline__ unsigned char to_u8(float v01) { return (unsigned char)__float2uint_rn(255.f * v01); }
+__device__ __forceinline__ void final_store(uint8_t* __restrict__ o, const ImgView& v, int io, long long img, int yl,
+                                            int X0, int W, const float (&f)[4][3]) {
+  if (io == kIoNhwcVec) {
+    uchar4* p = reinterpret_cast<uchar4*>(o + img * v.sn + (long long)yl * v.sy + (long long)X0 * 3);
+    p[0] = make_uchar4(to_u8(f[0][0]), to_u8(f[0][1]), to_u8(f[0][2]), to_u8(f[1][0]));
+    p[1] = make_uchar4(to_u8(f[1][1]), to_u8(f[1][2]), to_u8(f[2][0]), to_u8(f[2][1]));
+    p[2] = make_uchar4(to_u8(f[2][2]), to_u8(f[3][0]), to_u8(f[3][1]), to_u8(f[3][2]));
+  } else if (io == kIoNchwVec) {
+#pragma unroll
+    for (int c = 0; c < 3; ++c)
+      *reinterpret_cast<uchar4*>(o + img * v.sn + c * v.sc + (long long)yl * v.sy + X0) =
+          make_uchar4(to_u8(f[0][c]), to_u8(f[1][c]), to_u8(f[2][c]), to_u8(f[3][c]));
+  } else {
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int c = 0; c < 3; ++c)
+        if (X0 + i < W) o[img * v.sn + c * v.sc + (long long)yl * v.sy + (long long)(X0 + i) * v.sx] = to_u8(f[i][c]);
+  }
+}
 
 // x / out point at image row in_row0 (row-tiled shards); rows [row_begin, row_end) are produced,
 // row_begin a multiple of 4, rows_per_strip a multiple of 4.
-template <int N6, int N4>
+template <int N6, int N4, typename TIO>
 __global__ void __launch_bounds__(128, 4)
-msrcr_final_kernel(const float* __restrict__ x, float* __restrict__ out, ImgView v, int io, int W, int in_row0,
+msrcr_final_kernel(const TIO* __restrict__ x, TIO* __restrict__ out, ImgView v, int io, int W, int in_row0,
                    int row_begin, int row_end, int rows_per_strip, const __grid_constant__ FinalParams p) {
   constexpr int NV = 3 * (N6 + N4);
   __shared__ float s_v[2][4][NV][128];

@@ -300,16 +300,19 @@ int pick_strip(int rows, long long ctas_per_strip_row, int want, int lo, int hi,
 }
 
 template <int N6, int N4>
-void launch_final(dim3 grid, cudaStream_t st, const float* x, float* out, ImgView v, int io, int W, int in_row0,
+void launch_final(dim3 grid, cudaStream_t st, const void* x, void* out, bool u8, ImgView v, int io, int W, int in_row0,
                   int row_begin, int row_end, int rps, const FinalParams& fp) {
-  msrcr_final_kernel<N6, N4><<<grid, 128, 0, st>>>(x, out, v, io, W, in_row0, row_begin, row_end, rps, fp);
+  if (u8)
+    msrcr_final_kernel<N6, N4, uint8_t><<<grid, 128, 0, st>>>((const uint8_t*)x, (uint8_t*)out, v, io, W, in_row0, row_begin, row_end, rps, fp);
+  else
+    msrcr_final_kernel<N6, N4, float><<<grid, 128, 0, st>>>((const float*)x, (float*)out, v, io, W, in_row0, row_begin, row_end, rps, fp);
 }
 
 
 // K5 launches: rows [row_begin, row_end) of n images whose pointers start at image row in_row0.
-int final_passes(llie_ctx* ctx, cudaStream_t st, const MsrcrPlan* pl, const llie_msrcr_params& p, const float* in,
-                 float* out, const ImgView& v, bool vec, bool nhwc, int n, int h_view, int w, int in_row0, int row_begin,
-                 int row_end, int hC, int wC, const float* dSC, size_t c_elems, float* dAcc) {
+int final_passes(llie_ctx* ctx, cudaStream_t st, const MsrcrPlan* pl, const llie_msrcr_params& p, const void* in,
+                 void* out, const ImgView& v, bool vec, bool nhwc, int n, int h_view, int w, int in_row0, int row_begin,
+                 int row_end, int hC, int wC, const float* dSC, size_t c_elems, float* dAcc, bool u8 = false) {
   (void)h_view;
   const int io = vec ? (nhwc ? kIoNhwcVec : kIoNchwVec) : kIoScalar;
   const int cx = ceil_div(w, 4 * kFinalCells);
@@ -326,7 +329,7 @@ int final_passes(llie_ctx* ctx, cudaStream_t st, const MsrcrPlan* pl, const llie
   fp.beta_ln2 = (float)(p.beta * ln2);
   fp.gain255 = p.gain / 255.f;
   fp.offset255 = p.offset / 255.f;
-  fp.in_scale = p.in_scale; fp.in_bias = p.in_bias;
+  fp.in_scale = u8 ? p.in_scale / 255.f : p.in_scale; fp.in_bias = p.in_bias;  // uint8 images are read as 0..255
   int n6 = 0;
   for (auto& sc : pl->scales) n6 += (sc.level == 0);
   if (p.n_scales == 3 && n6 == 1) {
@@ -335,7 +338,7 @@ int final_passes(llie_ctx* ctx, cudaStream_t st, const MsrcrPlan* pl, const llie
       fp.map[i] = dSC + (size_t)k * c_elems;
       fp.w2[i] = (float)(ln2 * p.weight[k]);
     }
-    LLIE_LAUNCH(ctx, st, "msrcr_final_kernel", (launch_final<1, 2>(grid, st, in, out, v, io, w, in_row0, row_begin, row_end, rps, fp)));
+    LLIE_LAUNCH(ctx, st, "msrcr_final_kernel", (launch_final<1, 2>(grid, st, in, out, u8, v, io, w, in_row0, row_begin, row_end, rps, fp)));
   } else {
     for (int k0 = 0; k0 < p.n_scales; k0 += 3) {
       const int cnt = std::min(3, p.n_scales - k0);
@@ -345,9 +348,9 @@ int final_passes(llie_ctx* ctx, cudaStream_t st, const MsrcrPlan* pl, const llie
       }
       fp.acc_in = k0 > 0 ? (const float*)dAcc : nullptr;
       fp.acc_out = k0 + cnt < p.n_scales ? dAcc : nullptr;
-      if (cnt == 1) LLIE_LAUNCH(ctx, st, "msrcr_final_kernel", (launch_final<1, 0>(grid, st, in, out, v, io, w, in_row0, row_begin, row_end, rps, fp)));
-      if (cnt == 2) LLIE_LAUNCH(ctx, st, "msrcr_final_kernel", (launch_final<2, 0>(grid, st, in, out, v, io, w, in_row0, row_begin, row_end, rps, fp)));
-      if (cnt == 3) LLIE_LAUNCH(ctx, st, "msrcr_final_kernel", (launch_final<3, 0>(grid, st, in, out, v, io, w, in_row0, row_begin, row_end, rps, fp)));
+      if (cnt == 1) LLIE_LAUNCH(ctx, st, "msrcr_final_kernel", (launch_final<1, 0>(grid, st, in, out, u8, v, io, w, in_row0, row_begin, row_end, rps, fp)));
+      if (cnt == 2) LLIE_LAUNCH(ctx, st, "msrcr_final_kernel", (launch_final<2, 0>(grid, st, in, out, u8, v, io, w, in_row0, row_begin, row_end, rps, fp)));
+      if (cnt == 3) LLIE_LAUNCH(ctx, st, "msrcr_final_kernel", (launch_final<3, 0>(grid, st, in, out, u8, v, io, w, in_row0, row_begin, row_end, rps, fp)));
     }
   }
   return LLIE_OK;
@@ -357,6 +360,13 @@ int final_passes(llie_ctx* ctx, cudaStream_t st, const MsrcrPlan* pl, const llie
 
 int msrcr_pyramid_run(llie_ctx* ctx, const float* in, float* out, int n, int h, int w, int layout,
                       const llie_msrcr_params& p, cudaStream_t st) {
+  return msrcr_pyramid_run_io(ctx, in, out, false, n, h, w, layout, p, st);
+}
+
+// u8: in / out are uint8_t images (value = byte / 255 on the way in, rint(255 * value) on the way out), converted
+// inside the first and last kernels -- no extra pass over the image.
+int msrcr_pyramid_run_io(llie_ctx* ctx, const void* in, void* out, bool u8, int n, int h, int w, int layout,
+                         const llie_msrcr_params& p, cudaStream_t st) {
   LLIE_TRY(ensure_plan(ctx, p, st));
   MsrcrPlan* pl = ctx->plan;
   const int hC = level_c_size(h), wC = level_c_size(w), hB = level_b_size(h), wB = level_b_size(w);
@@ -381,8 +391,9 @@ int msrcr_pyramid_run(llie_ctx* ctx, const float* in, float* out, int n, int h, 
   if (p.n_scales > 3) LLIE_TRY(ctx->workspace("msrcr.acc", (size_t)n * h * w * 3 * 4, &dAcc));
 
   const ImgView v = make_view(layout, 3, h, w);
-  const bool vec = (w % 4 == 0) && ((reinterpret_cast<uintptr_t>(in) | reinterpret_cast<uintptr_t>(out)) % 16 == 0);
+  const bool vec = (w % 4 == 0) && ((reinterpret_cast<uintptr_t>(in) | reinterpret_cast<uintptr_t>(out)) % (u8 ? 4 : 16) == 0);
   const int want = 8 * ctx->sm_count;
+  const float in_scale = u8 ? p.in_scale / 255.f : p.in_scale;
 
   {  // K1: rows
     const long long plane_stride = nhwc ? (long long)h * RW : (long long)h * w;
@@ -390,24 +401,32 @@ int msrcr_pyramid_run(llie_ctx* ctx, const float* in, float* out, int n, int h, 
       const int cx = ceil_div(RW, 512);
       const int rps = pick_strip(hC, (long long)cx * planes_v, want, 16, 64, 1);
       dim3 grid(cx, ceil_div(hC, rps), planes_v);
-      LLIE_LAUNCH(ctx, st, "down4_rows_kernel",
-                  down4_rows_kernel<4><<<grid, 128, 0, st>>>(in, plane_stride, RW, h, 0, h, (float*)dV, hC, 0, hC, rps));
+      if (u8)
+        LLIE_LAUNCH(ctx, st, "down4_rows_kernel",
+                    (down4_rows_kernel<4, uint8_t><<<grid, 128, 0, st>>>((const uint8_t*)in, plane_stride, RW, h, 0, h, (float*)dV, hC, 0, hC, rps)));
+      else
+        LLIE_LAUNCH(ctx, st, "down4_rows_kernel",
+                    (down4_rows_kernel<4, float><<<grid, 128, 0, st>>>((const float*)in, plane_stride, RW, h, 0, h, (float*)dV, hC, 0, hC, rps)));
     } else {
       const int cx = ceil_div(RW, 128);
       const int rps = pick_strip(hC, (long long)cx * planes_v, want, 16, 64, 1);
       dim3 grid(cx, ceil_div(hC, rps), planes_v);
-      LLIE_LAUNCH(ctx, st, "down4_rows_kernel",
-                  down4_rows_kernel<1><<<grid, 128, 0, st>>>(in, plane_stride, RW, h, 0, h, (float*)dV, hC, 0, hC, rps));
+      if (u8)
+        LLIE_LAUNCH(ctx, st, "down4_rows_kernel",
+                    (down4_rows_kernel<1, uint8_t><<<grid, 128, 0, st>>>((const uint8_t*)in, plane_stride, RW, h, 0, h, (float*)dV, hC, 0, hC, rps)));
+      else
+        LLIE_LAUNCH(ctx, st, "down4_rows_kernel",
+                    (down4_rows_kernel<1, float><<<grid, 128, 0, st>>>((const float*)in, plane_stride, RW, h, 0, h, (float*)dV, hC, 0, hC, rps)));
     }
   }
   {  // K1b: columns
     dim3 grid(ceil_div(wC, 128), hC, planes_v);
     if (nhwc)
       LLIE_LAUNCH(ctx, st, "down4_cols_kernel",
-                  down4_cols_kernel<3><<<grid, 128, 0, st>>>((const float*)dV, (float*)dC, RW, w, hC, wC, 0, p.in_scale, p.in_bias));
+                  down4_cols_kernel<3><<<grid, 128, 0, st>>>((const float*)dV, (float*)dC, RW, w, hC, wC, 0, in_scale, p.in_bias));
     else
       LLIE_LAUNCH(ctx, st, "down4_cols_kernel",
-                  down4_cols_kernel<1><<<grid, 128, 0, st>>>((const float*)dV, (float*)dC, RW, w, hC, wC, 0, p.in_scale, p.in_bias));
+                  down4_cols_kernel<1><<<grid, 128, 0, st>>>((const float*)dV, (float*)dC, RW, w, hC, wC, 0, in_scale, p.in_bias));
   }
   if (n_b) {
     dim3 gx(ceil_div((long long)hC * wB, 256), 1, planes), gy(ceil_div((long long)hB * wB, 256), 1, planes);
@@ -435,7 +454,7 @@ int msrcr_pyramid_run(llie_ctx* ctx, const float* in, float* out, int n, int h, 
     }
   }
   LLIE_TRY(final_passes(ctx, st, pl, p, in, out, v, vec, nhwc, n, h, w, 0, 0, h, hC, wC, (const float*)dSC, c_elems,
-                        (float*)dAcc));
+                        (float*)dAcc, u8));
   return LLIE_OK;
 }
 
@@ -550,13 +569,13 @@ int tiled_phase_a(llie_ctx* ctx, int d, int n_dev, llie_ctx* const* ctxs, const 
       const int rps = pick_strip(v1 - v0, cx, want, 4, 64, 1);
       dim3 grid(cx, ceil_div(v1 - v0, rps), 1);
       LLIE_LAUNCH(ctx, st, "down4_rows_kernel",
-                  down4_rows_kernel<4><<<grid, 128, 0, st>>>(x, 0, RW, H, in_row0, in_rows, b.V, hC, v0, v1, rps));
+                  (down4_rows_kernel<4, float><<<grid, 128, 0, st>>>(x, 0, RW, H, in_row0, in_rows, b.V, hC, v0, v1, rps)));
     } else {
       const int cx = ceil_div(RW, 128);
       const int rps = pick_strip(v1 - v0, cx, want, 4, 64, 1);
       dim3 grid(cx, ceil_div(v1 - v0, rps), 1);
       LLIE_LAUNCH(ctx, st, "down4_rows_kernel",
-                  down4_rows_kernel<1><<<grid, 128, 0, st>>>(x, 0, RW, H, in_row0, in_rows, b.V, hC, v0, v1, rps));
+                  (down4_rows_kernel<1, float><<<grid, 128, 0, st>>>(x, 0, RW, H, in_row0, in_rows, b.V, hC, v0, v1, rps)));
     }
     return LLIE_OK;
   };

@@ -310,6 +310,63 @@ def test_dce_iters_and_sign(blob):
         assert (np.abs(y - ref).max() <= TOL_F32) if prec != "bf16" else (psnr(y, ref) >= PSNR_BF16)
 
 
+# ---------------------------------------------------------------- 8-bit images -------------
+def _u8_image(h, w, seed, gain=6.0):
+    return np.clip(np.rint(oracle.synth_lowlight(h, w, seed) * gain * 255.0), 0, 255).astype(np.uint8)
+
+
+def _assert_u8_close(got, want_u8, want_float255, slack):
+    """Bytes may differ from the oracle's only where the un-rounded value sits within `slack` (in 1/255 units) of
+    a rounding boundary, and then by exactly one."""
+    d = got.astype(np.int16) - want_u8.astype(np.int16)
+    assert np.abs(d).max() <= 1
+    bad = d != 0
+    frac = np.abs(want_float255 - np.floor(want_float255) - 0.5)
+    assert np.all(frac[bad] <= slack), float(frac[bad].max())
+    assert bad.mean() <= 0.02
+
+
+@pytest.mark.parametrize("shape", [(120, 200), (61, 133), (400, 600)])
+def test_msrcr_u8_matches_oracle(shape):
+    x = _u8_image(*shape, 7)
+    want, want_f = oracle.msrcr_u8(x)
+    y = L.enhance(x, "msrcr")
+    assert y.dtype == np.uint8 and y.shape == x.shape
+    _assert_u8_close(y, want, want_f, slack=255 * TOL_F32)
+    # NCHW torch tensor on the device, and agreement with the float path fed the same values
+    xc = torch.from_numpy(np.ascontiguousarray(x.transpose(2, 0, 1))[None]).cuda()
+    yc = L.enhance(xc, "msrcr", dict(layout="NCHW"))
+    assert yc.dtype == torch.uint8
+    assert np.abs(yc[0].cpu().numpy().transpose(1, 2, 0).astype(np.int16) - y.astype(np.int16)).max() <= 1
+    yf = L.enhance(oracle.from_u8(x), "msrcr")
+    assert np.abs(np.rint(yf * 255.0) - y.astype(np.float32)).max() <= 1
+
+
+@pytest.mark.parametrize("shape", [(135, 240), (70, 131)])
+def test_dce_u8_matches_oracle(shape, blob):
+    x = _u8_image(*shape, 8, gain=3.0)
+    want, want_f = oracle.zero_dce_u8(x, oracle.init_weights(0))
+    y = L.enhance(x, "zero_dce", dict(weights=blob, precision="bf16"))
+    assert y.dtype == np.uint8 and y.shape == x.shape
+    # bf16 operands: judged like the float path (PSNR on [0,1] values), plus a byte-level bound
+    assert psnr(y.astype(np.float64) / 255.0, want_f / 255.0) >= 48.0   # 8-bit quantisation alone is 58.9 dB
+    assert np.abs(y.astype(np.int16) - want.astype(np.int16)).max() <= 2
+    yf = L.enhance(oracle.from_u8(x), "zero_dce", dict(weights=blob, precision="bf16"))
+    assert np.abs(np.rint(yf * 255.0) - y.astype(np.float32)).max() <= 1
+
+
+def test_u8_rejections_and_host_pipeline(blob):
+    x = _u8_image(64, 96, 9)
+    with pytest.raises(L.LlieError):
+        L.enhance(x, "msrcr", dict(blur="direct"))
+    with pytest.raises(L.LlieError):
+        L.enhance(x, "zero_dce", dict(weights=blob, precision="fp32"))
+    xs = np.stack([_u8_image(300, 500, s) for s in range(5)])
+    yb = L.enhance(xs, "msrcr")
+    for i in range(5):
+        assert np.array_equal(yb[i], L.enhance(xs[i], "msrcr"))
+
+
 # ---------------------------------------------------------------- boundary ----------------
 def test_numpy_torch_cpu_and_cuda_inputs_agree(blob):
     x = np.stack([oracle.synth_lowlight(64, 96, s) for s in range(5)])

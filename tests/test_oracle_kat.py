@@ -132,3 +132,10 @@ def test_synth_lowlight_is_dark_and_seeded():
     assert np.array_equal(a, b) and a.dtype == np.float32 and a.shape == (64, 96, 3)
     assert 0 <= a.min() and a.max() < 0.2 and a.mean() < 0.06
     assert not np.array_equal(a, oracle.synth_lowlight(64, 96, 8))
+
+
+def test_u8_convention_round_trips():
+    """byte b <-> b / 255, rint on the way back (half to even)."""
+    b = np.arange(256, dtype=np.uint8)
+    assert np.array_equal(oracle.to_u8(oracle.from_u8(b)), b)
+    assert oracle.to_u8(np.array([0.5 / 255, 1.5 / 255, -1.0, 2.0, 0.4999 / 255])).tolist() == [0, 2, 0, 255, 0]
