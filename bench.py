@@ -63,6 +63,20 @@ MSRCR_KERNEL_BYTES_PER_PX_U8 = {"down4_rows_kernel": 3 + 3.0, "msrcr_final_kerne
 MSRCR_NORTH_STAR_BYTES_PER_PX_U8 = 3 + 36 + 36 + 3 + 3   # the same two-pass data flow with uint8 image I/O
 
 
+# DRAM bytes per pixel (dram__bytes_read.sum + dram__bytes_write.sum) of each kernel from the committed
+# `ncu --set full` captures: profiles/r01_ncu_full_dce_chain_16x1080p.md (16 x 1080p) and
+# profiles/r01_ncu_full_msrcr_8x4k_v2.md (8 x 4K).  `roofline.traffic` = this x the pixels one launch processes.
+NCU_DRAM_BYTES_PER_PX = {"dce_chain_c123_kernel": 6.92e9 / (16 * 1920 * 1080), "dce_chain_c45_kernel": 4.40e9 / (16 * 1920 * 1080),
+                         "dce_chain_c67_kernel": 7.70e9 / (16 * 1920 * 1080), "msrcr_final_kernel": 1750.8e6 / (8 * 3840 * 2160),
+                         "down4_rows_kernel": 1077.9e6 / (8 * 3840 * 2160)}
+MSRCR_NCU_DRAM_BYTES_PER_PX = 3310.9e6 / (8 * 3840 * 2160)   # all 15 launches of one MSRCR call: 49.9 B/px
+
+
+def ncu_traffic(kernel, px_per_step, steps, launches, io="f32"):
+    b = NCU_DRAM_BYTES_PER_PX.get(kernel)
+    return None if b is None or io != "f32" else int(b * px_per_step * steps / max(launches, 1))
+
+
 def load_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -232,7 +246,7 @@ def tc_roofline(prof, px_per_step, steps, peaks, split=False):
     chain = (3 if split else 1) * DCE_TENSOR_FLOP_PER_PX * px_per_step * steps / (chain_ms * 1e-3) / 1e12
     peak = peaks["tc_sustained"]
     return {"bound": "tensor", "kernel": dom, "achieved": round(ach, 2), "peak": peak, "unit": "TFLOP/s",
-            "frac": round(ach / peak, 4), "traffic": None, "peak_source": f"{peaks['source']} bf16 sustained",
+            "frac": round(ach / peak, 4), "traffic": ncu_traffic(dom, px_per_step, steps, tc[dom][0]), "peak_source": f"{peaks['source']} bf16 sustained",
             "launches": tc[dom][0], "avg_launch_ms": round(tc[dom][1] / tc[dom][0], 4),
             "conv2to7_chain": {"achieved": round(chain, 2), "frac": round(chain / peak, 4),
                                "frac_of_burst": round(chain / peaks["tc_burst"], 4)},
@@ -252,7 +266,13 @@ def hbm_roofline(prof, px_per_step, steps, peaks, total_ms_per_step, u8=False):
     ach = kbytes[dom] * px_per_step * steps / (ms * 1e-3) / 1e9
     ns = ns_bytes * px_per_step / (total_ms_per_step * 1e-3) / 1e9
     return {"bound": "hbm", "kernel": dom, "achieved": round(ach, 1), "peak": peaks["hbm"], "unit": "GB/s",
-            "frac": round(ach / peaks["hbm"], 4), "traffic": None, "peak_source": f"{peaks['source']} copy",
+            "frac": round(ach / peaks["hbm"], 4), "traffic": ncu_traffic(dom, px_per_step, steps, cnt, "u8" if u8 else "f32"),
+            "peak_source": f"{peaks['source']} copy",
+            **({} if u8 else {"whole_msrcr_at_ncu_dram_bytes": {
+                "bytes_per_px": round(MSRCR_NCU_DRAM_BYTES_PER_PX, 1),
+                "achieved": round(MSRCR_NCU_DRAM_BYTES_PER_PX * px_per_step / (total_ms_per_step * 1e-3) / 1e9, 1),
+                "frac": round(MSRCR_NCU_DRAM_BYTES_PER_PX * px_per_step / (total_ms_per_step * 1e-3) / 1e9 / peaks["hbm"], 4),
+                "note": "the cascade moves ~50 B/px through DRAM (ncu), not the 108 B/px of the two-pass data flow"}}),
             "kernel_bytes_per_px": kbytes[dom],
             "launches": cnt, "avg_launch_ms": round(ms / cnt, 4),
             f"whole_msrcr_at_{ns_bytes}B_per_px": {"achieved": round(ns, 1), "frac": round(ns / peaks["hbm"], 4)},

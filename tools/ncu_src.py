@@ -24,9 +24,14 @@ def main():
             cur["hdr"] = hdr
         elif cur is not None and hdr is not None:
             cur["rows"].append(row)
+    seen = set()
     for k in kernels:
-        if want not in k["name"]:
+        if want not in k["name"] or not k["rows"]:
             continue
+        key = (k["name"], len(k["rows"]), k["rows"][0][0])
+        if key in seen:      # ncu lists a kernel once per source view
+            continue
+        seen.add(key)
         hdr = k["hdr"]
         i_s, i_src, i_ex = hdr.index("# Samples"), hdr.index("Source"), hdr.index("Instructions Executed")
         stall = [(i, h) for i, h in enumerate(hdr) if h.startswith("stall_") and "Not Issued" not in h]
