@@ -5,9 +5,10 @@ hand-written sm_100a kernels of libllie.so, reached through the C ABI of include
 PyTorch is used only for device memory, pinned staging and streams.
 """
 from .api import (enhance, Enhancer, default_msrcr_params, default_dce_params, init_dce_weights,
-                  shard_slice, plan_query, msrcr_tiled, tile_rows)
+                  shard_slice, plan_query, msrcr_tiled, tile_rows, load_dce_state_dict)
 from ._lib import LlieError, LlieCudaError
 
 __all__ = ["enhance", "Enhancer", "default_msrcr_params", "default_dce_params", "init_dce_weights",
-           "shard_slice", "plan_query", "msrcr_tiled", "tile_rows", "LlieError", "LlieCudaError"]
+           "shard_slice", "plan_query", "msrcr_tiled", "tile_rows", "load_dce_state_dict", "LlieError",
+           "LlieCudaError"]
 __version__ = "0.1.0"

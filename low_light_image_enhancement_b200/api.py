@@ -48,6 +48,47 @@ def init_dce_weights(seed: int = 0, last_gain: float = 1.0) -> np.ndarray:
     return np.concatenate(parts).astype(np.float32)
 
 
+_UPSTREAM_KEYS = tuple(f"e_conv{i}" for i in range(1, 8))
+
+
+def load_dce_state_dict(src, *, strict: bool = True) -> np.ndarray:
+    """Packed weight blob from a Zero-DCE checkpoint.
+
+    src : a path to a torch checkpoint (.pth, loaded with weights_only=True on the CPU) or a mapping
+          name -> tensor/array.  Expected entries are the public Zero-DCE layer names e_conv1 .. e_conv7
+          (".weight" (Cout, Cin, 3, 3) and ".bias" (Cout,)), optionally behind a "module." prefix or inside a
+          {"state_dict": ...} wrapper.  The public model applies x + r (x^2 - x), i.e. pass
+          params["curve_sign"] = -1 with these weights (north_star's convention is +1).
+    Returns the 79 416-float blob W1 b1 ... W7 b7 that enhance(..., params={"weights": blob}) takes.
+    """
+    if isinstance(src, (str, bytes)) or hasattr(src, "__fspath__"):
+        sd = torch.load(src, map_location="cpu", weights_only=True)
+    else:
+        sd = src
+    if isinstance(sd, dict) and "state_dict" in sd and not any(str(k).startswith("e_conv") for k in sd):
+        sd = sd["state_dict"]
+    flat = {}
+    for k, v in sd.items():
+        k = str(k)
+        while k.startswith("module."):
+            k = k[len("module."):]
+        flat[k] = v.detach().cpu().numpy() if isinstance(v, torch.Tensor) else np.asarray(v)
+    parts = []
+    for name, (co, ci) in zip(_UPSTREAM_KEYS, DCE_LAYERS):
+        try:
+            w, b = flat.pop(name + ".weight"), flat.pop(name + ".bias")
+        except KeyError as e:
+            raise ValueError(f"checkpoint has no entry {e.args[0]!r}") from None
+        if w.shape != (co, ci, 3, 3) or b.shape != (co,):
+            raise ValueError(f"{name}: expected weight {(co, ci, 3, 3)} and bias {(co,)}, got {w.shape} and {b.shape}")
+        parts += [np.asarray(w, np.float32).ravel(), np.asarray(b, np.float32).ravel()]
+    if strict and flat:
+        raise ValueError(f"unexpected entries in the checkpoint: {sorted(flat)[:5]}")
+    blob = np.concatenate(parts).astype(np.float32)
+    assert blob.size == DCE_NUM_PARAMS
+    return blob
+
+
 def plan_query(sigma: float, truncate: float = 4.0) -> dict:
     """Host-side planner of the pyramid blur (needs no GPU): stride, low-res sigma/radius, kernel L1 error."""
     st, sl, rl, l1 = C.c_int(), C.c_double(), C.c_int(), C.c_double()
