@@ -152,10 +152,17 @@ down4_cols_kernel(const float* __restrict__ V, float* __restrict__ Cout, int RW,
   const int jx0 = blockIdx.x * 128;
   const int px0 = 4 * (jx0 - kPC) - kRD;
   const float* src = V + (plane * hC + jy) * (long long)RW;
-  for (int i = threadIdx.x; i < kSegPx * CS; i += 128) {
-    const int px = i / CS, c = i - px * CS;
-    const int xx = min(max(px0 + px, 0), W - 1);
-    seg[i] = __ldg(src + xx * CS + c);
+  static_assert((kSegPx * CS) % 4 == 0, "segment must be a whole number of float4");
+  if (px0 >= 0 && px0 + kSegPx <= W && (RW & 3) == 0) {
+    // interior segment: contiguous and 16-byte aligned (px0 * CS is a multiple of 32 floats) -> 128-bit copies
+    const float4* s4 = reinterpret_cast<const float4*>(src + (long long)px0 * CS);
+    for (int i = threadIdx.x; i < kSegPx * CS / 4; i += 128) reinterpret_cast<float4*>(seg)[i] = __ldg(s4 + i);
+  } else {
+    for (int i = threadIdx.x; i < kSegPx * CS; i += 128) {
+      const int px = i / CS, c = i - px * CS;
+      const int xx = min(max(px0 + px, 0), W - 1);
+      seg[i] = __ldg(src + xx * CS + c);
+    }
   }
   __syncthreads();
   const int jx = jx0 + threadIdx.x;
@@ -195,20 +202,31 @@ decim4_x_kernel(const float* __restrict__ Cin, float* __restrict__ T, int hC, in
   for (int t = 0; t <= 2 * kRD; ++t) acc = fmaf(gd(t), __ldg(src + min(max(c0 + t, 0), wC - 1)), acc);
   T[(plane * hC + row) * (long long)wB + jb] = acc;
 }
-// y pass: B[plane][jb][x] = sum_t g[t] T[plane][clamp(4(jb-PB)+PC+t-16, 0, hC-1)][x], B rows [b0, b1)
-__global__ void __launch_bounds__(256)
+// y pass: B[plane][jb][x] = sum_t g[t] T[plane][clamp(4(jb-PB)+PC+t-16, 0, hC-1)][x], B rows [b0, b1).
+// One column per lane, kDecQ consecutive B rows per thread: the 4 (kDecQ - 1) + 33 input rows are loaded once
+// (coalesced) and every output still sums its taps in order t = 0..32 (bit-identical to one output per thread).
+constexpr int kDecQ = 8;
+__global__ void __launch_bounds__(128)
 decim4_y_kernel(const float* __restrict__ T, float* __restrict__ B, int hC, int hB, int wB, int b0, int b1) {
   const long long plane = blockIdx.z;
-  const int i = blockIdx.x * 256 + threadIdx.x;
-  const int n = (b1 - b0) * wB;
-  if (i >= n) return;
-  const int jb = b0 + i / wB, xx = i % wB;
+  const int xx = blockIdx.x * 128 + threadIdx.x;
+  const int jb0 = b0 + blockIdx.y * kDecQ;
+  if (xx >= wB || jb0 >= b1) return;
   const float* src = T + plane * (long long)hC * wB + xx;
-  const int c0 = 4 * (jb - kPB) + kPC - kRD;
-  float acc = 0.f;
+  const int c0 = 4 * (jb0 - kPB) + kPC - kRD;
+  float acc[kDecQ];
 #pragma unroll
-  for (int t = 0; t <= 2 * kRD; ++t) acc = fmaf(gd(t), __ldg(src + (long long)min(max(c0 + t, 0), hC - 1) * wB), acc);
-  B[(plane * hB + jb) * (long long)wB + xx] = acc;
+  for (int q = 0; q < kDecQ; ++q) acc[q] = 0.f;
+#pragma unroll
+  for (int u = 0; u <= 4 * (kDecQ - 1) + 2 * kRD; ++u) {
+    const float v = __ldg(src + (long long)min(max(c0 + u, 0), hC - 1) * wB);
+#pragma unroll
+    for (int q = 0; q < kDecQ; ++q)
+      if (u - 4 * q >= 0 && u - 4 * q <= 2 * kRD) acc[q] = fmaf(gd(u - 4 * q), v, acc[q]);
+  }
+#pragma unroll
+  for (int q = 0; q < kDecQ; ++q)
+    if (jb0 + q < b1) B[(plane * hB + jb0 + q) * (long long)wB + xx] = acc[q];
 }
 
 // ---- level B -> level C: Gaussian-weighted x4 upsample ------------------------------------------
