@@ -187,20 +187,42 @@ down4_cols_kernel(const float* __restrict__ V, float* __restrict__ Cout, int RW,
 }
 
 // ---- level C -> level B: prefilter + decimate by 4 (same 33-tap Gaussian, in C samples) ---------
-// x pass: T[plane][row][jb] = sum_t g[t] C[plane][row][clamp(4(jb-PB)+PC+t-16, 0, wC-1)], rows [r0, r1)
-__global__ void __launch_bounds__(256)
+// x pass: T[plane][row][jb] = sum_t g[t] C[plane][row][clamp(4(jb-PB)+PC+t-16, 0, wC-1)], rows [r0, r1).
+// A CTA stages the edge-clamped C row segment of kDecXTile outputs in shared memory (one pad float after every
+// sixteen: thread g reads element 16 g + u at 17 g + ..., conflict-free) and every thread produces four outputs
+// from 45 samples instead of 4 x 33; each output still sums its taps in order t = 0..32.
+constexpr int kDecXQ = 4;
+constexpr int kDecXTile = 128 * kDecXQ;
+__global__ void __launch_bounds__(128)
 decim4_x_kernel(const float* __restrict__ Cin, float* __restrict__ T, int hC, int wC, int wB, int r0, int r1) {
+  constexpr int kSeg = 4 * kDecXTile + 2 * kRD + 16;
+  __shared__ float seg[kSeg + kSeg / 16 + 1];
   const long long plane = blockIdx.z;
-  const int i = blockIdx.x * 256 + threadIdx.x;
-  const int n = (r1 - r0) * wB;
-  if (i >= n) return;
-  const int row = r0 + i / wB, jb = i % wB;
+  const int row = r0 + blockIdx.y;
+  const int jb0 = blockIdx.x * kDecXTile;
+  const int outs = min(kDecXTile, wB - jb0);
   const float* src = Cin + (plane * hC + row) * (long long)wC;
-  const int c0 = 4 * (jb - kPB) + kPC - kRD;
-  float acc = 0.f;
+  const int c0 = 4 * (jb0 - kPB) + kPC - kRD;
+  const int need = 4 * outs + 2 * kRD;  // samples the outputs of this CTA reach (rounded up by the loop below)
+  for (int i = threadIdx.x; i < need + 12; i += 128) seg[i + (i >> 4)] = __ldg(src + min(max(c0 + i, 0), wC - 1));
+  __syncthreads();
+  const int g = threadIdx.x;
+  if (g * kDecXQ >= outs) return;
+  const float* sg = seg + 17 * g;  // element 16 g of the padded segment
+  float acc[kDecXQ];
 #pragma unroll
-  for (int t = 0; t <= 2 * kRD; ++t) acc = fmaf(gd(t), __ldg(src + min(max(c0 + t, 0), wC - 1)), acc);
-  T[(plane * hC + row) * (long long)wB + jb] = acc;
+  for (int q = 0; q < kDecXQ; ++q) acc[q] = 0.f;
+#pragma unroll
+  for (int u = 0; u <= 4 * (kDecXQ - 1) + 2 * kRD; ++u) {
+    const float v = sg[u + (u >> 4)];
+#pragma unroll
+    for (int q = 0; q < kDecXQ; ++q)
+      if (u - 4 * q >= 0 && u - 4 * q <= 2 * kRD) acc[q] = fmaf(gd(u - 4 * q), v, acc[q]);
+  }
+  float* dst = T + (plane * hC + row) * (long long)wB + jb0 + g * kDecXQ;
+#pragma unroll
+  for (int q = 0; q < kDecXQ; ++q)
+    if (g * kDecXQ + q < outs) dst[q] = acc[q];
 }
 // y pass: B[plane][jb][x] = sum_t g[t] T[plane][clamp(4(jb-PB)+PC+t-16, 0, hC-1)][x], B rows [b0, b1).
 // One column per lane, kDecQ consecutive B rows per thread: the 4 (kDecQ - 1) + 33 input rows are loaded once

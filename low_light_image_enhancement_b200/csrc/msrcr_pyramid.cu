@@ -429,8 +429,7 @@ int msrcr_pyramid_run_io(llie_ctx* ctx, const void* in, void* out, bool u8, int 
                   down4_cols_kernel<1><<<grid, 128, 0, st>>>((const float*)dV, (float*)dC, RW, w, hC, wC, 0, in_scale, p.in_bias));
   }
   if (n_b) {
-    dim3 gx(ceil_div((long long)hC * wB, 256), 1, planes), gy(ceil_div((long long)hB * wB, 256), 1, planes);
-    LLIE_LAUNCH(ctx, st, "decim4_x_kernel", decim4_x_kernel<<<gx, 256, 0, st>>>((const float*)dC, (float*)dTB, hC, wC, wB, 0, hC));
+    LLIE_LAUNCH(ctx, st, "decim4_x_kernel", decim4_x_kernel<<<dim3(ceil_div(wB, kDecXTile), hC, planes), 128, 0, st>>>((const float*)dC, (float*)dTB, hC, wC, wB, 0, hC));
     LLIE_LAUNCH(ctx, st, "decim4_y_kernel", decim4_y_kernel<<<dim3(ceil_div(wB, 128), ceil_div(hB, kDecQ), planes), 128, 0, st>>>((const float*)dTB, (float*)dB, hC, hB, wB, 0, hB));
   }
   (void)CS;
@@ -611,8 +610,7 @@ int tiled_phase_b(llie_ctx* ctx, int d, int n_dev, llie_ctx* const* ctxs, const 
   int n_b = 0;
   for (auto& sp : pl->scales) n_b += sp.level;
   if (n_b) {
-    dim3 gx(ceil_div((long long)(g.c1_hi - g.c1_lo) * wB, 256), 1, 3), gy(ceil_div((long long)(g.bb_hi - g.bb_lo) * wB, 256), 1, 3);
-    LLIE_LAUNCH(ctx, st, "decim4_x_kernel", decim4_x_kernel<<<gx, 256, 0, st>>>(b.C, b.TB, hC, wC, wB, g.c1_lo, g.c1_hi));
+    LLIE_LAUNCH(ctx, st, "decim4_x_kernel", decim4_x_kernel<<<dim3(ceil_div(wB, kDecXTile), g.c1_hi - g.c1_lo, 3), 128, 0, st>>>(b.C, b.TB, hC, wC, wB, g.c1_lo, g.c1_hi));
     LLIE_LAUNCH(ctx, st, "decim4_y_kernel", decim4_y_kernel<<<dim3(ceil_div(wB, 128), ceil_div(g.bb_hi - g.bb_lo, kDecQ), 3), 128, 0, st>>>(b.TB, b.B, hC, hB, wB, g.bb_lo, g.bb_hi));
   }
   for (int k = 0; k < p.n_scales; ++k) {
