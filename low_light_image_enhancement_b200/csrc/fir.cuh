@@ -110,6 +110,11 @@ __global__ void __launch_bounds__(128) fir_y_kernel(const float* __restrict__ in
 // C = 1).  Every output accumulates its taps strictly in order t = 0 .. 2r, whatever its position in the
 // thread's group of eight, so results do not depend on how rows / columns are grouped (row-tiled == whole).
 constexpr int kFir8 = 8;
+// Taps as a by-value kernel argument (constant bank): the tap of a step is then a uniform LDC instead of a
+// shared-memory load, which halves the load-store-unit work of the inner loop (8 LDS/LDG + 8 tap LDS per 64 FFMA
+// kept the LSU as busy as the FMA pipes).  Filters longer than kFirParamTaps fall back to taps in shared memory.
+constexpr int kFirParamTaps = 160;
+struct FirTaps { float t[kFirParamTaps]; };
 constexpr int kFirX8Tile = 128 * kFir8;  // pixels per CTA of fir_x8_kernel
 __host__ __device__ inline int fir8_steps(int r) { return (2 * r + kFir8 + 7) & ~7; }
 __host__ __device__ inline size_t fir_x8_smem(int r) {
@@ -119,9 +124,11 @@ __host__ __device__ inline size_t fir_x8_smem(int r) {
 
 // Row addressing as fir_x_kernel.  Shared memory: the clamped input segment, one pad float after every
 // eight (thread g reads element 8 g + u: bank 9 g + ..., conflict-free), then the zero-padded taps.
+template <bool kParamTaps>
 __global__ void __launch_bounds__(128) fir_x8_kernel(const float* __restrict__ in, float* __restrict__ out,
                                                      const float* __restrict__ taps, int r, int W,
-                                                     int rows_per_plane, int plane_rows, int row_lo) {
+                                                     int rows_per_plane, int plane_rows, int row_lo,
+                                                     const __grid_constant__ FirTaps ft) {
   extern __shared__ float seg[];
   const int x0 = blockIdx.y * kFirX8Tile;
   const int pl = blockIdx.x / rows_per_plane;
@@ -132,7 +139,8 @@ __global__ void __launch_bounds__(128) fir_x8_kernel(const float* __restrict__ i
   const int seg_px = tile + n_steps;
   float* stap = seg + seg_px + (seg_px >> 3) + 1;
   for (int i = threadIdx.x; i < seg_px; i += blockDim.x) seg[i + (i >> 3)] = __ldg(src + min(max(x0 - r + i, 0), W - 1));
-  for (int i = threadIdx.x; i < n_steps; i += blockDim.x) stap[i] = (i <= 2 * r) ? __ldg(taps + i) : 0.f;
+  if constexpr (!kParamTaps)
+    for (int i = threadIdx.x; i < n_steps; i += blockDim.x) stap[i] = (i <= 2 * r) ? __ldg(taps + i) : 0.f;
   __syncthreads();
   const int g = threadIdx.x;
   if (g * kFir8 >= tile) return;
@@ -145,7 +153,7 @@ __global__ void __launch_bounds__(128) fir_x8_kernel(const float* __restrict__ i
 #pragma unroll
     for (int s = 0; s < 8; ++s) {
       const float v = sb[s];
-      k[s] = stap[u0 + s];
+      k[s] = kParamTaps ? ft.t[u0 + s] : stap[u0 + s];
 #pragma unroll
       for (int q = 0; q < kFir8; ++q) acc[q] = fmaf(k[(s - q) & 7], v, acc[q]);
     }
@@ -157,14 +165,18 @@ __global__ void __launch_bounds__(128) fir_x8_kernel(const float* __restrict__ i
 }
 
 // Row addressing as fir_y_kernel; 8 consecutive rows per thread, one column per lane (coalesced).
+template <bool kParamTaps>
 __global__ void __launch_bounds__(128) fir_y8_kernel(const float* __restrict__ in, float* __restrict__ out,
                                                      const float* __restrict__ taps, int r, int H, int RW,
                                                      int in_row0, int in_rows, int out_row0, int out_rows,
-                                                     int out_buf_row0, int out_plane_rows) {
+                                                     int out_buf_row0, int out_plane_rows,
+                                                     const __grid_constant__ FirTaps ft) {
   extern __shared__ float stap[];
   const int n_steps = fir8_steps(r);
-  for (int i = threadIdx.x; i < n_steps; i += blockDim.x) stap[i] = (i <= 2 * r) ? __ldg(taps + i) : 0.f;
-  __syncthreads();
+  if constexpr (!kParamTaps) {
+    for (int i = threadIdx.x; i < n_steps; i += blockDim.x) stap[i] = (i <= 2 * r) ? __ldg(taps + i) : 0.f;
+    __syncthreads();
+  }
   const int j = blockIdx.x * blockDim.x + threadIdx.x;
   if (j >= RW) return;
   const int yb = blockIdx.y * kFir8;       // first output buffer row of this thread
@@ -179,7 +191,7 @@ __global__ void __launch_bounds__(128) fir_y8_kernel(const float* __restrict__ i
     for (int s = 0; s < 8; ++s) {
       const int y = min(max(y0 - r + u0 + s, 0), H - 1) - in_row0;
       const float v = __ldg(src + (long long)y * RW);
-      k[s] = stap[u0 + s];
+      k[s] = kParamTaps ? ft.t[u0 + s] : stap[u0 + s];
 #pragma unroll
       for (int q = 0; q < kFir8; ++q) acc[q] = fmaf(k[(s - q) & 7], v, acc[q]);
     }

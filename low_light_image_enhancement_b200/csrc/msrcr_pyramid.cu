@@ -299,6 +299,26 @@ int pick_strip(int rows, long long ctas_per_strip_row, int want, int lo, int hi,
   return (rps + mult - 1) / mult * mult;
 }
 
+// Low-resolution separable Gaussian (planar): taps go by value when they fit the kernel-argument struct.
+FirTaps make_fir_taps(const ScalePlan& sp, bool* fits) {
+  FirTaps ft;
+  memset(&ft, 0, sizeof(ft));
+  *fits = fir8_steps(sp.radius_low) <= kFirParamTaps && (int)sp.taps.size() == 2 * sp.radius_low + 1;
+  if (*fits)
+    for (size_t i = 0; i < sp.taps.size(); ++i) ft.t[i] = sp.taps[i];
+  return ft;
+}
+template <class... A>
+void launch_fir_x8(bool param, dim3 grid, size_t smem, cudaStream_t st, A... a) {
+  if (param) fir_x8_kernel<true><<<grid, 128, smem, st>>>(a...);
+  else fir_x8_kernel<false><<<grid, 128, smem, st>>>(a...);
+}
+template <class... A>
+void launch_fir_y8(bool param, dim3 grid, size_t smem, cudaStream_t st, A... a) {
+  if (param) fir_y8_kernel<true><<<grid, 128, smem, st>>>(a...);
+  else fir_y8_kernel<false><<<grid, 128, smem, st>>>(a...);
+}
+
 template <int N6, int N4>
 void launch_final(dim3 grid, cudaStream_t st, const void* x, void* out, bool u8, ImgView v, int io, int W, int in_row0,
                   int row_begin, int row_end, int rps, const FinalParams& fp) {
@@ -438,15 +458,17 @@ int msrcr_pyramid_run_io(llie_ctx* ctx, const void* in, void* out, bool u8, int 
     const float* taps = pl->d_taps + pl->tap_off[k];
     const int r = sp.radius_low;
     const size_t smx = fir_x8_smem(r), smy = (size_t)fir8_steps(r) * sizeof(float);
+    bool tp;
+    const FirTaps ft = make_fir_taps(sp, &tp);
     float* sc = (float*)dSC + (size_t)k * c_elems;
     if (sp.level == 0) {
       dim3 gx((unsigned)((long long)planes * hC), ceil_div(wC, kFirX8Tile)), gy(ceil_div(wC, 128), ceil_div(hC, kFir8), planes);
-      LLIE_LAUNCH(ctx, st, "fir_x_kernel", fir_x8_kernel<<<gx, 128, smx, st>>>((const float*)dC, (float*)dCt, taps, r, wC, planes * hC, 0, 0));
-      LLIE_LAUNCH(ctx, st, "fir_y_kernel", fir_y8_kernel<<<gy, 128, smy, st>>>((const float*)dCt, sc, taps, r, hC, wC, 0, hC, 0, hC, 0, hC));
+      LLIE_LAUNCH(ctx, st, "fir_x_kernel", (launch_fir_x8(tp, gx, smx, st, (const float*)dC, (float*)dCt, taps, r, wC, planes * hC, 0, 0, ft)));
+      LLIE_LAUNCH(ctx, st, "fir_y_kernel", (launch_fir_y8(tp, gy, smy, st, (const float*)dCt, sc, taps, r, hC, wC, 0, hC, 0, hC, 0, hC, ft)));
     } else {
       dim3 gx((unsigned)((long long)planes * hB), ceil_div(wB, kFirX8Tile)), gy(ceil_div(wB, 128), ceil_div(hB, kFir8), planes);
-      LLIE_LAUNCH(ctx, st, "fir_x_kernel", fir_x8_kernel<<<gx, 128, smx, st>>>((const float*)dB, (float*)dBt, taps, r, wB, planes * hB, 0, 0));
-      LLIE_LAUNCH(ctx, st, "fir_y_kernel", fir_y8_kernel<<<gy, 128, smy, st>>>((const float*)dBt, (float*)dSB, taps, r, hB, wB, 0, hB, 0, hB, 0, hB));
+      LLIE_LAUNCH(ctx, st, "fir_x_kernel", (launch_fir_x8(tp, gx, smx, st, (const float*)dB, (float*)dBt, taps, r, wB, planes * hB, 0, 0, ft)));
+      LLIE_LAUNCH(ctx, st, "fir_y_kernel", (launch_fir_y8(tp, gy, smy, st, (const float*)dBt, (float*)dSB, taps, r, hB, wB, 0, hB, 0, hB, 0, hB, ft)));
       dim3 ux(ceil_div((long long)hB * up_bc_x_groups(wC), 256), 1, planes), uy(ceil_div(wC, 128), up_bc_y_chunks(0, hC), planes);
       LLIE_LAUNCH(ctx, st, "up_bc_x_kernel", up_bc_x_kernel<<<ux, 256, 0, st>>>((const float*)dSB, (float*)dT2, hB, wB, wC, 0, hB, pl->uw));
       LLIE_LAUNCH(ctx, st, "up_bc_y_kernel", up_bc_y_kernel<<<uy, 128, 0, st>>>((const float*)dT2, sc, hB, hC, wC, 0, hC, pl->uw));
@@ -618,17 +640,19 @@ int tiled_phase_b(llie_ctx* ctx, int d, int n_dev, llie_ctx* const* ctxs, const 
     const float* taps = pl->d_taps + pl->tap_off[k];
     const int r = sp.radius_low;
     const size_t smx = fir_x8_smem(r), smy = (size_t)fir8_steps(r) * sizeof(float);
+    bool tp;
+    const FirTaps ft = make_fir_taps(sp, &tp);
     float* sc = b.SC + (size_t)k * c_elems;
     if (sp.level == 0) {
       const int x0 = clampi(g.s_lo - r, 0, hC), x1 = clampi(g.s_hi + r, 0, hC);
       dim3 gx(3 * (x1 - x0), ceil_div(wC, kFirX8Tile)), gy(ceil_div(wC, 128), ceil_div(g.s_hi - g.s_lo, kFir8), 3);
-      LLIE_LAUNCH(ctx, st, "fir_x_kernel", fir_x8_kernel<<<gx, 128, smx, st>>>(b.C, b.Ct, taps, r, wC, x1 - x0, hC, x0));
-      LLIE_LAUNCH(ctx, st, "fir_y_kernel", fir_y8_kernel<<<gy, 128, smy, st>>>(b.Ct, sc, taps, r, hC, wC, 0, hC, g.s_lo, g.s_hi - g.s_lo, g.s_lo, hC));
+      LLIE_LAUNCH(ctx, st, "fir_x_kernel", (launch_fir_x8(tp, gx, smx, st, b.C, b.Ct, taps, r, wC, x1 - x0, hC, x0, ft)));
+      LLIE_LAUNCH(ctx, st, "fir_y_kernel", (launch_fir_y8(tp, gy, smy, st, b.Ct, sc, taps, r, hC, wC, 0, hC, g.s_lo, g.s_hi - g.s_lo, g.s_lo, hC, ft)));
     } else {
       const int x0 = clampi(g.t_lo - r, 0, hB), x1 = clampi(g.t_hi + r, 0, hB);
       dim3 gx(3 * (x1 - x0), ceil_div(wB, kFirX8Tile)), gy(ceil_div(wB, 128), ceil_div(g.t_hi - g.t_lo, kFir8), 3);
-      LLIE_LAUNCH(ctx, st, "fir_x_kernel", fir_x8_kernel<<<gx, 128, smx, st>>>(b.B, b.Bt, taps, r, wB, x1 - x0, hB, x0));
-      LLIE_LAUNCH(ctx, st, "fir_y_kernel", fir_y8_kernel<<<gy, 128, smy, st>>>(b.Bt, b.SB, taps, r, hB, wB, 0, hB, g.t_lo, g.t_hi - g.t_lo, g.t_lo, hB));
+      LLIE_LAUNCH(ctx, st, "fir_x_kernel", (launch_fir_x8(tp, gx, smx, st, b.B, b.Bt, taps, r, wB, x1 - x0, hB, x0, ft)));
+      LLIE_LAUNCH(ctx, st, "fir_y_kernel", (launch_fir_y8(tp, gy, smy, st, b.Bt, b.SB, taps, r, hB, wB, 0, hB, g.t_lo, g.t_hi - g.t_lo, g.t_lo, hB, ft)));
       dim3 ux(ceil_div((long long)(g.t_hi - g.t_lo) * up_bc_x_groups(wC), 256), 1, 3), uy(ceil_div(wC, 128), up_bc_y_chunks(g.s_lo, g.s_hi), 3);
       LLIE_LAUNCH(ctx, st, "up_bc_x_kernel", up_bc_x_kernel<<<ux, 256, 0, st>>>(b.SB, b.T2, hB, wB, wC, g.t_lo, g.t_hi, pl->uw));
       LLIE_LAUNCH(ctx, st, "up_bc_y_kernel", up_bc_y_kernel<<<uy, 128, 0, st>>>(b.T2, sc, hB, hC, wC, g.s_lo, g.s_hi, pl->uw));
