@@ -354,11 +354,16 @@ class Enhancer:
             s = ci & 1
             lo, hi = ci * per, min(n, (ci + 1) * per)
             cnt = (hi - lo) * frame
-            if ci >= 2:
+            # The host blocks only where it touches a staging buffer itself.  With pinned input and output it never
+            # does: every buffer reuse below is ordered by stream-side event waits, so all chunks are enqueued ahead
+            # and H2D(ci) overlaps D2H(ci-2) (a host-side wait here serialised the two directions of the link).
+            if ci >= 2 and not out_pinned:
                 ev_out[s].synchronize()            # slot s: its previous D2H is done
                 self._drain(pending, y_flat, yp, frame, upto_slot=s)
             src = x_flat[lo * frame:hi * frame]
             if not in_pinned:
+                if ci >= 2:
+                    ev_in[s].synchronize()         # the previous H2D out of xp[s] is done
                 xp[s][:cnt].copy_(src)             # pageable -> pinned staging (host memcpy)
                 src = xp[s][:cnt]
             with torch.cuda.stream(h2d):
