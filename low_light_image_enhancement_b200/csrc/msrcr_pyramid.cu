@@ -322,10 +322,16 @@ void launch_fir_y8(bool param, dim3 grid, size_t smem, cudaStream_t st, A... a) 
 template <int N6, int N4>
 void launch_final(dim3 grid, cudaStream_t st, const void* x, void* out, bool u8, ImgView v, int io, int W, int in_row0,
                   int row_begin, int row_end, int rps, const FinalParams& fp) {
-  if (u8)
-    msrcr_final_kernel<N6, N4, uint8_t><<<grid, 128, 0, st>>>((const uint8_t*)x, (uint8_t*)out, v, io, W, in_row0, row_begin, row_end, rps, fp);
-  else
-    msrcr_final_kernel<N6, N4, float><<<grid, 128, 0, st>>>((const float*)x, (float*)out, v, io, W, in_row0, row_begin, row_end, rps, fp);
+  // equal weights over the scales of this launch and values bounded so that their product cannot overflow
+  bool eq = fp.in_scale * 255.f + fp.in_bias <= 1e9f && fp.in_bias >= 1e-9f;
+  for (int i = 1; i < N6 + N4; ++i) eq = eq && fp.w2[i] == fp.w2[0];
+  if (u8) {
+    if (eq) msrcr_final_kernel<N6, N4, uint8_t, true><<<grid, 128, 0, st>>>((const uint8_t*)x, (uint8_t*)out, v, io, W, in_row0, row_begin, row_end, rps, fp);
+    else msrcr_final_kernel<N6, N4, uint8_t, false><<<grid, 128, 0, st>>>((const uint8_t*)x, (uint8_t*)out, v, io, W, in_row0, row_begin, row_end, rps, fp);
+  } else {
+    if (eq) msrcr_final_kernel<N6, N4, float, true><<<grid, 128, 0, st>>>((const float*)x, (float*)out, v, io, W, in_row0, row_begin, row_end, rps, fp);
+    else msrcr_final_kernel<N6, N4, float, false><<<grid, 128, 0, st>>>((const float*)x, (float*)out, v, io, W, in_row0, row_begin, row_end, rps, fp);
+  }
 }
 
 
