@@ -51,6 +51,12 @@ extern "C" {
 #define LLIE_BLUR_PYRAMID 0 /* decimated Gaussian cascade, O(1) per pixel in sigma; needs sigma >= 12 */
 #define LLIE_BLUR_DIRECT 1  /* exact truncated FIR, O(sigma) per pixel; GPU ground truth   */
 
+/* MSRCR global-statistics finishers: applied per image and per channel to the un-clipped
+ * value v = (G C R + b) / 255 instead of the plain clip to [0, 1] */
+#define LLIE_FINISH_NONE 0    /* out = clip(v, 0, 1)                                                  */
+#define LLIE_FINISH_MINMAX 1  /* out = (v - min) / (max - min)                                        */
+#define LLIE_FINISH_MEANSTD 2 /* out = clip((v - (mean - k std)) / (2 k std), 0, 1), population std */
+
 #define LLIE_MAX_SCALES 8
 
 /* north_star (a): "multi-scale Gaussian surround at sigma=15/80/250, log-ratio, colour
@@ -64,6 +70,8 @@ typedef struct llie_msrcr_params {
   float alpha, beta, gain, offset;
   float in_scale, in_bias; /* I = in_scale * x + in_bias */
   int32_t blur;            /* LLIE_BLUR_* */
+  int32_t finish;          /* LLIE_FINISH_* (fp32 images, LLIE_BLUR_PYRAMID) */
+  float finish_k;          /* k of LLIE_FINISH_MEANSTD (default 2) */
 } llie_msrcr_params;
 
 /* north_star (b): "8 iterations of LE(x)=x+alpha*x*(1-x)"; SURVEY.md 9.2. */

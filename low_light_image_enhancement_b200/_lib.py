@@ -14,6 +14,7 @@ LIB_PATH = os.path.join(HERE, "libllie.so")
 OK, E_ARG, E_SHAPE, E_DTYPE, E_CUDA, E_NOPEER, E_NOMEM, E_STATE = 0, -1, -2, -3, -4, -5, -6, -7
 NHWC, NCHW = 0, 1
 F32, BF16, F32_SIMT = 0, 1, 2
+FINISH = {"none": 0, "minmax": 1, "meanstd": 2}
 BLUR_PYRAMID, BLUR_DIRECT = 0, 1
 MAX_SCALES = 8
 
@@ -36,6 +37,7 @@ class MsrcrParams(C.Structure):
         ("sigma", C.c_float * MAX_SCALES), ("weight", C.c_float * MAX_SCALES),
         ("truncate", C.c_float), ("alpha", C.c_float), ("beta", C.c_float), ("gain", C.c_float),
         ("offset", C.c_float), ("in_scale", C.c_float), ("in_bias", C.c_float), ("blur", C.c_int32),
+        ("finish", C.c_int32), ("finish_k", C.c_float),
     ]
 
 

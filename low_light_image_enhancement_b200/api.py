@@ -27,7 +27,8 @@ def default_msrcr_params() -> dict:
     _lib.check(_lib.load().llie_msrcr_default_params(C.byref(p)))
     n = p.n_scales
     return dict(sigmas=tuple(p.sigma[:n]), weights=tuple(p.weight[:n]), truncate=p.truncate, alpha=p.alpha,
-                beta=p.beta, gain=p.gain, offset=p.offset, in_scale=p.in_scale, in_bias=p.in_bias, blur="pyramid")
+                beta=p.beta, gain=p.gain, offset=p.offset, in_scale=p.in_scale, in_bias=p.in_bias, blur="pyramid",
+                finish="none", finish_k=p.finish_k)
 
 
 def default_dce_params() -> dict:
@@ -129,6 +130,9 @@ def _msrcr_struct(params: dict | None) -> MsrcrParams:
     if blur not in ("pyramid", "direct"):
         raise ValueError("blur must be 'pyramid' or 'direct'")
     p.blur = _lib.BLUR_PYRAMID if blur == "pyramid" else _lib.BLUR_DIRECT
+    if d["finish"] not in _lib.FINISH:
+        raise ValueError("finish must be 'none', 'minmax' or 'meanstd'")
+    p.finish, p.finish_k = _lib.FINISH[d["finish"]], float(d["finish_k"])
     return p
 
 
@@ -525,7 +529,8 @@ def enhance(images, method: str, params: dict | None = None, *, out=None, device
              CUDA tensors are processed in place on their device and stream (zero copy); NumPy
              arrays and CPU tensors are staged through pinned memory.
     method : 'msrcr'  -- params: sigmas, weights, truncate, alpha, beta, gain, offset, in_scale,
-                         in_bias, blur ('pyramid' | 'direct')
+                         in_bias, blur ('pyramid' | 'direct'), finish ('none' | 'minmax' | 'meanstd': per-image,
+                         per-channel stretch of the un-clipped result by min/max or mean +- finish_k std)
              'zero_dce' -- params: weights (79 416-float blob or [(W, b)] * 7), iters, curve_sign,
                          precision ('fp32' = hi/lo-split bf16 on the tensor cores, fp32-accurate |
                          'bf16' | 'fp32_simt' = plain fp32 FMA on the CUDA cores), return_maps

@@ -105,6 +105,8 @@ int llie_msrcr_default_params(llie_msrcr_params* p) {
   p->alpha = 125.f; p->beta = 46.f; p->gain = 0.6f; p->offset = 128.f;
   p->in_scale = 255.f; p->in_bias = 1.f;
   p->blur = LLIE_BLUR_PYRAMID;
+  p->finish = LLIE_FINISH_NONE;
+  p->finish_k = 2.0f;
   return LLIE_OK;
 }
 
@@ -231,6 +233,11 @@ static int check_msrcr_params(const llie_msrcr_params* p) {
   LLIE_REQUIRE(p->truncate > 0.f && p->truncate <= 8.f, LLIE_E_ARG, "truncate %g out of range", p->truncate);
   LLIE_REQUIRE(p->in_bias > 0.f && p->in_scale >= 0.f, LLIE_E_ARG, "in_scale/in_bias must keep I = scale*x+bias positive");
   LLIE_REQUIRE(p->blur == LLIE_BLUR_PYRAMID || p->blur == LLIE_BLUR_DIRECT, LLIE_E_ARG, "unknown blur mode %d", p->blur);
+  LLIE_REQUIRE(p->finish >= LLIE_FINISH_NONE && p->finish <= LLIE_FINISH_MEANSTD, LLIE_E_ARG, "unknown finish mode %d", p->finish);
+  LLIE_REQUIRE(p->finish == LLIE_FINISH_NONE || p->blur == LLIE_BLUR_PYRAMID, LLIE_E_ARG,
+               "global-statistics finishers need the pyramid blur");
+  LLIE_REQUIRE(p->finish != LLIE_FINISH_MEANSTD || (p->finish_k > 0.f && p->finish_k <= 16.f), LLIE_E_ARG,
+               "finish_k %g out of range (0, 16]", p->finish_k);
   return LLIE_OK;
 }
 
@@ -245,6 +252,7 @@ int llie_msrcr_f32(llie_ctx* ctx, const float* in, float* out, int n, int h, int
   int rc = params->blur == LLIE_BLUR_DIRECT ? msrcr_direct_run(ctx, in, out, n, h, w, layout, *params, st)
                                             : msrcr_pyramid_run(ctx, in, out, n, h, w, layout, *params, st);
   LLIE_TRY(rc);
+  if (params->finish != LLIE_FINISH_NONE) LLIE_TRY(msrcr_finish_run(ctx, out, n, h, w, layout, *params, st));
   if (!stream) LLIE_CUDA_OK(cudaStreamSynchronize(st));
   return LLIE_OK;
 }
@@ -255,6 +263,7 @@ int llie_msrcr_u8(llie_ctx* ctx, const uint8_t* in, uint8_t* out, int n, int h, 
   LLIE_TRY(check_batch(in, out, n, h, w, layout));
   LLIE_TRY(check_msrcr_params(params));
   LLIE_REQUIRE(params->blur == LLIE_BLUR_PYRAMID, LLIE_E_DTYPE, "uint8 images are supported by the pyramid blur only");
+  LLIE_REQUIRE(params->finish == LLIE_FINISH_NONE, LLIE_E_DTYPE, "global-statistics finishers need fp32 images");
   if (n == 0) return LLIE_OK;
   DeviceGuard g(ctx->device);
   cudaStream_t st = stream ? (cudaStream_t)stream : ctx->stream;

@@ -121,6 +121,8 @@ inline int check_launch(llie_ctx* ctx, const char* what, cudaStream_t st = nullp
 // kernels' host entry points (one per .cu)
 int msrcr_direct_run(llie_ctx* ctx, const float* in, float* out, int n, int h, int w, int layout,
                      const llie_msrcr_params& p, cudaStream_t st);
+int msrcr_finish_run(llie_ctx* ctx, float* out, int n, int h, int w, int layout, const llie_msrcr_params& p,
+                     cudaStream_t st);  // msrcr_finish.cu
 int msrcr_pyramid_run_io(llie_ctx* ctx, const void* in, void* out, bool u8, int n, int h, int w, int layout,
                          const llie_msrcr_params& p, cudaStream_t st);
 int dce_forward_u8(llie_ctx* ctx, const uint8_t* in, uint8_t* out, float* maps, int n, int h, int w, int layout,

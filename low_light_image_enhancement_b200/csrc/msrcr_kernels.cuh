@@ -344,6 +344,7 @@ struct FinalParams {
   float beta_ln_alpha, beta_ln2, gain255, offset255, in_scale, in_bias;
   const float* acc_in;  // optional partial sums  sum_k w2_k lg2 S_k  from an earlier pass (image layout)
   float* acc_out;       // if set: write the partial sums instead of the finished pixels
+  int no_clip;          // write the un-clipped value (a global-statistics finisher follows)
 };
 
 constexpr int kFinalCells = 123;
@@ -635,7 +636,8 @@ msrcr_final_kernel(const TIO* __restrict__ x, TIO* __restrict__ out, ImgView v, 
             for (int c = 0; c < 3; ++c) {
               const float R = fmaf(p.wsum2, l[c], -acc[i][c]);
               const float Cc = fmaf(p.beta_ln2, l[c] - lsum, p.beta_ln_alpha);
-              o[i][c] = __saturatef(fmaf(p.gain255 * Cc, R, p.offset255));
+              const float val = fmaf(p.gain255 * Cc, R, p.offset255);
+              o[i][c] = p.no_clip ? val : __saturatef(val);
             }
           }
           final_store(out, v, io, img, yl, X0, W, o);

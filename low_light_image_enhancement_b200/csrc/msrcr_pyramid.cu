@@ -356,6 +356,7 @@ int final_passes(llie_ctx* ctx, cudaStream_t st, const MsrcrPlan* pl, const llie
   fp.gain255 = p.gain / 255.f;
   fp.offset255 = p.offset / 255.f;
   fp.in_scale = u8 ? p.in_scale / 255.f : p.in_scale; fp.in_bias = p.in_bias;  // uint8 images are read as 0..255
+  fp.no_clip = (!u8 && p.finish != LLIE_FINISH_NONE) ? 1 : 0;
   int n6 = 0;
   for (auto& sc : pl->scales) n6 += (sc.level == 0);
   if (p.n_scales == 3 && n6 == 1) {

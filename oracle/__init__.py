@@ -19,7 +19,7 @@ reference legs may import this package.  The product path
 (low_light_image_enhancement_b200) never does.
 """
 from .msrcr import (MSRCR_DEFAULTS, gaussian_kernel_1d, blur_edge_clamp,
-                    msrcr, msrcr_window)
+                    msrcr, msrcr_window, msrcr_unclipped)
 from .zero_dce import (DCE_LAYERS, DCE_NUM_PARAMS, init_weights, pack_weights,
                        unpack_weights, dce_net, apply_curves, zero_dce)
 from .synth import synth_lowlight
@@ -27,7 +27,7 @@ from .u8 import from_u8, to_u8, msrcr_u8, zero_dce_u8
 
 __all__ = [
     "MSRCR_DEFAULTS", "gaussian_kernel_1d", "blur_edge_clamp", "msrcr",
-    "msrcr_window", "DCE_LAYERS", "DCE_NUM_PARAMS", "init_weights",
+    "msrcr_window", "msrcr_unclipped", "DCE_LAYERS", "DCE_NUM_PARAMS", "init_weights",
     "pack_weights", "unpack_weights", "dce_net", "apply_curves", "zero_dce",
     "synth_lowlight", "from_u8", "to_u8", "msrcr_u8", "zero_dce_u8",
 ]

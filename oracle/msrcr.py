@@ -10,6 +10,9 @@ infrastructure only; float64 arithmetic on float32 inputs.
     R      = sum_s w_s (ln I - ln S_s)
     C      = beta (ln(alpha I) - ln(I_R + I_G + I_B))
     out    = clip((G C R + b) / 255, 0, 1)
+    finish: instead of the plain clip, per channel over the whole image,
+            "minmax":  (v - min v) / (max v - min v)          with v = (G C R + b) / 255
+            "meanstd": clip((v - (m - k s)) / (2 k s), 0, 1)  with m, s = mean, population std of v
 """
 from __future__ import annotations
 
@@ -27,6 +30,8 @@ MSRCR_DEFAULTS = dict(
     offset=128.0,
     in_scale=255.0,
     in_bias=1.0,
+    finish="none",   # "none" | "minmax" | "meanstd" (per image, per channel)
+    finish_k=2.0,
 )
 
 
@@ -81,14 +86,12 @@ def blur_edge_clamp(img: np.ndarray, sigma: float, truncate: float = 4.0,
     return f(f(img, k, 1), k, 0)
 
 
-def msrcr(x: np.ndarray, params: dict | None = None, mode: str = "fft") -> np.ndarray:
-    """MSRCR on (H, W, 3) or (N, H, W, 3) float32 in [0, 1] -> float32 in [0, 1]."""
+def msrcr_unclipped(x: np.ndarray, params: dict | None = None, mode: str = "fft") -> np.ndarray:
+    """v = (G C R + b) / 255 of one (H, W, 3) image, float64, before any clip or finisher."""
     p = dict(MSRCR_DEFAULTS)
     if params:
         p.update(params)
     x = np.asarray(x)
-    if x.ndim == 4:
-        return np.stack([msrcr(xi, p, mode) for xi in x])
     assert x.ndim == 3 and x.shape[2] == 3, x.shape
     I = p["in_scale"] * x.astype(np.float64) + p["in_bias"]
     logI = np.log(I)
@@ -97,7 +100,28 @@ def msrcr(x: np.ndarray, params: dict | None = None, mode: str = "fft") -> np.nd
         S = blur_edge_clamp(I, s, p["truncate"], mode)
         R += w * (logI - np.log(S))
     C = p["beta"] * (np.log(p["alpha"] * I) - np.log(I.sum(axis=2, keepdims=True)))
-    out = (p["gain"] * C * R + p["offset"]) / 255.0
+    return (p["gain"] * C * R + p["offset"]) / 255.0
+
+
+def msrcr(x: np.ndarray, params: dict | None = None, mode: str = "fft") -> np.ndarray:
+    """MSRCR on (H, W, 3) or (N, H, W, 3) float32 in [0, 1] -> float32 in [0, 1]."""
+    p = dict(MSRCR_DEFAULTS)
+    if params:
+        p.update(params)
+    x = np.asarray(x)
+    if x.ndim == 4:
+        return np.stack([msrcr(xi, p, mode) for xi in x])
+    out = msrcr_unclipped(x, p, mode)
+    if p["finish"] != "none":
+        # global-statistics finisher: stretch the UN-clipped value per channel over the whole image
+        if p["finish"] == "minmax":
+            lo, hi = out.min(axis=(0, 1)), out.max(axis=(0, 1))
+        elif p["finish"] == "meanstd":
+            m, sd = out.mean(axis=(0, 1)), out.std(axis=(0, 1))   # population standard deviation
+            lo, hi = m - p["finish_k"] * sd, m + p["finish_k"] * sd
+        else:
+            raise ValueError(p["finish"])
+        out = np.where(hi > lo, (out - lo) / np.where(hi > lo, hi - lo, 1.0), 0.0)
     return np.clip(out, 0.0, 1.0).astype(np.float32)
 
 

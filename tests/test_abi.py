@@ -45,7 +45,7 @@ def test_version_and_defaults(lib_built):
 
 def test_struct_sizes_match_header_layout():
     # uint32 + int32 + 8f + 8f + 7f + int32
-    assert C.sizeof(_lib.MsrcrParams) == 4 + 4 + 32 + 32 + 28 + 4
+    assert C.sizeof(_lib.MsrcrParams) == 4 + 4 + 32 + 32 + 28 + 4 + 4 + 4
     assert C.sizeof(_lib.DceParams) == 16
 
 

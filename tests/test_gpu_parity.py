@@ -124,6 +124,30 @@ def test_msrcr_4k_windowed_oracle():
         assert np.abs(y[y0:y0 + 96, x0:x0 + 96] - ref).max() <= TOL_F32, (y0, x0)
 
 
+# ---------------------------------------------------------------- global-statistics finishers
+@pytest.mark.parametrize("finish", ["minmax", "meanstd"])
+def test_msrcr_finishers_match_oracle(finish):
+    """SURVEY.md 8(f) rank 2.  The stretch divides by (hi - lo) of the un-clipped value, which amplifies the 1e-4
+    budget of the fp32 path by 1 / (hi - lo); the bound below carries that factor."""
+    xs = np.stack([oracle.synth_lowlight(150, 220, s) * g for s, g in ((1, 1.0), (2, 4.0), (3, 7.0))]).astype(np.float32)
+    prm = dict(finish=finish, finish_k=1.5)
+    ref = oracle.msrcr(xs, prm)
+    y = L.enhance(xs, "msrcr", prm)
+    for i in range(3):
+        v = oracle.msrcr_unclipped(xs[i])
+        rng = (v.max(axis=(0, 1)) - v.min(axis=(0, 1))) if finish == "minmax" else 3.0 * v.std(axis=(0, 1))
+        tol = TOL_F32 / rng.min() + 2e-6
+        assert np.abs(y[i] - ref[i]).max() <= tol, (i, float(np.abs(y[i] - ref[i]).max()), tol)
+    if finish == "minmax":
+        assert y.min() == 0.0 and y.max() == 1.0
+    # NCHW device tensor, one image: same statistics, same result
+    xc = torch.from_numpy(np.ascontiguousarray(xs[1].transpose(2, 0, 1))[None]).cuda()
+    yc = L.enhance(xc, "msrcr", dict(prm, layout="NCHW"))[0].cpu().numpy().transpose(1, 2, 0)
+    assert np.abs(yc - y[1]).max() <= 1e-6
+    with pytest.raises(L.LlieError):
+        L.enhance(xs, "msrcr", dict(finish=finish, blur="direct"))
+
+
 # ---------------------------------------------------------------- Zero-DCE ----------------
 F32_PATHS = ["fp32", "fp32_simt"]   # hi/lo-split bf16 on the tensor cores | plain fp32 FMA on the CUDA cores
 

@@ -139,3 +139,15 @@ def test_u8_convention_round_trips():
     b = np.arange(256, dtype=np.uint8)
     assert np.array_equal(oracle.to_u8(oracle.from_u8(b)), b)
     assert oracle.to_u8(np.array([0.5 / 255, 1.5 / 255, -1.0, 2.0, 0.4999 / 255])).tolist() == [0, 2, 0, 255, 0]
+
+
+def test_msrcr_finishers_kat():
+    """min/max stretch reaches exactly 0 and 1 in every channel; mean/std stretch centres the
+    un-clipped value at 0.5 and is invariant to gain and offset (an affine map of v cancels in the stretch)."""
+    x = oracle.synth_lowlight(64, 80, 5)
+    y = oracle.msrcr(x, dict(finish="minmax"))
+    assert np.all(y.min(axis=(0, 1)) == 0.0) and np.all(y.max(axis=(0, 1)) == 1.0)
+    a = oracle.msrcr(x, dict(finish="meanstd", finish_k=3.0))
+    b = oracle.msrcr(x, dict(finish="meanstd", finish_k=3.0, gain=0.3, offset=60.0))
+    assert np.abs(a - b).max() <= 1e-6
+    assert np.abs(a.mean(axis=(0, 1)) - 0.5).max() <= 0.05     # clipping of the tails moves the mean only slightly
