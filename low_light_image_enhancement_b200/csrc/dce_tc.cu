@@ -14,6 +14,12 @@
 
 #include <cstring>
 
+#ifdef LLIE_MBAR_TRACE
+extern "C" int llie_debug_set_trace(void* host_mapped) {
+  return (int)cudaMemcpyToSymbol(g_llie_trace, &host_mapped, sizeof(void*));
+}
+#endif
+
 namespace llie {
 
 namespace {

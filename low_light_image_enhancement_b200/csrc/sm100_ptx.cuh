@@ -6,6 +6,10 @@
 #include <cstdint>
 #include <cstdio>
 
+#ifdef LLIE_MBAR_TRACE
+static __device__ unsigned long long* g_llie_trace = nullptr;  // per translation unit; set by llie_debug_set_trace
+#endif
+
 namespace llie {
 namespace ptx {
 
@@ -36,7 +40,19 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
 // Bounded spin: a protocol bug traps (launch error) instead of hanging the GPU.
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   for (uint32_t spins = 0; !mbar_try_wait(bar, parity); ++spins) {
-#ifdef LLIE_MBAR_DEBUG
+#ifdef LLIE_MBAR_TRACE
+    if (spins > (1u << 22)) {   // record who is stuck in host-mapped memory (survives the trap), then trap
+      if (g_llie_trace) {
+        const unsigned long long rec = ((unsigned long long)blockIdx.x << 48) | ((unsigned long long)(threadIdx.x >> 5) << 40) |
+                                       ((unsigned long long)parity << 32) | smem_u32(bar);
+        const unsigned long long slot = atomicAdd(g_llie_trace, 1ull);
+        if (slot < 1000) g_llie_trace[1 + slot] = rec;
+        __threadfence_system();
+      }
+      __nanosleep(2000000);
+      __trap();
+    }
+#elif defined(LLIE_MBAR_DEBUG)
     if (spins > (1u << 22)) {
       printf("mbar timeout: block %d warp %d bar@%u parity %u\n", blockIdx.x, threadIdx.x >> 5, smem_u32(bar), parity);
       return;
