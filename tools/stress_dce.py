@@ -1,3 +1,7 @@
+"""Stress matrix for the fused Zero-DCE chains (run on a B200): for many batch sizes / frame sizes the fused result
+must equal the one-launch-per-layer result bitwise, each case in its own process (a trap kills the context).
+    python tools/stress_dce.py
+"""
 import sys, subprocess
 CASE = r'''
 import sys, torch
