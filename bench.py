@@ -340,6 +340,21 @@ def gpu_workload(dist, name, steps, warmup, peaks, with_e2e=True, with_cpu=True,
                       "steps": e2e_steps, "api": "enhance(pinned torch CPU tensor, out=pinned) -> staged 3-stream pipeline"}
         if not torch.equal(yh, y.cpu()):
             res["e2e"]["warning"] = "host-path result differs from device-path result"
+        if io == "u8":   # the same frames one by one through the streaming front-end
+            frames = [xh[i] for i in range(n_local)]
+
+            def stream_step():
+                k = 0
+                for yf in enh.stream(frames, method, params, depth=4, copy=False):
+                    if k == n_local - 1:
+                        stream_step.last = yf.clone()
+                    k += 1
+            ms_s = run_e2e(dist, stream_step, e2e_steps, warmup)
+            res["e2e_stream"] = {"value": round(px_total / ms_s / 1e3, 1), "unit": "Mpixel/s", "ms_per_step": round(ms_s, 3),
+                                 "frames_per_s": round(total_frames / ms_s * 1e3, 1),
+                                 "api": "enhance_stream(pinned frames, depth=4, copy=False): one frame per item"}
+            if not torch.equal(stream_step.last, y[n_local - 1].cpu()):
+                res["e2e_stream"]["warning"] = "stream result differs from device-path result"
     if with_cpu and rank == 0:
         x0 = x[0].cpu().numpy()
         res["cpu_baseline"] = cpu_baseline(name, x0 if io == "f32" else x0.astype(np.float32) / np.float32(255), params)

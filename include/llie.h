@@ -56,6 +56,8 @@ extern "C" {
 #define LLIE_FINISH_NONE 0    /* out = clip(v, 0, 1)                                                  */
 #define LLIE_FINISH_MINMAX 1  /* out = (v - min) / (max - min)                                        */
 #define LLIE_FINISH_MEANSTD 2 /* out = clip((v - (mean - k std)) / (2 k std), 0, 1), population std */
+#define LLIE_FINISH_PERCENTILE 3 /* out = clip((v - lo) / (hi - lo), 0, 1); lo / hi = the r-th smallest / largest
+                                    value, r = floor(N k / 100) ("simplest colour balance", k percent per tail) */
 
 #define LLIE_MAX_SCALES 8
 
@@ -71,7 +73,7 @@ typedef struct llie_msrcr_params {
   float in_scale, in_bias; /* I = in_scale * x + in_bias */
   int32_t blur;            /* LLIE_BLUR_* */
   int32_t finish;          /* LLIE_FINISH_* (fp32 images, LLIE_BLUR_PYRAMID) */
-  float finish_k;          /* k of LLIE_FINISH_MEANSTD (default 2) */
+  float finish_k;          /* k of LLIE_FINISH_MEANSTD (default 2) / percent per tail of LLIE_FINISH_PERCENTILE */
 } llie_msrcr_params;
 
 /* north_star (b): "8 iterations of LE(x)=x+alpha*x*(1-x)"; SURVEY.md 9.2. */

@@ -14,7 +14,7 @@ LIB_PATH = os.path.join(HERE, "libllie.so")
 OK, E_ARG, E_SHAPE, E_DTYPE, E_CUDA, E_NOPEER, E_NOMEM, E_STATE = 0, -1, -2, -3, -4, -5, -6, -7
 NHWC, NCHW = 0, 1
 F32, BF16, F32_SIMT = 0, 1, 2
-FINISH = {"none": 0, "minmax": 1, "meanstd": 2}
+FINISH = {"none": 0, "minmax": 1, "meanstd": 2, "percentile": 3}
 BLUR_PYRAMID, BLUR_DIRECT = 0, 1
 MAX_SCALES = 8
 

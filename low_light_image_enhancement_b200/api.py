@@ -131,7 +131,7 @@ def _msrcr_struct(params: dict | None) -> MsrcrParams:
         raise ValueError("blur must be 'pyramid' or 'direct'")
     p.blur = _lib.BLUR_PYRAMID if blur == "pyramid" else _lib.BLUR_DIRECT
     if d["finish"] not in _lib.FINISH:
-        raise ValueError("finish must be 'none', 'minmax' or 'meanstd'")
+        raise ValueError("finish must be 'none', 'minmax', 'meanstd' or 'percentile'")
     p.finish, p.finish_k = _lib.FINISH[d["finish"]], float(d["finish_k"])
     return p
 
@@ -273,18 +273,7 @@ class Enhancer:
         if not t.is_contiguous():
             raise ValueError("images must be contiguous")
         n, h, w, layout, batched = _resolve_layout(t.shape, params.get("layout"))
-        if method == "msrcr":
-            mp, dp, want_maps = _msrcr_struct(params), None, False
-        else:
-            d = default_dce_params()
-            unknown = set(params) - set(d) - {"layout"}
-            if unknown:
-                raise ValueError(f"unknown zero_dce params: {sorted(unknown)}")
-            d.update({k: v for k, v in params.items() if k != "layout"})
-            if d["weights"] is None:
-                raise ValueError("zero_dce needs params['weights'] (packed blob or list of (W, b))")
-            self.set_dce_weights(d["weights"])
-            mp, dp, want_maps = None, _dce_struct(d), bool(d["return_maps"])
+        mp, dp, want_maps = self._method_structs(method, params)
 
         if t.is_cuda:
             if t.device.index != self.device:
@@ -305,6 +294,94 @@ class Enhancer:
         # host path: stage through pinned memory in frame chunks, overlapping H2D / compute / D2H
         y_t = self._host_pipeline(t, n, h, w, layout, mp, dp, want_maps, out, is_np)
         return y_t
+
+    def _method_structs(self, method: str, params: dict):
+        """(MsrcrParams | None, DceParams | None, want_maps) of one enhance() call; uploads the DCE-Net weights."""
+        if method == "msrcr":
+            return _msrcr_struct(params), None, False
+        d = default_dce_params()
+        unknown = set(params) - set(d) - {"layout"}
+        if unknown:
+            raise ValueError(f"unknown zero_dce params: {sorted(unknown)}")
+        d.update({k: v for k, v in params.items() if k != "layout"})
+        if d["weights"] is None:
+            raise ValueError("zero_dce needs params['weights'] (packed blob or list of (W, b))")
+        self.set_dce_weights(d["weights"])
+        return None, _dce_struct(d), bool(d["return_maps"])
+
+    def stream(self, frames, method: str, params: dict | None = None, *, depth: int = 3, copy: bool = True):
+        """Generator behind enhance_stream(): see there.  Parameters are checked here, before the first frame."""
+        params = dict(params or {})
+        if method not in ("msrcr", "zero_dce"):
+            raise ValueError(f"method must be 'msrcr' or 'zero_dce', got {method!r}")
+        if depth < 1:
+            raise ValueError("depth must be >= 1")
+        mp, dp, want_maps = self._method_structs(method, params)
+        if want_maps:
+            raise ValueError("enhance_stream does not return curve maps")
+        def gen():
+            dev = torch.device("cuda", self.device)
+            h2d, comp, d2h = (torch.cuda.Stream(dev) for _ in range(3))
+            slots, shape0 = [], None   # per slot: pinned in / out, device in / out, events, "is numpy"
+            inflight = []              # slot indices in submission order
+
+            def take(si):
+                sl = slots[si]
+                sl["ev_out"].synchronize()
+                y = sl["yp"].clone() if copy else sl["yp"]   # the pinned stage is reused `depth` frames later
+                return y.numpy() if sl["is_np"] else y
+
+            i = 0
+            for f in frames:
+                is_np = isinstance(f, np.ndarray)
+                t = torch.from_numpy(f) if is_np else f
+                if not isinstance(t, torch.Tensor) or t.is_cuda:
+                    raise TypeError("enhance_stream takes host frames (numpy.ndarray or CPU torch.Tensor)")
+                if t.dtype not in (torch.float32, torch.uint8) or not t.is_contiguous():
+                    raise TypeError("frames must be contiguous float32 or uint8")
+                if shape0 is None:
+                    shape0 = (tuple(t.shape), t.dtype)
+                    n, h, w, layout, _ = _resolve_layout(t.shape, params.get("layout"))
+                elif (tuple(t.shape), t.dtype) != shape0:
+                    raise ValueError(f"all frames of a stream must share shape and dtype: {shape0} vs {(tuple(t.shape), t.dtype)}")
+                si = i % depth
+                if len(slots) <= si:
+                    slots.append(dict(xp=torch.empty(t.shape, dtype=t.dtype, pin_memory=True),
+                                      yp=torch.empty(t.shape, dtype=t.dtype, pin_memory=True),
+                                      xd=torch.empty(t.shape, dtype=t.dtype, device=dev),
+                                      yd=torch.empty(t.shape, dtype=t.dtype, device=dev),
+                                      ev_in=torch.cuda.Event(), ev_comp=torch.cuda.Event(), ev_out=torch.cuda.Event(),
+                                      is_np=is_np))
+                else:
+                    yield take(inflight.pop(0))            # frame i - depth: its slot is free once it has been handed out
+                sl = slots[si]
+                sl["is_np"] = is_np
+                src = t
+                if not t.is_pinned():
+                    sl["xp"].copy_(t)                      # host memcpy into the pinned stage (H2D of frame i-depth is done)
+                    src = sl["xp"]
+                sl["src"] = src                            # a pinned caller frame stays referenced until its slot is reused
+                with torch.cuda.stream(h2d):
+                    h2d.wait_event(sl["ev_comp"])          # the compute that last read xd has finished
+                    sl["xd"].copy_(src, non_blocking=True)
+                    sl["ev_in"].record(h2d)
+                comp.wait_event(sl["ev_in"])
+                comp.wait_event(sl["ev_out"])              # the D2H that last read yd has finished
+                if mp is not None:
+                    self.msrcr_device(sl["xd"], sl["yd"], n, h, w, layout, mp, _stream_ptr(comp))
+                else:
+                    self.dce_device(sl["xd"], sl["yd"], None, n, h, w, layout, dp, _stream_ptr(comp))
+                sl["ev_comp"].record(comp)
+                with torch.cuda.stream(d2h):
+                    d2h.wait_event(sl["ev_comp"])
+                    sl["yp"].copy_(sl["yd"], non_blocking=True)
+                    sl["ev_out"].record(d2h)
+                inflight.append(si)
+                i += 1
+            while inflight:
+                yield take(inflight.pop(0))
+
+        return gen()
 
     def _pinned(self, name: str, nelem: int, dtype=torch.float32) -> torch.Tensor:
         name = f"{name}.{dtype}"
@@ -529,8 +606,9 @@ def enhance(images, method: str, params: dict | None = None, *, out=None, device
              CUDA tensors are processed in place on their device and stream (zero copy); NumPy
              arrays and CPU tensors are staged through pinned memory.
     method : 'msrcr'  -- params: sigmas, weights, truncate, alpha, beta, gain, offset, in_scale,
-                         in_bias, blur ('pyramid' | 'direct'), finish ('none' | 'minmax' | 'meanstd': per-image,
-                         per-channel stretch of the un-clipped result by min/max or mean +- finish_k std)
+                         in_bias, blur ('pyramid' | 'direct'), finish ('none' | 'minmax' | 'meanstd' | 'percentile': per-image,
+                         per-channel stretch of the un-clipped result by min/max, mean +- finish_k std, or the
+                         order statistics that clip finish_k percent of the pixels at each end)
              'zero_dce' -- params: weights (79 416-float blob or [(W, b)] * 7), iters, curve_sign,
                          precision ('fp32' = hi/lo-split bf16 on the tensor cores, fp32-accurate |
                          'bf16' | 'fp32_simt' = plain fp32 FMA on the CUDA cores), return_maps
@@ -544,3 +622,23 @@ def enhance(images, method: str, params: dict | None = None, *, out=None, device
         _lib.check(_lib.load().llie_device_count(C.byref(n)))
         device = torch.cuda.current_device()
     return _enhancer(device).enhance(images, method, params, out=out)
+
+
+def enhance_stream(frames, method: str, params: dict | None = None, *, depth: int = 3, copy: bool = True,
+                   device: int | None = None):
+    """Streaming front-end: enhance an iterable of host frames, yielding the results in order.
+
+    frames : iterable of numpy arrays / CPU tensors that all share one shape and dtype -- (H,W,3) frames or small
+             (N,H,W,3) / (N,3,H,W) groups, float32 or uint8 -- e.g. a video decoder's output.
+    depth  : frames in flight.  Each has its own pinned and device buffers; frame i's upload, frame i-1's kernels
+             and frame i-2's download run on three streams, so from depth = 3 the link and the SMs work concurrently.
+    copy   : True yields an independent array per frame.  False yields the slot's pinned staging buffer itself (no
+             host copy); it is overwritten `depth` frames later, so consume it before advancing that far.
+    Frames that are pinned CPU tensors are uploaded straight from the caller's memory (leave them untouched until the
+    result has been yielded); anything else is first copied into the slot's pinned stage.
+    Yields one result per frame (same type, shape and dtype), delayed by `depth` frames; the tail is flushed when the
+    iterable ends.  Same parameters and error behaviour as enhance(); return_maps is not supported.
+    """
+    if device is None:
+        device = torch.cuda.current_device()
+    return _enhancer(device).stream(frames, method, params, depth=depth, copy=copy)

@@ -233,11 +233,13 @@ static int check_msrcr_params(const llie_msrcr_params* p) {
   LLIE_REQUIRE(p->truncate > 0.f && p->truncate <= 8.f, LLIE_E_ARG, "truncate %g out of range", p->truncate);
   LLIE_REQUIRE(p->in_bias > 0.f && p->in_scale >= 0.f, LLIE_E_ARG, "in_scale/in_bias must keep I = scale*x+bias positive");
   LLIE_REQUIRE(p->blur == LLIE_BLUR_PYRAMID || p->blur == LLIE_BLUR_DIRECT, LLIE_E_ARG, "unknown blur mode %d", p->blur);
-  LLIE_REQUIRE(p->finish >= LLIE_FINISH_NONE && p->finish <= LLIE_FINISH_MEANSTD, LLIE_E_ARG, "unknown finish mode %d", p->finish);
+  LLIE_REQUIRE(p->finish >= LLIE_FINISH_NONE && p->finish <= LLIE_FINISH_PERCENTILE, LLIE_E_ARG, "unknown finish mode %d", p->finish);
   LLIE_REQUIRE(p->finish == LLIE_FINISH_NONE || p->blur == LLIE_BLUR_PYRAMID, LLIE_E_ARG,
                "global-statistics finishers need the pyramid blur");
   LLIE_REQUIRE(p->finish != LLIE_FINISH_MEANSTD || (p->finish_k > 0.f && p->finish_k <= 16.f), LLIE_E_ARG,
                "finish_k %g out of range (0, 16]", p->finish_k);
+  LLIE_REQUIRE(p->finish != LLIE_FINISH_PERCENTILE || (p->finish_k >= 0.f && p->finish_k < 50.f), LLIE_E_ARG,
+               "finish_k %g out of range [0, 50) percent", p->finish_k);
   return LLIE_OK;
 }
 

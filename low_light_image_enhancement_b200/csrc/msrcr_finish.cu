@@ -99,6 +99,122 @@ msrcr_stretch_kernel(float* __restrict__ v, ImgView iv, int H, int W, const floa
   }
 }
 
+
+// ---- percentile stretch ("simplest colour balance"): exact order statistics by a 3-pass radix select ------------
+// Per image and channel, lo = the r-th smallest un-clipped value and hi = the r-th largest, r = floor(N k / 100).
+// Keys are the order-preserving 32-bit image of the float; passes take 11, 11 and 10 bits.  Each pass: per-block
+// shared-memory histograms of the digit (of the keys that match the prefix selected so far, one histogram per
+// target) -> global histogram -> one warp per (channel, target) walks it and extends the prefix.
+constexpr int kSelBins = 2048;
+struct SelState { unsigned prefix[3][2]; unsigned rank[3][2]; };  // per image: [channel][lo, hi]
+
+__device__ __forceinline__ unsigned sel_key(float f) {
+  const unsigned u = __float_as_uint(f);
+  return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+__device__ __forceinline__ float sel_value(unsigned k) {
+  return __uint_as_float((k & 0x80000000u) ? (k & 0x7fffffffu) : ~k);
+}
+
+template <int PASS>
+__global__ void __launch_bounds__(kStatThreads)
+msrcr_select_hist_kernel(const float* __restrict__ v, ImgView iv, int H, int W, const SelState* __restrict__ state,
+                         unsigned* __restrict__ hist) {
+  constexpr int kShift = PASS == 0 ? 21 : (PASS == 1 ? 10 : 0);
+  constexpr int kMatchShift = PASS == 1 ? 21 : 10;  // bits above it are already selected
+  constexpr unsigned kMask = PASS == 2 ? 1023u : 2047u;
+  constexpr int kT = PASS == 0 ? 1 : 2;              // pass 0: both targets share one histogram
+  __shared__ unsigned sh[3][kT][kSelBins];
+  for (int i = threadIdx.x; i < 3 * kT * kSelBins; i += kStatThreads) (&sh[0][0][0])[i] = 0u;
+  const long long img = blockIdx.y;
+  unsigned pre[3][2];
+#pragma unroll
+  for (int c = 0; c < 3; ++c)
+#pragma unroll
+    for (int t = 0; t < 2; ++t) pre[c][t] = PASS == 0 ? 0u : (state[img].prefix[c][t] >> kMatchShift);
+  __syncthreads();
+  const long long npx = (long long)H * W;
+  const long long per = (npx + kStatBlocks - 1) / kStatBlocks;
+  const long long p0 = blockIdx.x * per, p1 = min(p0 + per, npx);
+  for (long long p = p0 + threadIdx.x; p < p1; p += kStatThreads) {
+    const int y = (int)(p / W), x = (int)(p - (long long)y * W);
+    const float* src = v + img * iv.sn + (long long)y * iv.sy + (long long)x * iv.sx;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      const unsigned k = sel_key(__ldg(src + c * iv.sc));
+      const unsigned d = (k >> kShift) & kMask;
+      if (PASS == 0) {
+        atomicAdd(&sh[c][0][d], 1u);
+      } else {
+        const unsigned top = k >> kMatchShift;
+        if (top == pre[c][0]) atomicAdd(&sh[c][0][d], 1u);
+        if (top == pre[c][1]) atomicAdd(&sh[c][kT - 1][d], 1u);
+      }
+    }
+  }
+  __syncthreads();
+  unsigned* g = hist + img * (3 * 2 * kSelBins);
+  for (int i = threadIdx.x; i < 3 * kT * kSelBins; i += kStatThreads) {
+    const unsigned cnt = (&sh[0][0][0])[i];
+    if (cnt) {
+      const int c = i / (kT * kSelBins), t = (i / kSelBins) % kT, b = i % kSelBins;
+      atomicAdd(g + (c * 2 + t) * kSelBins + b, cnt);
+    }
+  }
+}
+
+// one warp per (channel, target): find the bin holding the wanted rank, extend the prefix, keep the rank inside it
+template <int PASS>
+__global__ void msrcr_select_scan_kernel(const unsigned* __restrict__ hist, SelState* __restrict__ state,
+                                         float2* __restrict__ lo_inv, long long npx, float k) {
+  constexpr int kShift = PASS == 0 ? 21 : (PASS == 1 ? 10 : 0);
+  const int img = blockIdx.x, lane = threadIdx.x & 31, wrp = threadIdx.x >> 5;  // 6 warps
+  const int c = wrp >> 1, t = wrp & 1;
+  __shared__ float sh_val[3][2];
+  unsigned rank, prefix;
+  if (PASS == 0) {
+    long long r = (long long)floor((double)npx * (double)k / 100.0);
+    r = min(max(r, 0LL), (npx - 1) / 2);
+    rank = (unsigned)(t == 0 ? r : npx - 1 - r);
+    prefix = 0u;
+  } else {
+    rank = state[img].rank[c][t]; prefix = state[img].prefix[c][t];
+  }
+  const unsigned* h = hist + (long long)img * (3 * 2 * kSelBins) + (c * 2 + (PASS == 0 ? 0 : t)) * kSelBins;
+  constexpr int kPer = kSelBins / 32;
+  unsigned mine = 0;
+  for (int i = 0; i < kPer; ++i) mine += h[lane * kPer + i];
+  unsigned incl = mine;
+  for (int o = 1; o < 32; o <<= 1) { const unsigned n = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += n; }
+  const unsigned excl = incl - mine;
+  const bool has = rank >= excl && rank < incl;   // exactly one lane (the counts sum to more than rank)
+  if (has) {
+    unsigned acc = excl; int b = lane * kPer;
+    for (;; ++b) { const unsigned n = h[b]; if (rank < acc + n) break; acc += n; }
+    prefix |= (unsigned)b << kShift; rank -= acc;
+    state[img].prefix[c][t] = prefix; state[img].rank[c][t] = rank;
+    if (PASS == 2) sh_val[c][t] = sel_value(prefix);
+  }
+  if (PASS == 2) {
+    __syncthreads();
+    if (threadIdx.x < 3) {
+      const double l = sh_val[threadIdx.x][0], hh = sh_val[threadIdx.x][1];
+      lo_inv[img * 3 + threadIdx.x] = make_float2((float)l, hh > l ? (float)(1.0 / (hh - l)) : 0.f);
+    }
+  }
+}
+
+template <int PASS>
+int select_pass(llie_ctx* ctx, cudaStream_t st, const float* out, const ImgView& v, int n, int h, int w, SelState* d_state,
+                unsigned* d_hist, float2* d_li, float k) {
+  LLIE_CUDA_OK(cudaMemsetAsync(d_hist, 0, (size_t)n * 3 * 2 * kSelBins * sizeof(unsigned), st));
+  LLIE_LAUNCH(ctx, st, "msrcr_select_hist_kernel",
+              (msrcr_select_hist_kernel<PASS><<<dim3(kStatBlocks, n), kStatThreads, 0, st>>>(out, v, h, w, d_state, d_hist)));
+  LLIE_LAUNCH(ctx, st, "msrcr_select_scan_kernel",
+              (msrcr_select_scan_kernel<PASS><<<n, 192, 0, st>>>(d_hist, d_state, d_li, (long long)h * w, k)));
+  return LLIE_OK;
+}
+
 }  // namespace
 
 int msrcr_finish_run(llie_ctx* ctx, float* out, int n, int h, int w, int layout, const llie_msrcr_params& p, cudaStream_t st) {
@@ -106,10 +222,19 @@ int msrcr_finish_run(llie_ctx* ctx, float* out, int n, int h, int w, int layout,
   LLIE_TRY(ctx->workspace("msrcr.finish.partials", (size_t)n * kStatBlocks * sizeof(Partial), &d_part));
   LLIE_TRY(ctx->workspace("msrcr.finish.lo_inv", (size_t)n * 3 * sizeof(float2), &d_li));
   const ImgView v = make_view(layout, 3, h, w);
+  if (p.finish == LLIE_FINISH_PERCENTILE) {
+    void *d_state, *d_hist;
+    LLIE_TRY(ctx->workspace("msrcr.finish.select_state", (size_t)n * sizeof(SelState), &d_state));
+    LLIE_TRY(ctx->workspace("msrcr.finish.select_hist", (size_t)n * 3 * 2 * kSelBins * sizeof(unsigned), &d_hist));
+    LLIE_TRY(select_pass<0>(ctx, st, out, v, n, h, w, (SelState*)d_state, (unsigned*)d_hist, (float2*)d_li, p.finish_k));
+    LLIE_TRY(select_pass<1>(ctx, st, out, v, n, h, w, (SelState*)d_state, (unsigned*)d_hist, (float2*)d_li, p.finish_k));
+    LLIE_TRY(select_pass<2>(ctx, st, out, v, n, h, w, (SelState*)d_state, (unsigned*)d_hist, (float2*)d_li, p.finish_k));
+  } else {
   LLIE_LAUNCH(ctx, st, "msrcr_stats_kernel",
               (msrcr_stats_kernel<<<dim3(kStatBlocks, n), kStatThreads, 0, st>>>(out, v, h, w, (Partial*)d_part)));
   LLIE_LAUNCH(ctx, st, "msrcr_stats_fold_kernel",
               (msrcr_stats_fold_kernel<<<n, 32, 0, st>>>((const Partial*)d_part, (float2*)d_li, (double)h * w, p.finish, p.finish_k)));
+  }
   const long long npx = (long long)h * w;
   LLIE_LAUNCH(ctx, st, "msrcr_stretch_kernel",
               (msrcr_stretch_kernel<<<dim3((unsigned)((npx + 255) / 256), n), 256, 0, st>>>(out, v, h, w, (const float2*)d_li)));

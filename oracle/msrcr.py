@@ -13,6 +13,8 @@ infrastructure only; float64 arithmetic on float32 inputs.
     finish: instead of the plain clip, per channel over the whole image,
             "minmax":  (v - min v) / (max v - min v)          with v = (G C R + b) / 255
             "meanstd": clip((v - (m - k s)) / (2 k s), 0, 1)  with m, s = mean, population std of v
+            "percentile": clip((v - lo) / (hi - lo), 0, 1)    with lo / hi = the r-th smallest / largest v,
+                          r = floor(N k / 100) of the N pixels ("simplest colour balance", Limare et al. 2011)
 """
 from __future__ import annotations
 
@@ -30,7 +32,7 @@ MSRCR_DEFAULTS = dict(
     offset=128.0,
     in_scale=255.0,
     in_bias=1.0,
-    finish="none",   # "none" | "minmax" | "meanstd" (per image, per channel)
+    finish="none",   # "none" | "minmax" | "meanstd" | "percentile" (per image, per channel)
     finish_k=2.0,
 )
 
@@ -119,6 +121,13 @@ def msrcr(x: np.ndarray, params: dict | None = None, mode: str = "fft") -> np.nd
         elif p["finish"] == "meanstd":
             m, sd = out.mean(axis=(0, 1)), out.std(axis=(0, 1))   # population standard deviation
             lo, hi = m - p["finish_k"] * sd, m + p["finish_k"] * sd
+        elif p["finish"] == "percentile":
+            # "simplest colour balance": clip finish_k percent of the pixels at each end (exact order statistics)
+            flat = np.sort(out.reshape(-1, 3), axis=0)
+            n = flat.shape[0]
+            r = int(np.floor(n * float(np.float32(p["finish_k"])) / 100.0))
+            r = min(max(r, 0), (n - 1) // 2)
+            lo, hi = flat[r], flat[n - 1 - r]
         else:
             raise ValueError(p["finish"])
         out = np.where(hi > lo, (out - lo) / np.where(hi > lo, hi - lo, 1.0), 0.0)

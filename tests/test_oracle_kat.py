@@ -151,3 +151,11 @@ def test_msrcr_finishers_kat():
     b = oracle.msrcr(x, dict(finish="meanstd", finish_k=3.0, gain=0.3, offset=60.0))
     assert np.abs(a - b).max() <= 1e-6
     assert np.abs(a.mean(axis=(0, 1)) - 0.5).max() <= 0.05     # clipping of the tails moves the mean only slightly
+    # percentile stretch: k = 0 is the min/max stretch; k percent of the pixels saturate at each end
+    assert np.array_equal(oracle.msrcr(x, dict(finish="percentile", finish_k=0.0)), y)
+    q = oracle.msrcr(x, dict(finish="percentile", finish_k=5.0))
+    n, r = 64 * 80, int(64 * 80 * 5.0 / 100.0)
+    for c in range(3):
+        assert (q[..., c] == 0.0).sum() >= r + 1 and (q[..., c] == 1.0).sum() >= r + 1
+        assert (q[..., c] == 0.0).sum() <= r + 8 and (q[..., c] == 1.0).sum() <= r + 8    # ties only
+    assert np.abs(q - oracle.msrcr(x, dict(finish="percentile", finish_k=5.0, gain=0.3, offset=60.0))).max() <= 1e-6
