@@ -125,6 +125,11 @@ int llie_msrcr_f32(llie_ctx* ctx, const float* in, float* out, int n, int h, int
 int llie_msrcr_u8(llie_ctx* ctx, const uint8_t* in, uint8_t* out, int n, int h, int w, int layout,
                   const llie_msrcr_params* params, void* stream);
 
+/* 16-bit images (the other half of 8(f) rank 1): as llie_msrcr_u8 with a sample b meaning b/65535 and the result
+ * stored as rint(65535 * value); 2 bytes per sample on HBM and on PCIe. */
+int llie_msrcr_u16(llie_ctx* ctx, const uint16_t* in, uint16_t* out, int n, int h, int w, int layout,
+                   const llie_msrcr_params* params, void* stream);
+
 /* Host-side planner of the pyramid blur, exposed so that CPU tests can check it without a
  * GPU: for `sigma`/`truncate` returns the cascade level's stride (4 or 16), the low-res
  * Gaussian's sigma and radius, and the L1 distance between the cascade's effective kernel
@@ -146,6 +151,10 @@ int llie_dce_forward(llie_ctx* ctx, const float* in, float* out, float* maps_or_
  * maps, if requested, stay fp32). */
 int llie_dce_forward_u8(llie_ctx* ctx, const uint8_t* in, uint8_t* out, float* maps_or_null, int n, int h, int w,
                         int layout, const llie_dce_params* params, void* stream);
+
+/* 16-bit variant (same conventions as llie_msrcr_u16; LLIE_BF16 precision only). */
+int llie_dce_forward_u16(llie_ctx* ctx, const uint16_t* in, uint16_t* out, float* maps_or_null, int n, int h, int w,
+                         int layout, const llie_dce_params* params, void* stream);
 
 /* Test hook: after a LLIE_BF16 or LLIE_F32 forward, copies inter-layer activation `which` (1..6 = x1..x6 of
  * SURVEY.md 9.2) of frame `frame` of the last processed chunk to HOST memory as fp32 [32][h][w]. */

@@ -64,6 +64,8 @@ EXPORTS = {
     "llie_msrcr_f32": (_I, [_VP, _VP, _VP, _I, _I, _I, _I, C.POINTER(MsrcrParams), _VP]),
     "llie_msrcr_u8": (_I, [_VP, _VP, _VP, _I, _I, _I, _I, C.POINTER(MsrcrParams), _VP]),
     "llie_dce_forward_u8": (_I, [_VP, _VP, _VP, _VP, _I, _I, _I, _I, C.POINTER(DceParams), _VP]),
+    "llie_msrcr_u16": (_I, [_VP, _VP, _VP, _I, _I, _I, _I, C.POINTER(MsrcrParams), _VP]),
+    "llie_dce_forward_u16": (_I, [_VP, _VP, _VP, _VP, _I, _I, _I, _I, C.POINTER(DceParams), _VP]),
     "llie_msrcr_plan_query": (_I, [_F, _F, C.POINTER(_I), C.POINTER(C.c_double), C.POINTER(_I),
                                    C.POINTER(C.c_double)]),
     "llie_dce_set_weights": (_I, [_VP, C.POINTER(_F), C.c_size_t]),

@@ -247,11 +247,11 @@ class Enhancer:
 
     # -- device-pointer entry points (zero-copy for torch CUDA tensors) -----------------------
     def msrcr_device(self, x: torch.Tensor, out: torch.Tensor, n, h, w, layout, p: MsrcrParams, stream_ptr):
-        fn = self._lib.llie_msrcr_u8 if x.dtype == torch.uint8 else self._lib.llie_msrcr_f32
+        fn = {torch.uint8: self._lib.llie_msrcr_u8, torch.uint16: self._lib.llie_msrcr_u16}.get(x.dtype, self._lib.llie_msrcr_f32)
         _lib.check(fn(self._h, x.data_ptr(), out.data_ptr(), n, h, w, layout, C.byref(p), stream_ptr))
 
     def dce_device(self, x, out, maps, n, h, w, layout, p: DceParams, stream_ptr):
-        fn = self._lib.llie_dce_forward_u8 if x.dtype == torch.uint8 else self._lib.llie_dce_forward
+        fn = {torch.uint8: self._lib.llie_dce_forward_u8, torch.uint16: self._lib.llie_dce_forward_u16}.get(x.dtype, self._lib.llie_dce_forward)
         _lib.check(fn(self._h, x.data_ptr(), out.data_ptr(), maps.data_ptr() if maps is not None else None,
                       n, h, w, layout, C.byref(p), stream_ptr))
 
@@ -268,8 +268,8 @@ class Enhancer:
         if not is_np and not isinstance(images, torch.Tensor):
             raise TypeError("images must be a numpy.ndarray or a torch.Tensor")
         t = torch.from_numpy(images) if is_np else images
-        if t.dtype not in (torch.float32, torch.uint8):
-            raise TypeError(f"images must be float32 (values in [0,1]) or uint8 (byte / 255), got {t.dtype}")
+        if t.dtype not in (torch.float32, torch.uint8, torch.uint16):
+            raise TypeError(f"images must be float32 (values in [0,1]), uint8 (b / 255) or uint16 (b / 65535), got {t.dtype}")
         if not t.is_contiguous():
             raise ValueError("images must be contiguous")
         n, h, w, layout, batched = _resolve_layout(t.shape, params.get("layout"))
@@ -337,8 +337,8 @@ class Enhancer:
                 t = torch.from_numpy(f) if is_np else f
                 if not isinstance(t, torch.Tensor) or t.is_cuda:
                     raise TypeError("enhance_stream takes host frames (numpy.ndarray or CPU torch.Tensor)")
-                if t.dtype not in (torch.float32, torch.uint8) or not t.is_contiguous():
-                    raise TypeError("frames must be contiguous float32 or uint8")
+                if t.dtype not in (torch.float32, torch.uint8, torch.uint16) or not t.is_contiguous():
+                    raise TypeError("frames must be contiguous float32, uint8 or uint16")
                 if shape0 is None:
                     shape0 = (tuple(t.shape), t.dtype)
                     n, h, w, layout, _ = _resolve_layout(t.shape, params.get("layout"))
@@ -600,8 +600,9 @@ def msrcr_tiled_last_ms(shards: Sequence[torch.Tensor]) -> list[float]:
 def enhance(images, method: str, params: dict | None = None, *, out=None, device: int | None = None):
     """Enhance a low-light image batch on a B200.
 
-    images : numpy.ndarray or torch.Tensor, float32 in [0, 1] or uint8 (a byte b means b / 255; the result is
-             rint(255 * value) as uint8, converted inside the first / last kernel), shape (H,W,3), (N,H,W,3) or
+    images : numpy.ndarray or torch.Tensor, float32 in [0, 1], uint8 or uint16 (an integer b means b / 255 or
+             b / 65535; the result is rint(255 * value) or rint(65535 * value) in the same type, converted inside the
+             first / last kernel), shape (H,W,3), (N,H,W,3) or
              (N,3,H,W) (params['layout'] = 'NHWC' | 'NCHW' when the shape is ambiguous).
              CUDA tensors are processed in place on their device and stream (zero copy); NumPy
              arrays and CPU tensors are staged through pinned memory.

@@ -143,7 +143,7 @@ struct ChainArgs {
   ImgView vx, vm;
   int iters;
   float sign;
-  int u8;  // x / y are uint8_t images (value = byte / 255; stored as rint(255 * value))
+  int u8;  // x / y are integer images: 1 = uint8_t (value = byte / 255; stored as rint(255 * value)), 2 = uint16_t (65535)
   int N, H, W, Wp, strips, segs, seg_rows, units;
 };
 
@@ -538,9 +538,12 @@ __device__ __forceinline__ void epilogue_loop(const ChainArgs& a, const Smem<GID
         if (owned) {
           const long long bx = un.n * a.vx.sn + (long long)y * a.vx.sy + (long long)x * a.vx.sx;
           float p[3];
-          if (a.u8) {
+          if (a.u8 == 1) {
 #pragma unroll
             for (int c = 0; c < 3; ++c) p[c] = (float)__ldg(reinterpret_cast<const uint8_t*>(a.x) + bx + c * a.vx.sc) * (1.f / 255.f);
+          } else if (a.u8 == 2) {
+#pragma unroll
+            for (int c = 0; c < 3; ++c) p[c] = (float)__ldg(reinterpret_cast<const uint16_t*>(a.x) + bx + c * a.vx.sc) * (1.f / 65535.f);
           } else {
 #pragma unroll
             for (int c = 0; c < 3; ++c) p[c] = __ldg(a.x + bx + c * a.vx.sc);
@@ -554,10 +557,14 @@ __device__ __forceinline__ void epilogue_loop(const ChainArgs& a, const Smem<GID
 #pragma unroll
               for (int c = 0; c < 3; ++c) p[c] = fmaf(a.sign * A[3 * it + c] * p[c], 1.f - p[c], p[c]);
             }
-          if (a.u8) {
+          if (a.u8 == 1) {
 #pragma unroll
             for (int c = 0; c < 3; ++c)
               reinterpret_cast<uint8_t*>(a.y)[bx + c * a.vx.sc] = (uint8_t)__float2uint_rn(255.f * __saturatef(p[c]));
+          } else if (a.u8 == 2) {
+#pragma unroll
+            for (int c = 0; c < 3; ++c)
+              reinterpret_cast<uint16_t*>(a.y)[bx + c * a.vx.sc] = (uint16_t)__float2uint_rn(65535.f * __saturatef(p[c]));
           } else {
 #pragma unroll
             for (int c = 0; c < 3; ++c) a.y[bx + c * a.vx.sc] = p[c];

@@ -36,7 +36,7 @@ dce_pack_input_kernel(const TIn* __restrict__ x, ImgView v, __nv_bfloat16* __res
   const long long n = blockIdx.z;
   if (xx >= W) return;
   const TIn* p = x + n * v.sn + (long long)yy * v.sy + (long long)xx * v.sx;
-  constexpr float kIn = sizeof(TIn) == 1 ? 1.f / 255.f : 1.f;  // a byte b means b / 255
+  constexpr float kIn = sizeof(TIn) == 1 ? 1.f / 255.f : (sizeof(TIn) == 2 ? 1.f / 65535.f : 1.f);  // an integer b means b / 255 (65535)
   const float r = kIn * (float)__ldg(p), g = kIn * (float)__ldg(p + v.sc), b = kIn * (float)__ldg(p + 2 * v.sc);
   const __nv_bfloat162 rg = __floats2bfloat162_rn(r, g);
   uint4 o;
@@ -206,8 +206,8 @@ void dce_tc_release(llie_ctx* ctx) {
 // split = false: bf16 operands (config 2).  split = true: hi/lo bf16 pairs, three MMAs per product -- fp32-accurate
 // results (config 1) from the same tensor-core kernel, one launch per layer.
 static int dce_forward_tc(llie_ctx* ctx, const void* in_v, void* out_v, float* maps, int n, int h, int w, int layout,
-                          const llie_dce_params& p, cudaStream_t st, bool split, bool u8 = false) {
-  const size_t esz = u8 ? 1 : 4;  // bytes per image sample
+                          const llie_dce_params& p, cudaStream_t st, bool split, int iot = kIoF32) {
+  const size_t esz = io_bytes(iot);  // bytes per image sample
   DceWeights* dw = ctx->dce;
   LLIE_REQUIRE(dw != nullptr && dw->d_bf16 != nullptr, LLIE_E_STATE, "dce_forward: call llie_dce_set_weights first");
   DceTcPack& pk = g_packs[ctx];
@@ -241,9 +241,12 @@ static int dce_forward_tc(llie_ctx* ctx, const void* in_v, void* out_v, float* m
       if (split)
         LLIE_LAUNCH(ctx, st, "dce_pack_input_split_kernel",
                     (dce_pack_input_kernel<true, float><<<grid, 256, 0, st>>>(x, vx, pk.xin, h, w, wp)));
-      else if (u8)
+      else if (iot == kIoU8)
         LLIE_LAUNCH(ctx, st, "dce_pack_input_kernel",
                     (dce_pack_input_kernel<false, uint8_t><<<grid, 256, 0, st>>>(reinterpret_cast<const uint8_t*>(x), vx, pk.xin, h, w, wp)));
+      else if (iot == kIoU16)
+        LLIE_LAUNCH(ctx, st, "dce_pack_input_kernel",
+                    (dce_pack_input_kernel<false, uint16_t><<<grid, 256, 0, st>>>(reinterpret_cast<const uint16_t*>(x), vx, pk.xin, h, w, wp)));
       else
         LLIE_LAUNCH(ctx, st, "dce_pack_input_kernel",
                     (dce_pack_input_kernel<false, float><<<grid, 256, 0, st>>>(x, vx, pk.xin, h, w, wp)));
@@ -252,7 +255,7 @@ static int dce_forward_tc(llie_ctx* ctx, const void* in_v, void* out_v, float* m
     memset(&a, 0, sizeof(a));
     a.N = nb; a.H = h; a.W = w; a.Wp = wp;
     a.x = x; a.y = reinterpret_cast<float*>(static_cast<char*>(out_v) + (size_t)n0 * h * w * 3 * esz);
-    a.u8 = u8 ? 1 : 0;
+    a.u8 = iot;  // kIoF32 / kIoU8 / kIoU16 = 0 / 1 / 2
     a.maps = maps ? maps + n0 * (long long)h * w * 24 : nullptr;
     a.vx = vx; a.vm = vm; a.iters = p.iters; a.sign = p.curve_sign >= 0 ? 1.f : -1.f;
     // stage slot <- layer l (0..6): weights, bias, HBM destination (nullptr = keep on chip)
@@ -312,9 +315,9 @@ int dce_forward_bf16(llie_ctx* ctx, const float* in, float* out, float* maps, in
                      const llie_dce_params& p, cudaStream_t st) {
   return dce_forward_tc(ctx, in, out, maps, n, h, w, layout, p, st, false);
 }
-int dce_forward_u8(llie_ctx* ctx, const uint8_t* in, uint8_t* out, float* maps, int n, int h, int w, int layout,
-                   const llie_dce_params& p, cudaStream_t st) {
-  return dce_forward_tc(ctx, in, out, maps, n, h, w, layout, p, st, false, true);
+int dce_forward_int(llie_ctx* ctx, const void* in, void* out, int iot, float* maps, int n, int h, int w, int layout,
+                    const llie_dce_params& p, cudaStream_t st) {
+  return dce_forward_tc(ctx, in, out, maps, n, h, w, layout, p, st, false, iot);
 }
 int dce_forward_split(llie_ctx* ctx, const float* in, float* out, float* maps, int n, int h, int w, int layout,
                       const llie_dce_params& p, cudaStream_t st) {

@@ -259,19 +259,29 @@ int llie_msrcr_f32(llie_ctx* ctx, const float* in, float* out, int n, int h, int
   return LLIE_OK;
 }
 
-int llie_msrcr_u8(llie_ctx* ctx, const uint8_t* in, uint8_t* out, int n, int h, int w, int layout,
-                  const llie_msrcr_params* params, void* stream) {
+static int msrcr_int(llie_ctx* ctx, const void* in, void* out, int iot, int n, int h, int w, int layout,
+                     const llie_msrcr_params* params, void* stream) {
   LLIE_REQUIRE(ctx, LLIE_E_ARG, "null ctx");
   LLIE_TRY(check_batch(in, out, n, h, w, layout));
   LLIE_TRY(check_msrcr_params(params));
-  LLIE_REQUIRE(params->blur == LLIE_BLUR_PYRAMID, LLIE_E_DTYPE, "uint8 images are supported by the pyramid blur only");
+  LLIE_REQUIRE(params->blur == LLIE_BLUR_PYRAMID, LLIE_E_DTYPE, "integer images are supported by the pyramid blur only");
   LLIE_REQUIRE(params->finish == LLIE_FINISH_NONE, LLIE_E_DTYPE, "global-statistics finishers need fp32 images");
   if (n == 0) return LLIE_OK;
   DeviceGuard g(ctx->device);
   cudaStream_t st = stream ? (cudaStream_t)stream : ctx->stream;
-  LLIE_TRY(msrcr_pyramid_run_io(ctx, in, out, true, n, h, w, layout, *params, st));
+  LLIE_TRY(msrcr_pyramid_run_io(ctx, in, out, iot, n, h, w, layout, *params, st));
   if (!stream) LLIE_CUDA_OK(cudaStreamSynchronize(st));
   return LLIE_OK;
+}
+
+int llie_msrcr_u8(llie_ctx* ctx, const uint8_t* in, uint8_t* out, int n, int h, int w, int layout,
+                  const llie_msrcr_params* params, void* stream) {
+  return msrcr_int(ctx, in, out, kIoU8, n, h, w, layout, params, stream);
+}
+
+int llie_msrcr_u16(llie_ctx* ctx, const uint16_t* in, uint16_t* out, int n, int h, int w, int layout,
+                   const llie_msrcr_params* params, void* stream) {
+  return msrcr_int(ctx, in, out, kIoU16, n, h, w, layout, params, stream);
 }
 
 int llie_msrcr_plan_query(float sigma, float truncate, int* stride, double* sigma_low, int* radius_low,
@@ -313,18 +323,28 @@ int llie_dce_forward(llie_ctx* ctx, const float* in, float* out, float* maps_or_
   return LLIE_OK;
 }
 
-int llie_dce_forward_u8(llie_ctx* ctx, const uint8_t* in, uint8_t* out, float* maps_or_null, int n, int h, int w,
-                        int layout, const llie_dce_params* params, void* stream) {
+static int dce_int(llie_ctx* ctx, const void* in, void* out, int iot, float* maps_or_null, int n, int h, int w,
+                   int layout, const llie_dce_params* params, void* stream) {
   LLIE_REQUIRE(ctx, LLIE_E_ARG, "null ctx");
   LLIE_TRY(check_batch(in, out, n, h, w, layout));
   LLIE_TRY(check_dce_params(params));
-  LLIE_REQUIRE(params->precision == LLIE_BF16, LLIE_E_DTYPE, "uint8 images are supported by the LLIE_BF16 path only");
+  LLIE_REQUIRE(params->precision == LLIE_BF16, LLIE_E_DTYPE, "integer images are supported by the LLIE_BF16 path only");
   if (n == 0) return LLIE_OK;
   DeviceGuard g(ctx->device);
   cudaStream_t st = stream ? (cudaStream_t)stream : ctx->stream;
-  LLIE_TRY(dce_forward_u8(ctx, in, out, maps_or_null, n, h, w, layout, *params, st));
+  LLIE_TRY(dce_forward_int(ctx, in, out, iot, maps_or_null, n, h, w, layout, *params, st));
   if (!stream) LLIE_CUDA_OK(cudaStreamSynchronize(st));
   return LLIE_OK;
+}
+
+int llie_dce_forward_u8(llie_ctx* ctx, const uint8_t* in, uint8_t* out, float* maps_or_null, int n, int h, int w,
+                        int layout, const llie_dce_params* params, void* stream) {
+  return dce_int(ctx, in, out, kIoU8, maps_or_null, n, h, w, layout, params, stream);
+}
+
+int llie_dce_forward_u16(llie_ctx* ctx, const uint16_t* in, uint16_t* out, float* maps_or_null, int n, int h, int w,
+                         int layout, const llie_dce_params* params, void* stream) {
+  return dce_int(ctx, in, out, kIoU16, maps_or_null, n, h, w, layout, params, stream);
 }
 
 int llie_debug_dce_activation(llie_ctx* ctx, int which, int frame, float* host_out) {

@@ -118,15 +118,20 @@ inline int check_launch(llie_ctx* ctx, const char* what, cudaStream_t st = nullp
     LLIE_TRY(::llie::check_launch(ctx, name, st));       \
   } while (0)
 
+// image sample types of the typed entry points: float in [0, 1], or an integer b meaning b / io_levels
+constexpr int kIoF32 = 0, kIoU8 = 1, kIoU16 = 2;
+inline float io_levels(int iot) { return iot == kIoU8 ? 255.f : (iot == kIoU16 ? 65535.f : 1.f); }
+inline size_t io_bytes(int iot) { return iot == kIoU8 ? 1 : (iot == kIoU16 ? 2 : 4); }
+
 // kernels' host entry points (one per .cu)
 int msrcr_direct_run(llie_ctx* ctx, const float* in, float* out, int n, int h, int w, int layout,
                      const llie_msrcr_params& p, cudaStream_t st);
 int msrcr_finish_run(llie_ctx* ctx, float* out, int n, int h, int w, int layout, const llie_msrcr_params& p,
                      cudaStream_t st);  // msrcr_finish.cu
-int msrcr_pyramid_run_io(llie_ctx* ctx, const void* in, void* out, bool u8, int n, int h, int w, int layout,
+int msrcr_pyramid_run_io(llie_ctx* ctx, const void* in, void* out, int iot, int n, int h, int w, int layout,
                          const llie_msrcr_params& p, cudaStream_t st);
-int dce_forward_u8(llie_ctx* ctx, const uint8_t* in, uint8_t* out, float* maps, int n, int h, int w, int layout,
-                   const llie_dce_params& p, cudaStream_t st);
+int dce_forward_int(llie_ctx* ctx, const void* in, void* out, int iot, float* maps, int n, int h, int w, int layout,
+                    const llie_dce_params& p, cudaStream_t st);  // 8- / 16-bit images, bf16 operands
 int msrcr_pyramid_run(llie_ctx* ctx, const float* in, float* out, int n, int h, int w, int layout,
                       const llie_msrcr_params& p, cudaStream_t st);
 int msrcr_plan_query(float sigma, float truncate, int* stride, double* sigma_low, int* radius_low, double* l1);

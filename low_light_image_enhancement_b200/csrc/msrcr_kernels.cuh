@@ -85,6 +85,9 @@ down4_rows_kernel(const TIn* __restrict__ x, long long plane_stride, int RW, int
       if constexpr (VEC == 4 && sizeof(TIn) == 1) {
         const uchar4 t = __ldg(reinterpret_cast<const uchar4*>(q));
         buf[p][0] = (float)t.x; buf[p][1] = (float)t.y; buf[p][2] = (float)t.z; buf[p][3] = (float)t.w;
+      } else if constexpr (VEC == 4 && sizeof(TIn) == 2) {
+        const ushort4 t = __ldg(reinterpret_cast<const ushort4*>(q));
+        buf[p][0] = (float)t.x; buf[p][1] = (float)t.y; buf[p][2] = (float)t.z; buf[p][3] = (float)t.w;
       } else if constexpr (VEC == 4) {
         const float4 t = __ldg(reinterpret_cast<const float4*>(q));
         buf[p][0] = t.x; buf[p][1] = t.y; buf[p][2] = t.z; buf[p][3] = t.w;
@@ -378,7 +381,7 @@ __device__ __forceinline__ void final_prefetch(const T* __restrict__ x, const Im
 }
 
 // 4 pixels x 3 channels of one row of the cell: f[px][c].  uint8_t images are read as raw 0..255 values
-// (FinalParams.in_scale carries the 1/255) and written as rint(255 * value).
+// (FinalParams.in_scale carries the 1/255) and written as rint(255 * value); uint16_t likewise with 65535.
 __device__ __forceinline__ void final_load(const float* __restrict__ x, const ImgView& v, int io, long long img,
                                            int yl, int X0, int W, float (&f)[4][3]) {
   if (io == kIoNhwcVec) {
@@ -411,6 +414,27 @@ __device__ __forceinline__ void final_load(const uint8_t* __restrict__ x, const 
 #pragma unroll
     for (int c = 0; c < 3; ++c) {
       const uchar4 a = __ldg(reinterpret_cast<const uchar4*>(x + img * v.sn + c * v.sc + (long long)yl * v.sy + X0));
+      f[0][c] = a.x; f[1][c] = a.y; f[2][c] = a.z; f[3][c] = a.w;
+    }
+  } else {
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int c = 0; c < 3; ++c)
+        f[i][c] = (X0 + i < W) ? (float)__ldg(x + img * v.sn + c * v.sc + (long long)yl * v.sy + (long long)(X0 + i) * v.sx) : 0.f;
+  }
+}
+__device__ __forceinline__ void final_load(const uint16_t* __restrict__ x, const ImgView& v, int io, long long img,
+                                           int yl, int X0, int W, float (&f)[4][3]) {
+  if (io == kIoNhwcVec) {
+    const ushort4* p = reinterpret_cast<const ushort4*>(x + img * v.sn + (long long)yl * v.sy + (long long)X0 * 3);
+    const ushort4 a = __ldg(p), b = __ldg(p + 1), c = __ldg(p + 2);
+    f[0][0] = a.x; f[0][1] = a.y; f[0][2] = a.z; f[1][0] = a.w; f[1][1] = b.x; f[1][2] = b.y;
+    f[2][0] = b.z; f[2][1] = b.w; f[2][2] = c.x; f[3][0] = c.y; f[3][1] = c.z; f[3][2] = c.w;
+  } else if (io == kIoNchwVec) {
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      const ushort4 a = __ldg(reinterpret_cast<const ushort4*>(x + img * v.sn + c * v.sc + (long long)yl * v.sy + X0));
       f[0][c] = a.x; f[1][c] = a.y; f[2][c] = a.z; f[3][c] = a.w;
     }
   } else {
@@ -460,6 +484,28 @@ __device__ __forceinline__ void final_store(uint8_t* __restrict__ o, const ImgVi
 #pragma unroll
       for (int c = 0; c < 3; ++c)
         if (X0 + i < W) o[img * v.sn + c * v.sc + (long long)yl * v.sy + (long long)(X0 + i) * v.sx] = to_u8(f[i][c]);
+  }
+}
+
+__device__ __forceinline__ unsigned short to_u16(float v01) { return (unsigned short)__float2uint_rn(65535.f * v01); }
+__device__ __forceinline__ void final_store(uint16_t* __restrict__ o, const ImgView& v, int io, long long img, int yl,
+                                            int X0, int W, const float (&f)[4][3]) {
+  if (io == kIoNhwcVec) {
+    ushort4* p = reinterpret_cast<ushort4*>(o + img * v.sn + (long long)yl * v.sy + (long long)X0 * 3);
+    p[0] = make_ushort4(to_u16(f[0][0]), to_u16(f[0][1]), to_u16(f[0][2]), to_u16(f[1][0]));
+    p[1] = make_ushort4(to_u16(f[1][1]), to_u16(f[1][2]), to_u16(f[2][0]), to_u16(f[2][1]));
+    p[2] = make_ushort4(to_u16(f[2][2]), to_u16(f[3][0]), to_u16(f[3][1]), to_u16(f[3][2]));
+  } else if (io == kIoNchwVec) {
+#pragma unroll
+    for (int c = 0; c < 3; ++c)
+      *reinterpret_cast<ushort4*>(o + img * v.sn + c * v.sc + (long long)yl * v.sy + X0) =
+          make_ushort4(to_u16(f[0][c]), to_u16(f[1][c]), to_u16(f[2][c]), to_u16(f[3][c]));
+  } else {
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int c = 0; c < 3; ++c)
+        if (X0 + i < W) o[img * v.sn + c * v.sc + (long long)yl * v.sy + (long long)(X0 + i) * v.sx] = to_u16(f[i][c]);
   }
 }
 

@@ -320,12 +320,15 @@ void launch_fir_y8(bool param, dim3 grid, size_t smem, cudaStream_t st, A... a) 
 }
 
 template <int N6, int N4>
-void launch_final(dim3 grid, cudaStream_t st, const void* x, void* out, bool u8, ImgView v, int io, int W, int in_row0,
+void launch_final(dim3 grid, cudaStream_t st, const void* x, void* out, int iot, ImgView v, int io, int W, int in_row0,
                   int row_begin, int row_end, int rps, const FinalParams& fp) {
   // equal weights over the scales of this launch and values bounded so that their product cannot overflow
-  bool eq = fp.in_scale * 255.f + fp.in_bias <= 1e9f && fp.in_bias >= 1e-9f;
+  bool eq = fp.in_scale * fmaxf(255.f, io_levels(iot)) + fp.in_bias <= 1e9f && fp.in_bias >= 1e-9f;
   for (int i = 1; i < N6 + N4; ++i) eq = eq && fp.w2[i] == fp.w2[0];
-  if (u8) {
+  if (iot == kIoU16) {
+    if (eq) msrcr_final_kernel<N6, N4, uint16_t, true><<<grid, 128, 0, st>>>((const uint16_t*)x, (uint16_t*)out, v, io, W, in_row0, row_begin, row_end, rps, fp);
+    else msrcr_final_kernel<N6, N4, uint16_t, false><<<grid, 128, 0, st>>>((const uint16_t*)x, (uint16_t*)out, v, io, W, in_row0, row_begin, row_end, rps, fp);
+  } else if (iot == kIoU8) {
     if (eq) msrcr_final_kernel<N6, N4, uint8_t, true><<<grid, 128, 0, st>>>((const uint8_t*)x, (uint8_t*)out, v, io, W, in_row0, row_begin, row_end, rps, fp);
     else msrcr_final_kernel<N6, N4, uint8_t, false><<<grid, 128, 0, st>>>((const uint8_t*)x, (uint8_t*)out, v, io, W, in_row0, row_begin, row_end, rps, fp);
   } else {
@@ -338,7 +341,7 @@ void launch_final(dim3 grid, cudaStream_t st, const void* x, void* out, bool u8,
 // K5 launches: rows [row_begin, row_end) of n images whose pointers start at image row in_row0.
 int final_passes(llie_ctx* ctx, cudaStream_t st, const MsrcrPlan* pl, const llie_msrcr_params& p, const void* in,
                  void* out, const ImgView& v, bool vec, bool nhwc, int n, int h_view, int w, int in_row0, int row_begin,
-                 int row_end, int hC, int wC, const float* dSC, size_t c_elems, float* dAcc, bool u8 = false) {
+                 int row_end, int hC, int wC, const float* dSC, size_t c_elems, float* dAcc, int iot = kIoF32) {
   (void)h_view;
   const int io = vec ? (nhwc ? kIoNhwcVec : kIoNchwVec) : kIoScalar;
   const int cx = ceil_div(w, 4 * kFinalCells);
@@ -355,8 +358,8 @@ int final_passes(llie_ctx* ctx, cudaStream_t st, const MsrcrPlan* pl, const llie
   fp.beta_ln2 = (float)(p.beta * ln2);
   fp.gain255 = p.gain / 255.f;
   fp.offset255 = p.offset / 255.f;
-  fp.in_scale = u8 ? p.in_scale / 255.f : p.in_scale; fp.in_bias = p.in_bias;  // uint8 images are read as 0..255
-  fp.no_clip = (!u8 && p.finish != LLIE_FINISH_NONE) ? 1 : 0;
+  fp.in_scale = p.in_scale / io_levels(iot); fp.in_bias = p.in_bias;  // integer images are read as raw 0..255 / 0..65535
+  fp.no_clip = (iot == kIoF32 && p.finish != LLIE_FINISH_NONE) ? 1 : 0;
   int n6 = 0;
   for (auto& sc : pl->scales) n6 += (sc.level == 0);
   if (p.n_scales == 3 && n6 == 1) {
@@ -365,7 +368,7 @@ int final_passes(llie_ctx* ctx, cudaStream_t st, const MsrcrPlan* pl, const llie
       fp.map[i] = dSC + (size_t)k * c_elems;
       fp.w2[i] = (float)(ln2 * p.weight[k]);
     }
-    LLIE_LAUNCH(ctx, st, "msrcr_final_kernel", (launch_final<1, 2>(grid, st, in, out, u8, v, io, w, in_row0, row_begin, row_end, rps, fp)));
+    LLIE_LAUNCH(ctx, st, "msrcr_final_kernel", (launch_final<1, 2>(grid, st, in, out, iot, v, io, w, in_row0, row_begin, row_end, rps, fp)));
   } else {
     for (int k0 = 0; k0 < p.n_scales; k0 += 3) {
       const int cnt = std::min(3, p.n_scales - k0);
@@ -375,9 +378,9 @@ int final_passes(llie_ctx* ctx, cudaStream_t st, const MsrcrPlan* pl, const llie
       }
       fp.acc_in = k0 > 0 ? (const float*)dAcc : nullptr;
       fp.acc_out = k0 + cnt < p.n_scales ? dAcc : nullptr;
-      if (cnt == 1) LLIE_LAUNCH(ctx, st, "msrcr_final_kernel", (launch_final<1, 0>(grid, st, in, out, u8, v, io, w, in_row0, row_begin, row_end, rps, fp)));
-      if (cnt == 2) LLIE_LAUNCH(ctx, st, "msrcr_final_kernel", (launch_final<2, 0>(grid, st, in, out, u8, v, io, w, in_row0, row_begin, row_end, rps, fp)));
-      if (cnt == 3) LLIE_LAUNCH(ctx, st, "msrcr_final_kernel", (launch_final<3, 0>(grid, st, in, out, u8, v, io, w, in_row0, row_begin, row_end, rps, fp)));
+      if (cnt == 1) LLIE_LAUNCH(ctx, st, "msrcr_final_kernel", (launch_final<1, 0>(grid, st, in, out, iot, v, io, w, in_row0, row_begin, row_end, rps, fp)));
+      if (cnt == 2) LLIE_LAUNCH(ctx, st, "msrcr_final_kernel", (launch_final<2, 0>(grid, st, in, out, iot, v, io, w, in_row0, row_begin, row_end, rps, fp)));
+      if (cnt == 3) LLIE_LAUNCH(ctx, st, "msrcr_final_kernel", (launch_final<3, 0>(grid, st, in, out, iot, v, io, w, in_row0, row_begin, row_end, rps, fp)));
     }
   }
   return LLIE_OK;
@@ -392,7 +395,7 @@ int msrcr_pyramid_run(llie_ctx* ctx, const float* in, float* out, int n, int h, 
 
 // u8: in / out are uint8_t images (value = byte / 255 on the way in, rint(255 * value) on the way out), converted
 // inside the first and last kernels -- no extra pass over the image.
-int msrcr_pyramid_run_io(llie_ctx* ctx, const void* in, void* out, bool u8, int n, int h, int w, int layout,
+int msrcr_pyramid_run_io(llie_ctx* ctx, const void* in, void* out, int iot, int n, int h, int w, int layout,
                          const llie_msrcr_params& p, cudaStream_t st) {
   LLIE_TRY(ensure_plan(ctx, p, st));
   MsrcrPlan* pl = ctx->plan;
@@ -418,9 +421,9 @@ int msrcr_pyramid_run_io(llie_ctx* ctx, const void* in, void* out, bool u8, int 
   if (p.n_scales > 3) LLIE_TRY(ctx->workspace("msrcr.acc", (size_t)n * h * w * 3 * 4, &dAcc));
 
   const ImgView v = make_view(layout, 3, h, w);
-  const bool vec = (w % 4 == 0) && ((reinterpret_cast<uintptr_t>(in) | reinterpret_cast<uintptr_t>(out)) % (u8 ? 4 : 16) == 0);
+  const bool vec = (w % 4 == 0) && ((reinterpret_cast<uintptr_t>(in) | reinterpret_cast<uintptr_t>(out)) % (iot == kIoU8 ? 4 : (iot == kIoU16 ? 8 : 16)) == 0);
   const int want = 8 * ctx->sm_count;
-  const float in_scale = u8 ? p.in_scale / 255.f : p.in_scale;
+  const float in_scale = p.in_scale / io_levels(iot);
 
   {  // K1: rows
     const long long plane_stride = nhwc ? (long long)h * RW : (long long)h * w;
@@ -428,7 +431,10 @@ int msrcr_pyramid_run_io(llie_ctx* ctx, const void* in, void* out, bool u8, int 
       const int cx = ceil_div(RW, 512);
       const int rps = pick_strip(hC, (long long)cx * planes_v, want, 16, 64, 1);
       dim3 grid(cx, ceil_div(hC, rps), planes_v);
-      if (u8)
+      if (iot == kIoU16)
+        LLIE_LAUNCH(ctx, st, "down4_rows_kernel",
+                    (down4_rows_kernel<4, uint16_t><<<grid, 128, 0, st>>>((const uint16_t*)in, plane_stride, RW, h, 0, h, (float*)dV, hC, 0, hC, rps)));
+      else if (iot == kIoU8)
         LLIE_LAUNCH(ctx, st, "down4_rows_kernel",
                     (down4_rows_kernel<4, uint8_t><<<grid, 128, 0, st>>>((const uint8_t*)in, plane_stride, RW, h, 0, h, (float*)dV, hC, 0, hC, rps)));
       else
@@ -438,7 +444,10 @@ int msrcr_pyramid_run_io(llie_ctx* ctx, const void* in, void* out, bool u8, int 
       const int cx = ceil_div(RW, 128);
       const int rps = pick_strip(hC, (long long)cx * planes_v, want, 16, 64, 1);
       dim3 grid(cx, ceil_div(hC, rps), planes_v);
-      if (u8)
+      if (iot == kIoU16)
+        LLIE_LAUNCH(ctx, st, "down4_rows_kernel",
+                    (down4_rows_kernel<1, uint16_t><<<grid, 128, 0, st>>>((const uint16_t*)in, plane_stride, RW, h, 0, h, (float*)dV, hC, 0, hC, rps)));
+      else if (iot == kIoU8)
         LLIE_LAUNCH(ctx, st, "down4_rows_kernel",
                     (down4_rows_kernel<1, uint8_t><<<grid, 128, 0, st>>>((const uint8_t*)in, plane_stride, RW, h, 0, h, (float*)dV, hC, 0, hC, rps)));
       else
@@ -482,7 +491,7 @@ int msrcr_pyramid_run_io(llie_ctx* ctx, const void* in, void* out, bool u8, int 
     }
   }
   LLIE_TRY(final_passes(ctx, st, pl, p, in, out, v, vec, nhwc, n, h, w, 0, 0, h, hC, wC, (const float*)dSC, c_elems,
-                        (float*)dAcc, u8));
+                        (float*)dAcc, iot));
   return LLIE_OK;
 }
 

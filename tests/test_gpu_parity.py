@@ -384,6 +384,45 @@ def test_dce_u8_matches_oracle(shape, blob):
     assert np.abs(np.rint(yf * 255.0) - y.astype(np.float32)).max() <= 1
 
 
+def _u16_image(h, w, seed, gain=6.0):
+    return np.clip(np.rint(oracle.synth_lowlight(h, w, seed) * gain * 65535.0), 0, 65535).astype(np.uint16)
+
+
+@pytest.mark.parametrize("shape", [(120, 200), (61, 133)])
+def test_msrcr_u16_matches_oracle(shape):
+    """16-bit images: the fp32 budget of 1e-4 is 6.6 levels of 65535, so the bound is in levels, not in ties."""
+    x = _u16_image(*shape, 17)
+    want, want_f = oracle.msrcr_u16(x)
+    y = L.enhance(x, "msrcr")
+    assert y.dtype == np.uint16 and y.shape == x.shape
+    assert np.abs(y.astype(np.float64) - want_f).max() <= 65535 * TOL_F32 + 0.5
+    xc = torch.from_numpy(np.ascontiguousarray(x.transpose(2, 0, 1))[None]).cuda()
+    yc = L.enhance(xc, "msrcr", dict(layout="NCHW"))
+    assert yc.dtype == torch.uint16
+    assert np.abs(yc[0].cpu().numpy().transpose(1, 2, 0).astype(np.int32) - y.astype(np.int32)).max() <= 2
+    yf = L.enhance(oracle.from_u16(x), "msrcr")
+    assert np.abs(yf.astype(np.float64) * 65535.0 - y).max() <= 2.0
+    # batches through the host pipeline equal single frames
+    xs = np.stack([_u16_image(96, 160, s) for s in range(3)])
+    yb = L.enhance(xs, "msrcr")
+    for i in range(3):
+        assert np.array_equal(yb[i], L.enhance(xs[i], "msrcr"))
+
+
+def test_dce_u16_matches_oracle(blob):
+    x = _u16_image(135, 240, 18, gain=3.0)
+    want, want_f = oracle.zero_dce_u16(x, oracle.init_weights(0))
+    y = L.enhance(x, "zero_dce", dict(weights=blob, precision="bf16"))
+    assert y.dtype == np.uint16 and y.shape == x.shape
+    assert psnr(y.astype(np.float64) / 65535.0, want_f / 65535.0) >= 50.0     # the bf16 bar of north_star
+    yf = L.enhance(oracle.from_u16(x), "zero_dce", dict(weights=blob, precision="bf16"))
+    assert np.abs(np.rint(yf.astype(np.float64) * 65535.0) - y).max() <= 1
+    with pytest.raises(L.LlieError):
+        L.enhance(x, "zero_dce", dict(weights=blob, precision="fp32"))
+    with pytest.raises(L.LlieError):
+        L.enhance(x, "msrcr", dict(blur="direct"))
+
+
 def test_u8_rejections_and_host_pipeline(blob):
     x = _u8_image(64, 96, 9)
     with pytest.raises(L.LlieError):

@@ -141,6 +141,16 @@ def test_u8_convention_round_trips():
     assert oracle.to_u8(np.array([0.5 / 255, 1.5 / 255, -1.0, 2.0, 0.4999 / 255])).tolist() == [0, 2, 0, 255, 0]
 
 
+def test_u16_convention_kat():
+    b = np.array([0, 1, 32767, 65535], np.uint16)
+    assert np.array_equal(oracle.to_u16(oracle.from_u16(b)), b)
+    assert oracle.to_u16(np.array([0.5 / 65535, 1.5 / 65535, -1.0, 2.0])).tolist() == [0, 2, 0, 65535]
+    x8 = np.clip(np.rint(oracle.synth_lowlight(48, 64, 3) * 6 * 255), 0, 255).astype(np.uint8)
+    y16, _ = oracle.msrcr_u16(x8.astype(np.uint16) * 257)       # 257 b / 65535 == b / 255: the same image
+    y8, y8f = oracle.msrcr_u8(x8)
+    assert np.abs(y16.astype(np.float64) / 257.0 - y8f).max() <= 0.01
+
+
 def test_msrcr_finishers_kat():
     """min/max stretch reaches exactly 0 and 1 in every channel; mean/std stretch centres the
     un-clipped value at 0.5 and is invariant to gain and offset (an affine map of v cancels in the stretch)."""
