@@ -128,6 +128,11 @@ int msrcr_direct_run(llie_ctx* ctx, const float* in, float* out, int n, int h, i
                      const llie_msrcr_params& p, cudaStream_t st);
 int msrcr_finish_run(llie_ctx* ctx, float* out, int n, int h, int w, int layout, const llie_msrcr_params& p,
                      cudaStream_t st);  // msrcr_finish.cu
+size_t msrcr_finish_partials_bytes();   // one band / image: 256 partials
+size_t msrcr_finish_partial_size();
+int msrcr_finish_stats(llie_ctx* ctx, cudaStream_t st, const float* out, int n, int h, int w, int layout, void* d_part);
+int msrcr_finish_apply(llie_ctx* ctx, cudaStream_t st, float* out, int n, int h, int w, int layout, const void* d_part,
+                       int nparts, double npx, const llie_msrcr_params& p, void* d_li);
 int msrcr_pyramid_run_io(llie_ctx* ctx, const void* in, void* out, int iot, int n, int h, int w, int layout,
                          const llie_msrcr_params& p, cudaStream_t st);
 int dce_forward_int(llie_ctx* ctx, const void* in, void* out, int iot, float* maps, int n, int h, int w, int layout,

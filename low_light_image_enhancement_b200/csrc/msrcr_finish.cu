@@ -69,12 +69,12 @@ msrcr_stats_kernel(const float* __restrict__ v, ImgView iv, int H, int W, Partia
 }
 
 // lo_inv[img][c] = (lo, 1 / (hi - lo)); a constant channel (hi == lo) maps to 0
-__global__ void msrcr_stats_fold_kernel(const Partial* __restrict__ part, float2* __restrict__ lo_inv, double npx, int mode, float k) {
+__global__ void msrcr_stats_fold_kernel(const Partial* __restrict__ part, int nparts, float2* __restrict__ lo_inv, double npx, int mode, float k) {
   const int img = blockIdx.x, c = threadIdx.x;
   if (c >= 3) return;
   double a = 0, b = 0; float lo = INFINITY, hi = -INFINITY;
-  for (int i = 0; i < kStatBlocks; ++i) {
-    const Partial& p = part[(long long)img * kStatBlocks + i];
+  for (int i = 0; i < nparts; ++i) {
+    const Partial& p = part[(long long)img * nparts + i];
     a += p.sum[c]; b += p.sumsq[c]; lo = fminf(lo, p.mn[c]); hi = fmaxf(hi, p.mx[c]);
   }
   double l = lo, h = hi;
@@ -217,6 +217,30 @@ int select_pass(llie_ctx* ctx, cudaStream_t st, const float* out, const ImgView&
 
 }  // namespace
 
+// The two halves of the min/max and mean/std finishers, also used by the row-tiled path (msrcr_tiled_run), where the
+// partials of every device's band are gathered before the fold.
+size_t msrcr_finish_partials_bytes() { return kStatBlocks * sizeof(Partial); }
+size_t msrcr_finish_partial_size() { return sizeof(Partial); }
+
+int msrcr_finish_stats(llie_ctx* ctx, cudaStream_t st, const float* out, int n, int h, int w, int layout, void* d_part) {
+  const ImgView v = make_view(layout, 3, h, w);
+  LLIE_LAUNCH(ctx, st, "msrcr_stats_kernel",
+              (msrcr_stats_kernel<<<dim3(kStatBlocks, n), kStatThreads, 0, st>>>(out, v, h, w, (Partial*)d_part)));
+  return LLIE_OK;
+}
+
+// nparts partials per image; npx = pixels per image the partials cover (the whole image, not the band)
+int msrcr_finish_apply(llie_ctx* ctx, cudaStream_t st, float* out, int n, int h, int w, int layout, const void* d_part,
+                       int nparts, double npx, const llie_msrcr_params& p, void* d_li) {
+  const ImgView v = make_view(layout, 3, h, w);
+  LLIE_LAUNCH(ctx, st, "msrcr_stats_fold_kernel",
+              (msrcr_stats_fold_kernel<<<n, 32, 0, st>>>((const Partial*)d_part, nparts, (float2*)d_li, npx, p.finish, p.finish_k)));
+  const long long band_px = (long long)h * w;
+  LLIE_LAUNCH(ctx, st, "msrcr_stretch_kernel",
+              (msrcr_stretch_kernel<<<dim3((unsigned)((band_px + 255) / 256), n), 256, 0, st>>>(out, v, h, w, (const float2*)d_li)));
+  return LLIE_OK;
+}
+
 int msrcr_finish_run(llie_ctx* ctx, float* out, int n, int h, int w, int layout, const llie_msrcr_params& p, cudaStream_t st) {
   void *d_part, *d_li;
   LLIE_TRY(ctx->workspace("msrcr.finish.partials", (size_t)n * kStatBlocks * sizeof(Partial), &d_part));
@@ -229,15 +253,13 @@ int msrcr_finish_run(llie_ctx* ctx, float* out, int n, int h, int w, int layout,
     LLIE_TRY(select_pass<0>(ctx, st, out, v, n, h, w, (SelState*)d_state, (unsigned*)d_hist, (float2*)d_li, p.finish_k));
     LLIE_TRY(select_pass<1>(ctx, st, out, v, n, h, w, (SelState*)d_state, (unsigned*)d_hist, (float2*)d_li, p.finish_k));
     LLIE_TRY(select_pass<2>(ctx, st, out, v, n, h, w, (SelState*)d_state, (unsigned*)d_hist, (float2*)d_li, p.finish_k));
+    const long long npx = (long long)h * w;
+    LLIE_LAUNCH(ctx, st, "msrcr_stretch_kernel",
+                (msrcr_stretch_kernel<<<dim3((unsigned)((npx + 255) / 256), n), 256, 0, st>>>(out, v, h, w, (const float2*)d_li)));
   } else {
-  LLIE_LAUNCH(ctx, st, "msrcr_stats_kernel",
-              (msrcr_stats_kernel<<<dim3(kStatBlocks, n), kStatThreads, 0, st>>>(out, v, h, w, (Partial*)d_part)));
-  LLIE_LAUNCH(ctx, st, "msrcr_stats_fold_kernel",
-              (msrcr_stats_fold_kernel<<<n, 32, 0, st>>>((const Partial*)d_part, (float2*)d_li, (double)h * w, p.finish, p.finish_k)));
+    LLIE_TRY(msrcr_finish_stats(ctx, st, out, n, h, w, layout, d_part));
+    LLIE_TRY(msrcr_finish_apply(ctx, st, out, n, h, w, layout, d_part, kStatBlocks, (double)h * w, p, d_li));
   }
-  const long long npx = (long long)h * w;
-  LLIE_LAUNCH(ctx, st, "msrcr_stretch_kernel",
-              (msrcr_stretch_kernel<<<dim3((unsigned)((npx + 255) / 256), n), 256, 0, st>>>(out, v, h, w, (const float2*)d_li)));
   return LLIE_OK;
 }
 

@@ -567,6 +567,7 @@ namespace {
 
 struct TileBufs {
   float *V, *C, *Ct, *SC, *TB, *B, *Bt, *SB, *T2, *band_top, *band_bot;
+  void *fin_part = nullptr, *fin_gather = nullptr, *fin_li = nullptr;  // global-statistics finisher
 };
 
 constexpr int kBandTopRows = 48, kBandBotRows = 64, kHaloRaw = 16;
@@ -738,6 +739,11 @@ int msrcr_tiled_run(llie_ctx* const* ctxs, int n_dev, const float* const* in, fl
       LLIE_TRY(ctx->workspace("tile.T2", (size_t)3 * hB * wC * 4, &q)); b.T2 = (float*)q;
       LLIE_TRY(ctx->workspace("tile.band_top", (size_t)kBandTopRows * RW * 4, &q)); b.band_top = (float*)q;
       LLIE_TRY(ctx->workspace("tile.band_bot", (size_t)kBandBotRows * RW * 4, &q)); b.band_bot = (float*)q;
+      if (p.finish != LLIE_FINISH_NONE) {
+        LLIE_TRY(ctx->workspace("tile.finish.partials", msrcr_finish_partials_bytes(), &b.fin_part));
+        LLIE_TRY(ctx->workspace("tile.finish.gather", msrcr_finish_partials_bytes() * n_dev, &b.fin_gather));
+        LLIE_TRY(ctx->workspace("tile.finish.lo_inv", 3 * sizeof(float2), &b.fin_li));
+      }
       if (!ctx->tile_event) {
         LLIE_CUDA_OK(cudaEventCreateWithFlags(&ctx->tile_event, cudaEventDisableTiming));
         LLIE_CUDA_OK(cudaEventCreate(&ctx->tile_t0));
@@ -764,8 +770,37 @@ int msrcr_tiled_run(llie_ctx* const* ctxs, int n_dev, const float* const* in, fl
     if (all_ok) {
       rc[d] = tiled_phase_b(ctx, d, n_dev, ctxs, in, out, geo, bufs, ev_c, H, W, p);
       if (rc[d] != LLIE_OK) msg[d] = llie_last_error();
-      else cudaEventRecord(ctx->tile_t1, ctx->stream);
     }
+    if (p.finish != LLIE_FINISH_NONE) {
+      // Global-statistics finisher across the shards ("one tiny all-reduce"): every device
+      // reduces its own band to 256 partials and pushes them into every device's gather buffer (an all-gather of
+      // 16 KB blocks by peer copies); each device then folds all partials in the same order -- identical (lo, 1/(hi-lo))
+      // everywhere -- and stretches its band in place.
+      const size_t pb = msrcr_finish_partials_bytes();
+      const int band_rows = geo[d].R1 - geo[d].R0;
+      auto stage1 = [&]() -> int {
+        LLIE_TRY(msrcr_finish_stats(ctx, ctx->stream, out[d], 1, band_rows, W, LLIE_NHWC, bufs[d].fin_part));
+        for (int e = 0; e < n_dev; ++e)
+          LLIE_TRY(copy_dev((char*)bufs[e].fin_gather + (size_t)d * pb, ctxs[e]->device, bufs[d].fin_part, ctx->device, pb, ctx->stream));
+        LLIE_CUDA_OK(cudaEventRecord(ev_c[d], ctx->stream));
+        return LLIE_OK;
+      };
+      auto stage2 = [&]() -> int {
+        for (int e = 0; e < n_dev; ++e)
+          if (e != d) LLIE_CUDA_OK(cudaStreamWaitEvent(ctx->stream, ev_c[e], 0));
+        return msrcr_finish_apply(ctx, ctx->stream, out[d], 1, band_rows, W, LLIE_NHWC, bufs[d].fin_gather,
+                                  n_dev * (int)(pb / msrcr_finish_partial_size()), (double)H * W, p, bufs[d].fin_li);
+      };
+      bar.wait();  // every device has enqueued its phase-B waits on ev_c before anyone records it again
+      const bool ok_b = all_ok && rc[d] == LLIE_OK;
+      if (ok_b) { rc[d] = stage1(); if (rc[d] != LLIE_OK) msg[d] = llie_last_error(); }
+      bar.wait();  // all partial pushes are enqueued and their events recorded
+      bool all_ok2 = all_ok;
+      for (int e = 0; e < n_dev; ++e) all_ok2 = all_ok2 && rc[e] == LLIE_OK;
+      bar.wait();
+      if (all_ok2) { rc[d] = stage2(); if (rc[d] != LLIE_OK) msg[d] = llie_last_error(); }
+    }
+    if (all_ok && rc[d] == LLIE_OK) cudaEventRecord(ctx->tile_t1, ctx->stream);
     cudaError_t e = cudaStreamSynchronize(ctx->stream);
     if (e == cudaSuccess && all_ok && rc[d] == LLIE_OK) cudaEventElapsedTime(&ctx->tile_ms, ctx->tile_t0, ctx->tile_t1);
     if (e != cudaSuccess && rc[d] == LLIE_OK) {

@@ -16,8 +16,12 @@ extern "C" int llie_msrcr_tiled(llie_ctx* const* ctxs, int n_dev, const float* c
   LLIE_REQUIRE(params->struct_size == sizeof(llie_msrcr_params), LLIE_E_ARG, "llie_msrcr_params.struct_size %u != %zu",
                params->struct_size, sizeof(llie_msrcr_params));
   LLIE_REQUIRE(params->blur == LLIE_BLUR_PYRAMID, LLIE_E_ARG, "row-tiled MSRCR uses the pyramid blur only");
-  LLIE_REQUIRE(params->finish == LLIE_FINISH_NONE, LLIE_E_ARG,
-               "row-tiled MSRCR has no global-statistics finisher yet (it needs a cross-device reduction)");
+  LLIE_REQUIRE(params->finish != LLIE_FINISH_PERCENTILE, LLIE_E_ARG,
+               "row-tiled MSRCR supports the minmax and meanstd finishers only (no cross-device radix select)");
+  LLIE_REQUIRE(params->finish >= LLIE_FINISH_NONE && params->finish <= LLIE_FINISH_MEANSTD, LLIE_E_ARG, "unknown finish mode %d",
+               params->finish);
+  LLIE_REQUIRE(params->finish != LLIE_FINISH_MEANSTD || (params->finish_k > 0.f && params->finish_k <= 16.f), LLIE_E_ARG,
+               "finish_k %g out of range (0, 16]", params->finish_k);
   LLIE_REQUIRE(params->n_scales >= 1 && params->n_scales <= 3, LLIE_E_ARG, "row-tiled MSRCR supports 1..3 scales (got %d)",
                params->n_scales);
   LLIE_REQUIRE(params->truncate > 0.f && params->truncate <= 8.f && params->in_bias > 0.f && params->in_scale >= 0.f,

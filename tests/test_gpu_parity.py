@@ -559,6 +559,23 @@ def test_msrcr_tiled_equals_single_device(parts):
     assert np.abs(y - ref).max() <= 1e-6, (parts, float(np.abs(y - ref).max()))
 
 
+@pytest.mark.parametrize("finish", ["minmax", "meanstd"])
+@pytest.mark.parametrize("parts", [1, 3, 8])
+def test_msrcr_tiled_finishers_equal_single_device(parts, finish):
+    """SURVEY.md 8(f) rank 2 on the row-tiled path: the per-band partial statistics are all-gathered by peer copies
+    and folded identically on every shard, so the stretched image equals the one-device finisher (fp64 sums differ
+    only in their grouping)."""
+    x = oracle.synth_lowlight(600, 520, 12)
+    prm = dict(finish=finish, finish_k=1.5)
+    ref = L.enhance(torch.from_numpy(x).cuda(), "msrcr", prm).cpu().numpy()
+    y = _run_tiled(x, parts, prm)
+    assert np.abs(y - ref).max() <= 2e-6, (parts, float(np.abs(y - ref).max()))
+    if finish == "minmax":
+        assert y.min() == 0.0 and y.max() == 1.0
+    with pytest.raises(L.LlieError):
+        _run_tiled(x, parts, dict(finish="percentile"))
+
+
 def test_msrcr_tiled_vs_oracle_and_odd_sizes():
     """Tiled path against the oracle itself, on a size with ragged width / last shard."""
     x = oracle.synth_lowlight(777, 501, 12)
