@@ -232,10 +232,9 @@ class Enhancer:
         _lib.check(self._lib.llie_debug_dce_activation(self._h, which, frame, out.ctypes.data_as(C.POINTER(C.c_float))))
         return out
 
-    def debug_dce_mode(self, keep_all: bool = False, unfused: bool = False, pack_pass: bool = False) -> None:
-        """Test hook (bf16 path): keep_all also stores x4/x6 to HBM; unfused runs one launch per layer; pack_pass
-        stages the image with a separate kernel instead of inside conv1's producer warp."""
-        _lib.check(self._lib.llie_debug_dce_mode(self._h, (1 if keep_all else 0) | (2 if unfused else 0) | (4 if pack_pass else 0)))
+    def debug_dce_mode(self, keep_all: bool = False, unfused: bool = False) -> None:
+        """Test hook (bf16 path): keep_all also stores x4/x6 to HBM; unfused runs one launch per layer."""
+        _lib.check(self._lib.llie_debug_dce_mode(self._h, (1 if keep_all else 0) | (2 if unfused else 0)))
 
     # -- weights -----------------------------------------------------------------------------
     def set_dce_weights(self, weights) -> None:

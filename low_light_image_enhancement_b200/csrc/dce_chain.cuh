@@ -145,7 +145,6 @@ struct ChainArgs {
   float sign;
   int u8;  // x / y are integer images: 1 = uint8_t (value = byte / 255; stored as rint(255 * value)), 2 = uint16_t (65535)
   int N, H, W, Wp, strips, segs, seg_rows, units;
-  int img_in;  // conv1's producer reads the caller's image itself (no packed copy in HBM; bf16 groups 0 and 3 only)
 };
 
 __device__ __forceinline__ uint32_t pack_bf16_relu(uint32_t a, uint32_t b) {
@@ -278,82 +277,6 @@ __device__ __forceinline__ void producer_loop(const ChainArgs& a, const Smem<GID
         }
       }
       __syncwarp();
-    }
-  }
-}
-
-// ---- producer of conv1 reading the caller's image: convert in flight, no packed copy in HBM -------------------
-// One warp builds each 132-pixel ring row itself: lane l owns positions l, l+32, ..: it loads the pixel's three
-// samples (fp32, or 8 / 16-bit integers) one row ahead of the row it is storing (the DRAM latency of row y+1 hides
-// behind the wait for row y's slot), packs them as [r g b 0 0 0 0 0] bf16 -- the same expressions as
-// dce_pack_input_kernel, so the activations stay bit-identical -- and stores 16 B per pixel; columns outside the
-// image are zeros.  Generic-proxy stores -> fence.proxy.async -> one arrive on the slot's full barrier.
-template <int GID, int S_, int J_>
-__device__ __forceinline__ void producer_loop_image(const ChainArgs& a, const Smem<GID>& sm) {
-  constexpr Group G = group_cfg(GID);
-  constexpr Src R = G.st[S_].src[J_];
-  static_assert(R.chunks == 1 && !G.split, "image producer: conv1 of the bf16 groups");
-  constexpr int L = G.S - 1;
-  constexpr int kDepth = R.depth;
-  constexpr int kValid = valid_px(G);
-  constexpr int kPer = (kRowPx + 31) / 32;
-  uint8_t* ring = sm.template ring<S_, J_>();
-  uint64_t* full = sm.template ring_full<S_, J_>();
-  uint64_t* empty = sm.template ring_empty<S_, J_>();
-  const int lane = threadIdx.x & 31;
-  uint32_t cnt = 0;
-  for (int u = blockIdx.x; u < a.units; u += gridDim.x) {
-    const Unit un = decode_unit(a, u);
-    const StageRows sr = stage_rows(un.ys, un.ye, a.H, L, S_);
-    const int x0 = un.sx * kValid - (L - S_) - 1;  // image x of ring position 0
-    long long base[kPer];
-    bool ok[kPer];
-#pragma unroll
-    for (int k = 0; k < kPer; ++k) {
-      const int i = lane + 32 * k, x = x0 + i;
-      ok[k] = i < kRowPx && x >= 0 && x < a.W;
-      base[k] = un.n * a.vx.sn + (long long)x * a.vx.sx;
-    }
-    auto load_row = [&](int y, float (&v)[kPer][3]) {
-#pragma unroll
-      for (int k = 0; k < kPer; ++k) {
-        const long long b = base[k] + (long long)y * a.vx.sy;
-#pragma unroll
-        for (int c = 0; c < 3; ++c) {
-          float t = 0.f;
-          if (ok[k]) {
-            if (a.u8 == 1) t = (1.f / 255.f) * (float)__ldg(reinterpret_cast<const uint8_t*>(a.x) + b + c * a.vx.sc);
-            else if (a.u8 == 2) t = (1.f / 65535.f) * (float)__ldg(reinterpret_cast<const uint16_t*>(a.x) + b + c * a.vx.sc);
-            else t = __ldg(a.x + b + c * a.vx.sc);
-          }
-          v[k][c] = t;
-        }
-      }
-    };
-    float cur[kPer][3], nxt[kPer][3];
-    load_row(sr.in_lo, cur);
-    for (int y = sr.in_lo; y < sr.in_hi; ++y, ++cnt) {
-      if (y + 1 < sr.in_hi) load_row(y + 1, nxt);
-      const uint32_t slot = cnt % kDepth;
-      mbar_wait(&empty[slot], ((cnt / kDepth) & 1) ^ 1);
-      uint8_t* dst = ring + slot * kRowBytes;
-#pragma unroll
-      for (int k = 0; k < kPer; ++k) {
-        const int i = lane + 32 * k;
-        if (i < kRowPx) {
-          const __nv_bfloat162 rg = __floats2bfloat162_rn(cur[k][0], cur[k][1]);
-          const __nv_bfloat162 b0 = __floats2bfloat162_rn(cur[k][2], 0.f);
-          *reinterpret_cast<uint4*>(dst + i * 16) =
-              make_uint4(*reinterpret_cast<const uint32_t*>(&rg), *reinterpret_cast<const uint32_t*>(&b0), 0u, 0u);
-        }
-      }
-      fence_proxy_async_smem();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&full[slot]);
-#pragma unroll
-      for (int k = 0; k < kPer; ++k)
-#pragma unroll
-        for (int c = 0; c < 3; ++c) cur[k][c] = nxt[k][c];
     }
   }
 }
@@ -741,14 +664,7 @@ __global__ void __launch_bounds__(n_threads(group_cfg(GID)), 1) dce_chain_kernel
       if constexpr (group_cfg(GID).st[s].src[j].ext != 0) {
         constexpr int mine = producer_index(group_cfg(GID), s, j);
         static_assert(group_cfg(GID).S + mine < kFirstEpiWarp, "issuer + producer warps must fit below the epilogue warps");
-        if (p == mine) {
-          if constexpr (s == 0 && j == 0 && group_cfg(GID).st[0].src[0].chunks == 1 && !group_cfg(GID).split) {
-            if (a.img_in) producer_loop_image<GID, s, j>(a, sm);
-            else producer_loop<GID, s, j>(a, sm);
-          } else {
-            producer_loop<GID, s, j>(a, sm);
-          }
-        }
+        if (p == mine) producer_loop<GID, s, j>(a, sm);
       }
     });
   } else {

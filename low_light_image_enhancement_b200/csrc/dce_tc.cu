@@ -102,7 +102,6 @@ struct DceTcPack {
   __nv_bfloat16* xin = nullptr;  // packed input [n][h][wp][8]
   bool keep_all = false;         // test hook: also write x4 / x6 (never needed by a later launch) to HBM
   bool unfused = false;          // test hook: one launch per layer (the same kernel with S = 1)
-  bool pack_pass = false;        // test hook: separate dce_pack_input_kernel pass instead of conv1's image producer
   __nv_bfloat16* act[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
 };
 static std::map<llie_ctx*, DceTcPack> g_packs;  // keyed by ctx (ctx is single-threaded by contract)
@@ -237,8 +236,7 @@ static int dce_forward_tc(llie_ctx* ctx, const void* in_v, void* out_v, float* m
   for (long long n0 = 0; n0 < n; n0 += chunk) {
     const int nb = (int)((n - n0 < chunk) ? (n - n0) : chunk);
     const float* x = reinterpret_cast<const float*>(static_cast<const char*>(in_v) + (size_t)n0 * h * w * 3 * esz);
-    const bool img_in = !split && !pk.pack_pass;  // conv1's producer converts the image itself
-    if (!img_in) {
+    {
       dim3 grid((w + 255) / 256, h, nb);
       if (split)
         LLIE_LAUNCH(ctx, st, "dce_pack_input_split_kernel",
@@ -258,7 +256,6 @@ static int dce_forward_tc(llie_ctx* ctx, const void* in_v, void* out_v, float* m
     a.N = nb; a.H = h; a.W = w; a.Wp = wp;
     a.x = x; a.y = reinterpret_cast<float*>(static_cast<char*>(out_v) + (size_t)n0 * h * w * 3 * esz);
     a.u8 = iot;  // kIoF32 / kIoU8 / kIoU16 = 0 / 1 / 2
-    a.img_in = img_in ? 1 : 0;
     a.maps = maps ? maps + n0 * (long long)h * w * 24 : nullptr;
     a.vx = vx; a.vm = vm; a.iters = p.iters; a.sign = p.curve_sign >= 0 ? 1.f : -1.f;
     // stage slot <- layer l (0..6): weights, bias, HBM destination (nullptr = keep on chip)
@@ -332,7 +329,6 @@ int dce_debug_mode(llie_ctx* ctx, int mode) {
   DceTcPack& pk = g_packs[ctx];
   pk.keep_all = (mode & 1) != 0;
   pk.unfused = (mode & 2) != 0;
-  pk.pack_pass = (mode & 4) != 0;  // stage the image with dce_pack_input_kernel instead of in conv1's producer
   return LLIE_OK;
 }
 
