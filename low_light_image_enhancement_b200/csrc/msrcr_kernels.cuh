@@ -557,6 +557,7 @@ msrcr_final_kernel(const TIO* __restrict__ x, TIO* __restrict__ out, ImgView v, 
       for (int i = 0; i < 4; ++i) win4[k][c][i] = ld(m4[k], c, jfirst - 1 + i);
 
   const int nsteps = (ye - ys + 3) / 4;
+  if (h_on && ys + 1 < ye) final_prefetch(x, v, io, img, ys + 1 - in_row0, X0);
   for (int s = 0; s < nsteps; ++s) {
     const int Y0 = ys + 4 * s, j0 = Y0 / 4 + kPC;
     float (*sv)[NV][128] = s_v[s & 1];
@@ -608,7 +609,7 @@ msrcr_final_kernel(const TIO* __restrict__ x, TIO* __restrict__ out, ImgView v, 
         if (Y >= ye) break;
         const int yl = Y - in_row0;
         float f[4][3], acc[4][3];
-        if (Y + 1 < ye) final_prefetch(x, v, io, img, yl + 1, X0);
+        if (Y + 2 < ye) final_prefetch(x, v, io, img, yl + 2, X0);  // two rows ahead: one row is shorter than the DRAM latency
         final_load(x, v, io, img, yl, X0, W, f);
         if (p.acc_in) {
           final_load(p.acc_in, v, io, img, yl, X0, W, acc);
