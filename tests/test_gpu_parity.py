@@ -456,6 +456,10 @@ def test_enhance_stream_equals_enhance(depth, blob):
     for grp, g in zip(groups, L.enhance_stream(groups, "msrcr", depth=depth)):
         assert np.array_equal(g, L.enhance(grp, "msrcr"))
     assert list(L.enhance_stream([], "msrcr", depth=depth)) == []
+    # 16-bit frames, zero-copy hand-out of the pinned stage (consumed before the slot is reused)
+    frames16 = [_u16_image(96, 160, s) for s in range(4)]
+    for f, g in zip(frames16, L.enhance_stream(frames16, "msrcr", depth=depth, copy=False)):
+        assert g.dtype == np.uint16 and np.array_equal(g, L.enhance(f, "msrcr"))
 
 
 def test_enhance_stream_errors(blob):
