@@ -632,3 +632,11 @@ def test_msrcr_tiled_real_devices_peer_copies():
     y = np.concatenate([o.cpu().numpy() for o in outs], 0)
     assert np.abs(y - ref).max() <= 1e-6
     assert all(o.device.index == d for d, o in enumerate(outs))
+    # global-statistics finisher: the partials cross the devices as peer copies too
+    for finish in ("minmax", "meanstd"):
+        prm = dict(finish=finish, finish_k=1.5)
+        ref = L.enhance(torch.from_numpy(x).cuda(0), "msrcr", prm).cpu().numpy()
+        for rep in range(3):
+            outs = L.msrcr_tiled(shards, prm)
+            y = np.concatenate([o.cpu().numpy() for o in outs], 0)
+            assert np.abs(y - ref).max() <= 2e-6, (finish, rep)
