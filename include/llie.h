@@ -131,11 +131,27 @@ int llie_msrcr_u16(llie_ctx* ctx, const uint16_t* in, uint16_t* out, int n, int 
                    const llie_msrcr_params* params, void* stream);
 
 /* Host-side planner of the pyramid blur, exposed so that CPU tests can check it without a
- * GPU: for `sigma`/`truncate` returns the cascade level's stride (4 or 16), the low-res
- * Gaussian's sigma and radius, and the L1 distance between the cascade's effective kernel
+ * GPU: for `sigma`/`truncate` returns the cascade level's stride (4 or 16), the radius of the
+ * low-resolution filter and the square root of its second moment (its taps are free-form,
+ * fitted by weighted least squares), and the L1 distance between the cascade's effective kernel
  * and the oracle's truncated Gaussian.  Needs no device. */
 int llie_msrcr_plan_query(float sigma, float truncate, int* stride, double* sigma_low, int* radius_low,
                           double* l1_error);
+
+/* Accuracy figures of that plan, all for the default map I = 255 x + 1 (a black pixel is I = 1, a white one 256):
+ *   l1_error    sum |k_cascade - k_oracle|, phase average: bounds the relative error of a surround on fine texture;
+ *   edge_error  largest relative error |dS| / S of the surround of a BLACK pixel beside a WHITE half-plane, over
+ *               all distances from the edge (the oracle's hard 4-sigma cut-off cannot be placed more finely than
+ *               the stride-4 grid);
+ *   line_error  the same for a 1-pixel white line on black.
+ * The MSRCR output moves by (gain C / 255) weight_k * (that figure) -- 0.135 x with the defaults (C = 171.6 for a
+ * grey-black pixel) -- so the 1e-4 parity budget of the fp32 path holds on such content only while the figure is
+ * below 7.4e-4; see DESIGN.md 2.1 for the measured bounds per content class.  LLIE_BLUR_DIRECT has no such term. */
+int llie_msrcr_plan_errors(float sigma, float truncate, double* l1_error, double* edge_error, double* line_error);
+
+/* The low-resolution taps of that plan (2 radius_low + 1 floats, centred).  *count receives the number of taps;
+ * taps may be NULL with capacity 0 to query the count only. */
+int llie_msrcr_plan_taps(float sigma, float truncate, float* taps, int capacity, int* count);
 
 /* north_star kernel (2): upload DCE-Net weights.  host_packed: the 79 416-float blob
  * W1 b1 ... W7 b7 (OIHW) of SURVEY.md 9.2, in HOST memory. */

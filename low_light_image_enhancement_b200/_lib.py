@@ -68,6 +68,8 @@ EXPORTS = {
     "llie_dce_forward_u16": (_I, [_VP, _VP, _VP, _VP, _I, _I, _I, _I, C.POINTER(DceParams), _VP]),
     "llie_msrcr_plan_query": (_I, [_F, _F, C.POINTER(_I), C.POINTER(C.c_double), C.POINTER(_I),
                                    C.POINTER(C.c_double)]),
+    "llie_msrcr_plan_errors": (_I, [_F, _F, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_double)]),
+    "llie_msrcr_plan_taps": (_I, [_F, _F, C.POINTER(_F), _I, C.POINTER(_I)]),
     "llie_dce_set_weights": (_I, [_VP, C.POINTER(_F), C.c_size_t]),
     "llie_dce_forward": (_I, [_VP, _VP, _VP, _VP, _I, _I, _I, _I, C.POINTER(DceParams), _VP]),
     "llie_debug_dce_activation": (_I, [_VP, _I, _I, C.POINTER(_F)]),

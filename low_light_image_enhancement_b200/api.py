@@ -91,11 +91,21 @@ def load_dce_state_dict(src, *, strict: bool = True) -> np.ndarray:
 
 
 def plan_query(sigma: float, truncate: float = 4.0) -> dict:
-    """Host-side planner of the pyramid blur (needs no GPU): stride, low-res sigma/radius, kernel L1 error."""
+    """Host-side planner of the pyramid blur (needs no GPU): stride, low-res radius and taps, and the three
+    accuracy figures of include/llie.h (l1_error; edge_error / line_error = relative error of the surround of a
+    black pixel beside a white half-plane / a 1-pixel white line, for I = 255 x + 1)."""
+    lib = _lib.load()
     st, sl, rl, l1 = C.c_int(), C.c_double(), C.c_int(), C.c_double()
-    _lib.check(_lib.load().llie_msrcr_plan_query(float(sigma), float(truncate), C.byref(st), C.byref(sl),
-                                                 C.byref(rl), C.byref(l1)))
-    return dict(stride=st.value, sigma_low=sl.value, radius_low=rl.value, l1_error=l1.value)
+    _lib.check(lib.llie_msrcr_plan_query(float(sigma), float(truncate), C.byref(st), C.byref(sl), C.byref(rl), C.byref(l1)))
+    e1, ee, el = C.c_double(), C.c_double(), C.c_double()
+    _lib.check(lib.llie_msrcr_plan_errors(float(sigma), float(truncate), C.byref(e1), C.byref(ee), C.byref(el)))
+    cnt = C.c_int()
+    _lib.check(lib.llie_msrcr_plan_taps(float(sigma), float(truncate), None, 0, C.byref(cnt)))
+    taps = np.empty(cnt.value, np.float32)
+    _lib.check(lib.llie_msrcr_plan_taps(float(sigma), float(truncate), taps.ctypes.data_as(C.POINTER(C.c_float)),
+                                        cnt.value, C.byref(cnt)))
+    return dict(stride=st.value, sigma_low=sl.value, radius_low=rl.value, l1_error=l1.value, edge_error=ee.value,
+                line_error=el.value, taps=taps)
 
 
 def shard_slice(n: int, rank: int, world: int) -> slice:

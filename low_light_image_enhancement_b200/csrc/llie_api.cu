@@ -290,6 +290,17 @@ int llie_msrcr_plan_query(float sigma, float truncate, int* stride, double* sigm
   return msrcr_plan_query(sigma, truncate, stride, sigma_low, radius_low, l1_error);
 }
 
+int llie_msrcr_plan_errors(float sigma, float truncate, double* l1_error, double* edge_error, double* line_error) {
+  LLIE_REQUIRE(l1_error && edge_error && line_error, LLIE_E_ARG, "null out-pointer");
+  return msrcr_plan_detail(sigma, truncate, l1_error, edge_error, line_error, nullptr, 0, nullptr);
+}
+
+int llie_msrcr_plan_taps(float sigma, float truncate, float* taps, int capacity, int* count) {
+  LLIE_REQUIRE(count, LLIE_E_ARG, "null count");
+  LLIE_REQUIRE(capacity >= 0 && (taps || capacity == 0), LLIE_E_ARG, "bad tap buffer");
+  return msrcr_plan_detail(sigma, truncate, nullptr, nullptr, nullptr, capacity ? taps : nullptr, capacity, count);
+}
+
 int llie_dce_set_weights(llie_ctx* ctx, const float* host_packed, size_t count) {
   LLIE_REQUIRE(ctx, LLIE_E_ARG, "null ctx");
   DeviceGuard g(ctx->device);

@@ -140,6 +140,8 @@ int dce_forward_int(llie_ctx* ctx, const void* in, void* out, int iot, float* ma
 int msrcr_pyramid_run(llie_ctx* ctx, const float* in, float* out, int n, int h, int w, int layout,
                       const llie_msrcr_params& p, cudaStream_t st);
 int msrcr_plan_query(float sigma, float truncate, int* stride, double* sigma_low, int* radius_low, double* l1);
+int msrcr_plan_detail(float sigma, float truncate, double* l1, double* edge, double* line, float* taps, int capacity,
+                      int* count);
 void msrcr_plan_free(MsrcrPlan* p);
 int msrcr_tiled_run(llie_ctx* const* ctxs, int n_dev, const float* const* in, float* const* out, const int* row0,
                     const int* rows, int H, int W, const llie_msrcr_params& p);

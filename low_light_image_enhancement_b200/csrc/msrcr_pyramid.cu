@@ -90,6 +90,7 @@ struct ScalePlan {
   double sigma_low;  // in low-res samples
   int radius_low;
   double l1;         // L1 distance of the effective kernel to the oracle kernel (phase average)
+  double edge, line; // relative surround errors of a black pixel beside a white half-plane / 1-px line (KernelErr)
   std::vector<float> taps;
 };
 
@@ -154,24 +155,85 @@ double cascade_l1(int level, const std::vector<Sig>& left, const std::vector<dou
 
 constexpr double kMinSigma = 12.0;  // below this the stride-4 grid is too coarse for 1e-4 parity
 constexpr double kLevelBSigma = 40.0;
+// Contrast the planner designs for: I = in_scale x + in_bias with the default 255 / 1, i.e. a pure black pixel
+// (I = 1) next to pure white (I = 256).
+constexpr double kDesignContrast = 255.0;
 
-int plan_scale(double sigma, double truncate, ScalePlan* out) {
-  if (sigma < kMinSigma) {
-    set_error("pyramid blur needs sigma >= %g (got %g); use blur=direct for small scales", kMinSigma, sigma);
-    return LLIE_E_ARG;
+// Error figures of an effective kernel against the oracle's (all phases; both sides):
+//   l1   phase-averaged sum |dk|                                    (fine texture, noise)
+//   edge max over distance d of rho |sum_{t >= d} dk| / (1 + rho tail_o(d))  = relative error of the surround S
+//        of a black pixel at distance d from a white half-plane (rho = 255: I = 1 next to I = 256)
+//   line max of rho |dk(d)| / (1 + rho k_o(d))                      = the same for a 1-pixel white line
+struct KernelErr { double l1 = 0, edge = 0, line = 0; };
+
+// Unit responses: h[ph] = weights on PIXELS (index = absolute position, the pixel itself is `ph`) of a unit
+// low-resolution tap at low-res offset 0, for the pixel of phase ph.  A low-res tap at offset j shifts it by s j.
+std::vector<Sig> unit_responses(int level) {
+  const int s = level ? 16 : 4;
+  const std::vector<double> gd = gauss_taps(4.0, kRD);
+  std::vector<Sig> h;
+  for (int ph = 0; ph < s; ++ph) {
+    Sig c = lagrange_sig(level ? 4 : 6, ph);
+    Sig e = level ? through_upsampler(c) : c;
+    if (level) e = spread4(e, gd);
+    h.push_back(spread4(e, gd));
   }
-  const int level = sigma >= kLevelBSigma ? 1 : 0;
+  return h;
+}
+
+// dense effective kernel of phase ph on offsets -R..R (relative to the pixel) for symmetric low-res taps x[0..rl]
+void effective_dense(const Sig& h, int ph, int s, const std::vector<double>& x, int R, std::vector<double>* out) {
+  out->assign(2 * R + 1, 0.0);
+  const int rl = (int)x.size() - 1;
+  for (int j = -rl; j <= rl; ++j) {
+    const double xv = x[j < 0 ? -j : j];
+    if (xv == 0.0) continue;
+    // absolute position a = h.lo + i + s j  ->  offset t = a - ph
+    for (size_t i = 0; i < h.v.size(); ++i) {
+      const int t = h.lo + (int)i + s * j - ph;
+      if (t >= -R && t <= R) (*out)[t + R] += xv * h.v[i];
+    }
+  }
+}
+
+KernelErr kernel_errors(int level, const std::vector<Sig>& h, const std::vector<double>& x, const std::vector<double>& kor) {
+  const int s = level ? 16 : 4, rl = (int)x.size() - 1, ro = ((int)kor.size() - 1) / 2;
+  int ext = 0;
+  for (auto& q : h) ext = std::max(ext, std::max(std::abs(q.lo), std::abs(q.lo + (int)q.v.size())));
+  const int R = std::max(ro, s * rl + ext) + s;
+  const int L = 2 * R + 1;
+  std::vector<double> ko(L, 0.0), tail_r(L + 1, 0.0), tail_l(L + 1, 0.0), e;
+  for (int t = -ro; t <= ro; ++t) ko[t + R] = kor[t + ro];
+  for (int i = L - 1; i >= 0; --i) tail_r[i] = tail_r[i + 1] + ko[i];
+  for (int i = 0; i < L; ++i) tail_l[i + 1] = tail_l[i] + ko[i];
+  KernelErr r;
+  const double rho = kDesignContrast;
+  for (int ph = 0; ph < s; ++ph) {
+    effective_dense(h[ph], ph, s, x, R, &e);
+    double l1 = 0, acc = 0;
+    for (int i = L - 1; i >= 0; --i) {  // white half-plane on the right, starting at offset i - R
+      const double dk = e[i] - ko[i];
+      l1 += std::fabs(dk);
+      acc += dk;
+      r.edge = std::max(r.edge, rho * std::fabs(acc) / (1.0 + rho * tail_r[i]));
+      r.line = std::max(r.line, rho * std::fabs(dk) / (1.0 + rho * ko[i]));
+    }
+    acc = 0;
+    for (int i = 0; i < L; ++i) {  // ... on the left
+      acc += e[i] - ko[i];
+      r.edge = std::max(r.edge, rho * std::fabs(acc) / (1.0 + rho * tail_l[i + 1]));
+    }
+    r.l1 += l1 / s;
+  }
+  return r;
+}
+
+// v1 family: a truncated Gaussian (sigma_low, r_low), sigma_low by golden-section search on the L1 distance.
+void plan_taps_gauss(int level, double sigma, int ro, const std::vector<Sig>& left, const std::vector<double>& gd,
+                     const std::vector<double>& kor, std::vector<double>* taps) {
   const int s = level ? 16 : 4;
   const double var_fixed = level ? (16.0 + 256.0 + 256.0) : 16.0;  // prefilters (+ upsampler), pixel^2
   const double sl0 = std::sqrt(sigma * sigma - var_fixed) / s;
-  const int ro = (int)std::ceil(truncate * sigma);
-  const std::vector<double> kor = gauss_taps(sigma, ro);
-  const std::vector<double> gd = gauss_taps(4.0, kRD);
-  std::vector<Sig> left;
-  for (int ph = 0; ph < s; ++ph) {
-    Sig c = lagrange_sig(level ? 4 : 6, ph);
-    left.push_back(level ? through_upsampler(c) : c);
-  }
   double best_l1 = 1e30, best_sl = sl0;
   int best_rl = 1;
   const int rl_mid = ro / s;
@@ -195,12 +257,157 @@ int plan_scale(double sigma, double truncate, ScalePlan* out) {
     const double xb = f1 < f2 ? x1 : x2, fb = f1 < f2 ? f1 : f2;
     if (fb < best_l1) { best_l1 = fb; best_sl = xb; best_rl = rl; }
   }
+  *taps = gauss_taps(best_sl, best_rl);
+}
+
+// v2: free-form symmetric low-res taps x[0..rl] by weighted linear least squares.  The effective kernel is linear
+// in the taps; the objective is the squared error of (a) the one-sided cumulative sums of the kernel (the response
+// to a straight edge), each weighted by rho / (1 + rho tail) -- the relative error it causes in the surround of a
+// black pixel beside a white half-plane -- and (b) the kernel itself weighted by rho / (1 + rho k_o) (a 1-pixel
+// line), subject to sum(taps) = 1.  The v1 family only minimised the L1 distance, which left the oracle's hard
+// 4-sigma truncation smeared over ~23 px at stride 16: 5.8e-4 in the output on a black-to-white edge against
+// 1.3e-4 (sigma = 15), 1.0e-4 (80), 3.7e-5 (250) now.  What remains is the floor of a stride-4 grid: a jump of
+// k_o(r) per pixel cannot be placed more finely than the grid.
+bool plan_taps_ls(int level, int rl, const std::vector<Sig>& h, const std::vector<double>& kor, std::vector<double>* x_out) {
+  const int s = level ? 16 : 4, ro = ((int)kor.size() - 1) / 2, n = rl + 1;
+  int ext = 0;
+  for (auto& q : h) ext = std::max(ext, std::max(std::abs(q.lo), std::abs(q.lo + (int)q.v.size())));
+  const int R = std::max(ro, s * rl + ext) + s;
+  const int L = 2 * R + 1;
+  const double rho = kDesignContrast;
+  std::vector<double> ko(L, 0.0), tail_r(L + 1, 0.0), tail_l(L + 1, 0.0);
+  for (int t = -ro; t <= ro; ++t) ko[t + R] = kor[t + ro];
+  for (int i = L - 1; i >= 0; --i) tail_r[i] = tail_r[i + 1] + ko[i];
+  for (int i = 0; i < L; ++i) tail_l[i + 1] = tail_l[i] + ko[i];
+  std::vector<double> M((size_t)n * n, 0.0), v(n, 0.0);
+  std::vector<double> A((size_t)L * n), row(n), unit(n, 0.0), col;
+  for (int ph = 0; ph < s; ++ph) {
+    // A[i][j] = d e(offset i - R) / d x_j
+    for (int j = 0; j < n; ++j) {
+      unit.assign(n, 0.0);
+      unit[j] = 1.0;
+      effective_dense(h[ph], ph, s, unit, R, &col);
+      for (int i = 0; i < L; ++i) A[(size_t)i * n + j] = col[i];
+    }
+    auto add_row = [&](const double* a, double b, double w) {
+      if (w == 0.0) return;
+      for (int j = 0; j < n; ++j) {
+        const double aw = a[j] * w * w;
+        if (aw == 0.0) continue;
+        v[j] += aw * b;
+        double* m = &M[(size_t)j * n];
+        for (int k = j; k < n; ++k) m[k] += aw * a[k];
+      }
+    };
+    row.assign(n, 0.0);
+    for (int i = L - 1; i >= 0; --i) {  // cumulative from the right
+      for (int j = 0; j < n; ++j) row[j] += A[(size_t)i * n + j];
+      add_row(row.data(), tail_r[i], rho / (1.0 + rho * tail_r[i]));
+      add_row(&A[(size_t)i * n], ko[i], rho / (1.0 + rho * ko[i]));
+    }
+    row.assign(n, 0.0);
+    for (int i = 0; i < L; ++i) {  // cumulative from the left
+      for (int j = 0; j < n; ++j) row[j] += A[(size_t)i * n + j];
+      add_row(row.data(), tail_l[i + 1], rho / (1.0 + rho * tail_l[i + 1]));
+    }
+  }
+  for (int j = 0; j < n; ++j)
+    for (int k = 0; k < j; ++k) M[(size_t)j * n + k] = M[(size_t)k * n + j];
+  double tr = 0;
+  for (int j = 0; j < n; ++j) tr += M[(size_t)j * n + j];
+  for (int j = 0; j < n; ++j) M[(size_t)j * n + j] += 1e-9 * tr / n;  // Tikhonov: the far taps are weakly determined
+  // KKT system [M c; c^T 0] [x; mu] = [v; 1], c = (1, 2, 2, ...): Gaussian elimination with partial pivoting
+  const int m = n + 1;
+  std::vector<long double> K((size_t)m * (m + 1), 0.0L);
+  for (int j = 0; j < n; ++j) {
+    for (int k = 0; k < n; ++k) K[(size_t)j * (m + 1) + k] = M[(size_t)j * n + k];
+    const long double c = j == 0 ? 1.0L : 2.0L;
+    K[(size_t)j * (m + 1) + n] = c;
+    K[(size_t)n * (m + 1) + j] = c;
+    K[(size_t)j * (m + 1) + m] = v[j];
+  }
+  K[(size_t)n * (m + 1) + m] = 1.0L;
+  for (int c = 0; c < m; ++c) {
+    int piv = c;
+    for (int r2 = c + 1; r2 < m; ++r2)
+      if (fabsl(K[(size_t)r2 * (m + 1) + c]) > fabsl(K[(size_t)piv * (m + 1) + c])) piv = r2;
+    if (fabsl(K[(size_t)piv * (m + 1) + c]) < 1e-300L) return false;
+    if (piv != c)
+      for (int k = 0; k <= m; ++k) std::swap(K[(size_t)piv * (m + 1) + k], K[(size_t)c * (m + 1) + k]);
+    for (int r2 = c + 1; r2 < m; ++r2) {
+      const long double f = K[(size_t)r2 * (m + 1) + c] / K[(size_t)c * (m + 1) + c];
+      if (f == 0.0L) continue;
+      for (int k = c; k <= m; ++k) K[(size_t)r2 * (m + 1) + k] -= f * K[(size_t)c * (m + 1) + k];
+    }
+  }
+  std::vector<long double> sol(m);
+  for (int r2 = m - 1; r2 >= 0; --r2) {
+    long double a = K[(size_t)r2 * (m + 1) + m];
+    for (int k = r2 + 1; k < m; ++k) a -= K[(size_t)r2 * (m + 1) + k] * sol[k];
+    sol[r2] = a / K[(size_t)r2 * (m + 1) + r2];
+  }
+  x_out->resize(n);
+  for (int j = 0; j < n; ++j) {
+    (*x_out)[j] = (double)sol[j];
+    if (!std::isfinite((*x_out)[j])) return false;
+  }
+  return true;
+}
+
+constexpr int kMaxLsRadius = 96;  // the least-squares fit is O(L n^2) per phase; beyond this (sigma > ~1400) keep v1
+
+int plan_scale(double sigma, double truncate, ScalePlan* out) {
+  if (sigma < kMinSigma) {
+    set_error("pyramid blur needs sigma >= %g (got %g); use blur=direct for small scales", kMinSigma, sigma);
+    return LLIE_E_ARG;
+  }
+  const int level = sigma >= kLevelBSigma ? 1 : 0;
+  const int s = level ? 16 : 4;
+  const int ro = (int)std::ceil(truncate * sigma);
+  const std::vector<double> kor = gauss_taps(sigma, ro);
+  const std::vector<double> gd = gauss_taps(4.0, kRD);
+  std::vector<Sig> left;
+  for (int ph = 0; ph < s; ++ph) {
+    Sig c = lagrange_sig(level ? 4 : 6, ph);
+    left.push_back(level ? through_upsampler(c) : c);
+  }
+  const std::vector<Sig> h = unit_responses(level);
+  auto half = [](const std::vector<double>& k) {  // centred taps -> x[0..rl]
+    const int rl = ((int)k.size() - 1) / 2;
+    return std::vector<double>(k.begin() + rl, k.end());
+  };
+  // candidate 1: the Gaussian family (v1)
+  std::vector<double> kg;
+  plan_taps_gauss(level, sigma, ro, left, gd, kor, &kg);
+  std::vector<double> best = half(kg);
+  KernelErr best_err = kernel_errors(level, h, best, kor);
+  // candidate 2: weighted least squares with a few more taps than the oracle's radius covers
+  const int rl_ls = (ro + s - 1) / s + (level ? 5 : 2);
+  if (rl_ls <= kMaxLsRadius) {
+    std::vector<double> x;
+    if (plan_taps_ls(level, rl_ls, h, kor, &x)) {
+      const KernelErr e = kernel_errors(level, h, x, kor);
+      if (std::max(e.edge, e.line) < std::max(best_err.edge, best_err.line) && e.l1 < 4.0 * best_err.l1 + 1e-4) {
+        best = x;
+        best_err = e;
+      }
+    }
+  }
+  const int rl = (int)best.size() - 1;
+  std::vector<double> k(2 * rl + 1);
+  double m2 = 0, m0 = 0;
+  for (int t = -rl; t <= rl; ++t) {
+    k[t + rl] = best[t < 0 ? -t : t];
+    m0 += k[t + rl];
+    m2 += k[t + rl] * t * t;
+  }
   out->level = level;
   out->stride = s;
-  out->sigma_low = best_sl;
-  out->radius_low = best_rl;
-  out->l1 = best_l1;
-  std::vector<double> k = gauss_taps(best_sl, best_rl);
+  out->sigma_low = std::sqrt(std::max(m2 / m0, 0.0));  // second moment of the taps (they are free-form now)
+  out->radius_low = rl;
+  out->l1 = best_err.l1;
+  out->edge = best_err.edge;
+  out->line = best_err.line;
   out->taps.assign(k.begin(), k.end());
   return LLIE_OK;
 }
@@ -247,6 +454,21 @@ int msrcr_plan_query(float sigma, float truncate, int* stride, double* sigma_low
   *sigma_low = sp.sigma_low;
   *radius_low = sp.radius_low;
   *l1 = sp.l1;
+  return LLIE_OK;
+}
+
+int msrcr_plan_detail(float sigma, float truncate, double* l1, double* edge, double* line, float* taps, int capacity,
+                      int* count) {
+  ScalePlan sp;
+  LLIE_TRY(get_scale_plan(sigma, truncate, &sp));
+  if (l1) *l1 = sp.l1;
+  if (edge) *edge = sp.edge;
+  if (line) *line = sp.line;
+  if (count) *count = (int)sp.taps.size();
+  if (taps) {
+    LLIE_REQUIRE(capacity >= (int)sp.taps.size(), LLIE_E_ARG, "tap buffer too small: %d < %zu", capacity, sp.taps.size());
+    std::copy(sp.taps.begin(), sp.taps.end(), taps);
+  }
   return LLIE_OK;
 }
 

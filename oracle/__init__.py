@@ -22,12 +22,12 @@ from .msrcr import (MSRCR_DEFAULTS, gaussian_kernel_1d, blur_edge_clamp,
                     msrcr, msrcr_window, msrcr_unclipped)
 from .zero_dce import (DCE_LAYERS, DCE_NUM_PARAMS, init_weights, pack_weights,
                        unpack_weights, dce_net, apply_curves, zero_dce)
-from .synth import synth_lowlight
+from .synth import synth_lowlight, hard_cases, HARD_CASE_CLASS
 from .u8 import from_u8, to_u8, msrcr_u8, zero_dce_u8, from_u16, to_u16, msrcr_u16, zero_dce_u16
 
 __all__ = [
     "MSRCR_DEFAULTS", "gaussian_kernel_1d", "blur_edge_clamp", "msrcr",
     "msrcr_window", "msrcr_unclipped", "DCE_LAYERS", "DCE_NUM_PARAMS", "init_weights",
     "pack_weights", "unpack_weights", "dce_net", "apply_curves", "zero_dce",
-    "synth_lowlight", "from_u8", "to_u8", "msrcr_u8", "zero_dce_u8", "from_u16", "to_u16", "msrcr_u16", "zero_dce_u16",
+    "synth_lowlight", "hard_cases", "HARD_CASE_CLASS", "from_u8", "to_u8", "msrcr_u8", "zero_dce_u8", "from_u16", "to_u16", "msrcr_u16", "zero_dce_u16",
 ]

@@ -55,12 +55,43 @@ def test_pyramid_planner_matches_the_oracle_kernel():
         q = L.plan_query(sigma)
         assert q["stride"] == stride
         assert q["l1_error"] < 1.5e-4, (sigma, q)
-        # variances add: low-res Gaussian + prefilter(s) (+ the B->C Gaussian upsampler) ~ sigma^2
+        # variances add: low-res filter + prefilter(s) (+ the B->C Gaussian upsampler) ~ sigma^2
         eff = (q["sigma_low"] * stride) ** 2
         assert abs(np.sqrt(eff + (16 if stride == 4 else 16 + 256 + 256)) / sigma - 1) < 0.03
-        assert abs(q["radius_low"] * stride - 4 * sigma) <= 2 * stride
+        assert 0 <= q["radius_low"] * stride - 4 * sigma <= 6 * stride
+        assert q["taps"].shape == (2 * q["radius_low"] + 1,) and abs(float(q["taps"].astype(np.float64).sum()) - 1) < 1e-6
+        assert np.array_equal(q["taps"], q["taps"][::-1])
     with pytest.raises(L.LlieError):
         L.plan_query(6.0)  # below the cascade's range: an error, not a silent fallback
+
+
+def test_pyramid_planner_hard_edge_figures():
+    """the planner's own figures for a black pixel beside white content (I = 1 vs 256).  The
+    MSRCR output moves by 0.404 / 3 = 0.135 x the relative surround error.  The v1 planner (Gaussian taps, L1 only)
+    gave 3.9e-4 / 5.8e-4 / 2.0e-4 on a straight edge for sigma = 15 / 80 / 250; the least-squares taps must stay
+    at the stride-4 floor documented in DESIGN.md 2.1."""
+    amp = 0.6 * 46.0 * np.log(125.0 / 3.0) / 255.0 / 3.0
+    bound = {15.0: (1.35e-4, 1.30e-4), 80.0: (1.10e-4, 0.4e-4), 250.0: (0.45e-4, 0.15e-4)}
+    for sigma, (edge_max, line_max) in bound.items():
+        q = L.plan_query(sigma)
+        assert amp * q["edge_error"] <= edge_max, (sigma, amp * q["edge_error"])
+        assert amp * q["line_error"] <= line_max, (sigma, amp * q["line_error"])
+
+
+def test_cascade_model_on_hard_content():
+    """The float64 twin of the cascade (tools/cascade_model.py: the GPU path's operators in exact arithmetic, with
+    the planner's taps) against the oracle on small hard-content images: what the kernel approximation alone costs."""
+    import sys
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import cascade_model
+    import oracle
+    worst = {}
+    for name, x in oracle.hard_cases(200, 288).items():
+        d = float(np.abs(cascade_model.msrcr_cascade(x) - oracle.msrcr(x)).max())
+        cls = oracle.HARD_CASE_CLASS[name]
+        worst[cls] = max(worst.get(cls, 0.0), d)
+        assert d <= (1.5e-4 if cls == "bw" else 5e-5), (name, d)
+    assert worst["bw"] > 1e-5  # the class is exercised: the truncation edge of sigma = 15 lies inside these images
 
 
 def test_shard_slice_partitions_exactly():

@@ -124,6 +124,49 @@ def test_msrcr_4k_windowed_oracle():
         assert np.abs(y[y0:y0 + 96, x0:x0 + 96] - ref).max() <= TOL_F32, (y0, x0)
 
 
+# Hard content.  The cascade evaluates every surround on a stride-4 (sigma < 40) or stride-16
+# grid, so the oracle's HARD 4-sigma cut-off -- a jump of k(r) per pixel in the kernel -- cannot be placed more
+# finely than that grid.  It only shows where a pure-black pixel (I = 1) has pure-white content (I = 256) exactly
+# 4 sigma away: measured bound 1.5e-4 for that class ("bw"), 1e-4 for everything else.
+TOL_F32_BW = 1.5e-4
+
+
+@pytest.mark.parametrize("layout", ["NHWC", "NCHW"])
+def test_msrcr_pyramid_hard_content(layout):
+    h, w = 1300, 2400   # the dark side of the vertical features is wider than 4 * 250
+    worst = {}
+    for name, x in oracle.hard_cases(h, w).items():
+        ref = oracle.msrcr(x)
+        if layout == "NHWC":
+            y = L.enhance(torch.from_numpy(x).cuda(), "msrcr").cpu().numpy()
+        else:
+            xc = torch.from_numpy(np.ascontiguousarray(x.transpose(2, 0, 1))[None]).cuda()
+            y = L.enhance(xc, "msrcr", dict(layout="NCHW"))[0].permute(1, 2, 0).cpu().numpy()
+        d = np.abs(y.astype(np.float64) - ref)
+        iy, ix, ic = np.unravel_index(d.argmax(), d.shape)
+        cls = oracle.HARD_CASE_CLASS[name]
+        worst[cls] = max(worst.get(cls, 0.0), float(d.max()))
+        print(f"hard content [{layout}] {name:24s} [{cls:4s}] max-abs {d.max():.3e} at (y={iy}, x={ix}, c={ic})")
+        assert d.max() <= (TOL_F32_BW if cls == "bw" else TOL_F32), (name, float(d.max()))
+        if layout == "NHWC" and name in ("edge_v_0_1", "line1_white_on_black", "noise_uniform"):
+            yd = L.enhance(torch.from_numpy(np.ascontiguousarray(x[:64])).cuda(), "msrcr", dict(blur="direct")).cpu().numpy()
+            assert np.abs(yd - oracle.msrcr(np.ascontiguousarray(x[:64]))).max() <= TOL_F32, name   # the exact FIR has no such term
+    print(f"hard content [{layout}] worst per class: " + ", ".join(f"{k} {v:.3e}" for k, v in sorted(worst.items())))
+
+
+def test_msrcr_pyramid_hard_content_u8():
+    """8-bit images of the same family: bytes differ from the oracle's by at most one level."""
+    h, w = 700, 1400
+    for name, x in oracle.hard_cases(h, w).items():
+        if name in ("edge_v_lowlight", "noise_uniform"):
+            continue
+        xb = oracle.to_u8(x)
+        ref = oracle.msrcr_u8(xb)[0].astype(np.int32)
+        y = L.enhance(torch.from_numpy(xb).cuda(), "msrcr").cpu().numpy().astype(np.int32)
+        assert np.abs(y - ref).max() <= 1, name
+        assert float(np.mean(y != ref)) <= 2e-3, (name, float(np.mean(y != ref)))
+
+
 # ---------------------------------------------------------------- global-statistics finishers
 @pytest.mark.parametrize("finish", ["minmax", "meanstd", "percentile"])
 def test_msrcr_finishers_match_oracle(finish):
