@@ -92,14 +92,22 @@ const char* llie_last_error(void);
 /* fills *count with the number of CUDA devices; LLIE_E_CUDA if none (no CPU fallback) */
 int llie_device_count(int* count);
 
-/* Fill a params struct with the SURVEY.md section 9 defaults. */
+/* Fill a params struct with the SURVEY.md section 9 defaults.  The structs are versioned by their leading
+ * struct_size: the CALLER sets p->struct_size = sizeof(its struct) BEFORE the call and the library writes exactly
+ * that many bytes (LLIE_E_ARG for 0 or any size it does not know).  llie_msrcr_params is accepted in its first
+ * layout (104 bytes, through `blur`) and the current one (112 bytes); a shorter struct means finish = NONE. */
 int llie_msrcr_default_params(llie_msrcr_params* p);
 int llie_dce_default_params(llie_dce_params* p);
 
 /* A context binds one device (SURVEY.md 8(b) "ownership": streams, workspaces and
- * packed weights belong to the ctx; no allocation on the hot path after warm-up). */
+ * packed weights belong to the ctx; no allocation on the hot path after warm-up).  A ctx is not thread-safe: one
+ * ctx per host thread; different ctxs share no state and may be driven from different threads concurrently. */
 int llie_create(llie_ctx** out, int device);
 int llie_destroy(llie_ctx* ctx);
+/* SURVEY.md 8(b) `llie_create(out, device_ids, n_dev)`: one ctx per listed device, all or nothing (out_ctxs has
+ * n_dev slots).  The same device may be listed more than once ("virtual devices" for one-GPU tests). */
+int llie_create_group(llie_ctx** out_ctxs, const int* device_ids, int n_dev);
+int llie_destroy_group(llie_ctx* const* ctxs, int n_dev);
 int llie_sync(llie_ctx* ctx);
 /* bytes of device workspace currently held by the ctx */
 int llie_workspace_bytes(llie_ctx* ctx, size_t* bytes);
@@ -184,6 +192,30 @@ int llie_debug_dce_mode(llie_ctx* ctx, int mode);
 /* north_star kernel (3) alone: curves from given maps (N,H,W,24)/(N,24,H,W) fp32. */
 int llie_dce_curves(llie_ctx* ctx, const float* in, const float* maps, float* out, int n, int h, int w,
                     int layout, const llie_dce_params* params, void* stream);
+
+/* Batch sharder (north_star: "shards batches of independent images or frames across the
+ * 8xB200 box with no collectives").  ONE call processes n_dev independent sub-batches: ctxs[d] enhances the
+ * n_per_dev[d] images at in_per_dev[d] into out_per_dev[d] (h x w x 3 each, `layout`, samples of io_type) with the
+ * unchanged single-device launch sequence on its own stream.  Nothing is exchanged between devices; every device
+ * is synchronised once, at the end (the call is synchronous).  params: const llie_msrcr_params* or
+ * const llie_dce_params* according to method (Zero-DCE: llie_dce_set_weights on every ctx first; no curve maps).
+ * where = LLIE_SHARD_DEVICE: the pointers are device memory on ctxs[d]'s device (zero copy).
+ * where = LLIE_SHARD_HOST:   the pointers are HOST memory; each device streams its frames through three staging
+ *                            slots on three streams (upload / kernels / download overlap).  Pinned memory is
+ *                            copied in place, pageable memory through pinned stages owned by the ctx.
+ * The ctxs must be distinct and live on n_dev distinct devices, or all on one device ("virtual devices"). */
+#define LLIE_METHOD_MSRCR 0
+#define LLIE_METHOD_ZERO_DCE 1
+#define LLIE_IO_F32 0
+#define LLIE_IO_U8 1
+#define LLIE_IO_U16 2
+#define LLIE_SHARD_DEVICE 0
+#define LLIE_SHARD_HOST 1
+int llie_enhance_sharded(llie_ctx* const* ctxs, int n_dev, int method, int io_type, const void* const* in_per_dev,
+                         void* const* out_per_dev, const int* n_per_dev, int h, int w, int layout, const void* params,
+                         int where);
+/* Device-side duration (CUDA events on the ctx's stream) of this ctx's shard in the last llie_enhance_sharded call. */
+int llie_shard_last_ms(llie_ctx* ctx, float* ms);
 
 /* Row-tiled MSRCR of ONE image across several devices of this process (config 5):
  * device d holds rows [row0[d], row0[d]+rows[d]) of the h_total x w image in

@@ -16,6 +16,8 @@ NHWC, NCHW = 0, 1
 F32, BF16, F32_SIMT = 0, 1, 2
 FINISH = {"none": 0, "minmax": 1, "meanstd": 2, "percentile": 3}
 BLUR_PYRAMID, BLUR_DIRECT = 0, 1
+METHOD = {"msrcr": 0, "zero_dce": 1}
+SHARD_DEVICE, SHARD_HOST = 0, 1
 MAX_SCALES = 8
 
 
@@ -56,6 +58,11 @@ EXPORTS = {
     "llie_dce_default_params": (_I, [C.POINTER(DceParams)]),
     "llie_create": (_I, [C.POINTER(_VP), _I]),
     "llie_destroy": (_I, [_VP]),
+    "llie_create_group": (_I, [C.POINTER(_VP), C.POINTER(_I), _I]),
+    "llie_destroy_group": (_I, [C.POINTER(_VP), _I]),
+    "llie_enhance_sharded": (_I, [C.POINTER(_VP), _I, _I, _I, C.POINTER(_VP), C.POINTER(_VP), C.POINTER(_I), _I, _I, _I,
+                                  _VP, _I]),
+    "llie_shard_last_ms": (_I, [_VP, C.POINTER(_F)]),
     "llie_sync": (_I, [_VP]),
     "llie_workspace_bytes": (_I, [_VP, C.POINTER(C.c_size_t)]),
     "llie_launch_count": (_I, [_VP, C.POINTER(C.c_uint64)]),

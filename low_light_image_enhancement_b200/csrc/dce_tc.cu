@@ -104,10 +104,15 @@ struct DceTcPack {
   bool unfused = false;          // test hook: one launch per layer (the same kernel with S = 1)
   __nv_bfloat16* act[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
 };
-static std::map<llie_ctx*, DceTcPack> g_packs;  // keyed by ctx (ctx is single-threaded by contract)
+// Owned by the ctx (llie_ctx::tc), created on first use: no process-wide state, so host threads that each drive
+// their own ctx never touch a shared container.
+static DceTcPack& tc_pack(llie_ctx* ctx) {
+  if (!ctx->tc) ctx->tc = new DceTcPack;
+  return *ctx->tc;
+}
 
 int dce_pack_bf16(llie_ctx* ctx, DceWeights* dw) {
-  DceTcPack& pk = g_packs[ctx];
+  DceTcPack& pk = tc_pack(ctx);
   const float* raw = dw->host_raw.data();
   std::vector<__nv_bfloat16> tiles;
   float* biases = pk.h_bias;
@@ -198,9 +203,8 @@ int dce_pack_bf16(llie_ctx* ctx, DceWeights* dw) {
 }
 
 void dce_tc_release(llie_ctx* ctx) {
-  auto it = g_packs.find(ctx);
-  if (it == g_packs.end()) return;
-  g_packs.erase(it);
+  delete ctx->tc;
+  ctx->tc = nullptr;
 }
 
 // split = false: bf16 operands (config 2).  split = true: hi/lo bf16 pairs, three MMAs per product -- fp32-accurate
@@ -210,7 +214,7 @@ static int dce_forward_tc(llie_ctx* ctx, const void* in_v, void* out_v, float* m
   const size_t esz = io_bytes(iot);  // bytes per image sample
   DceWeights* dw = ctx->dce;
   LLIE_REQUIRE(dw != nullptr && dw->d_bf16 != nullptr, LLIE_E_STATE, "dce_forward: call llie_dce_set_weights first");
-  DceTcPack& pk = g_packs[ctx];
+  DceTcPack& pk = tc_pack(ctx);
   // row pitch in pixels: kPadL zero columns on the left, and enough zero columns on the right for the
   // last strip's 132-pixel staged rows (a strip's first staged column is < W + kPadL)
   const int wp = w + kPadL + kRowPx + 4;
@@ -326,7 +330,7 @@ int dce_forward_split(llie_ctx* ctx, const float* in, float* out, float* maps, i
 
 // Test hooks: mode bit 0 = also store x4 / x6; bit 1 = run one launch per layer.
 int dce_debug_mode(llie_ctx* ctx, int mode) {
-  DceTcPack& pk = g_packs[ctx];
+  DceTcPack& pk = tc_pack(ctx);
   pk.keep_all = (mode & 1) != 0;
   pk.unfused = (mode & 2) != 0;
   return LLIE_OK;
@@ -334,9 +338,8 @@ int dce_debug_mode(llie_ctx* ctx, int mode) {
 
 // Test hook: activation `which` (1..6) of frame `frame` from the last bf16 forward, as fp32 [32][h][w].
 int dce_debug_activation(llie_ctx* ctx, int which, int frame, float* host_out) {
-  auto it = g_packs.find(ctx);
-  LLIE_REQUIRE(it != g_packs.end() && it->second.act[0], LLIE_E_STATE, "no bf16 forward has run on this ctx");
-  DceTcPack& pk = it->second;
+  LLIE_REQUIRE(ctx->tc && ctx->tc->act[0], LLIE_E_STATE, "no bf16 forward has run on this ctx");
+  DceTcPack& pk = *ctx->tc;
   LLIE_REQUIRE(which >= 1 && which <= 6 && frame >= 0 && frame < pk.n && host_out, LLIE_E_ARG, "bad activation query");
   const int planes = pk.split ? 8 : 4;
   const size_t per = (size_t)pk.h * planes * pk.wp * 8;

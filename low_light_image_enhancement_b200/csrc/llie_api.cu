@@ -17,6 +17,8 @@ void set_error(const char* fmt, ...) {
   va_end(ap);
 }
 
+const char* last_error_text() { return g_err; }
+
 // RAII device switch so that a ctx can be driven from a thread whose current device differs.
 struct DeviceGuard {
   int prev = -1;
@@ -74,6 +76,38 @@ size_t llie_ctx::workspace_total() const {
   return t;
 }
 
+static void msrcr_defaults(llie_msrcr_params* d) {
+  memset(d, 0, sizeof(*d));
+  d->struct_size = sizeof(*d);
+  d->n_scales = 3;
+  d->sigma[0] = 15.f; d->sigma[1] = 80.f; d->sigma[2] = 250.f;
+  for (int i = 0; i < 3; ++i) d->weight[i] = 1.0f / 3.0f;
+  d->truncate = 4.0f;
+  d->alpha = 125.f; d->beta = 46.f; d->gain = 0.6f; d->offset = 128.f;
+  d->in_scale = 255.f; d->in_bias = 1.f;
+  d->blur = LLIE_BLUR_PYRAMID;
+  d->finish = LLIE_FINISH_NONE;
+  d->finish_k = 2.0f;
+}
+
+// Size of the first published layout of llie_msrcr_params (through `blur`); `finish` / `finish_k` came later.
+static constexpr size_t kMsrcrParamsV1 = offsetof(llie_msrcr_params, finish);
+
+namespace llie {
+// Copies the caller's struct (struct_size bytes: the v1 layout without finish / finish_k, or the current one) into
+// a full one; fields the caller's layout does not have keep their defaults.
+int msrcr_params_normalise(const llie_msrcr_params* p, llie_msrcr_params* full) {
+  LLIE_REQUIRE(p, LLIE_E_ARG, "null params");
+  const uint32_t sz = p->struct_size;
+  LLIE_REQUIRE(sz >= kMsrcrParamsV1 && sz <= sizeof(*p), LLIE_E_ARG, "llie_msrcr_params.struct_size %u is not in [%zu, %zu]",
+               sz, kMsrcrParamsV1, sizeof(*p));
+  msrcr_defaults(full);
+  memcpy(full, p, sz);
+  full->struct_size = sizeof(*full);
+  return LLIE_OK;
+}
+}  // namespace llie
+
 extern "C" {
 
 int llie_version(void) { return LLIE_VERSION; }
@@ -94,25 +128,26 @@ int llie_device_count(int* count) {
   return LLIE_OK;
 }
 
+// The structs are versioned by their leading struct_size: the CALLER states how many bytes its
+// struct has, and the library never writes or reads beyond that.
 int llie_msrcr_default_params(llie_msrcr_params* p) {
   LLIE_REQUIRE(p, LLIE_E_ARG, "null params");
-  memset(p, 0, sizeof(*p));
-  p->struct_size = sizeof(*p);
-  p->n_scales = 3;
-  p->sigma[0] = 15.f; p->sigma[1] = 80.f; p->sigma[2] = 250.f;
-  for (int i = 0; i < 3; ++i) p->weight[i] = 1.0f / 3.0f;
-  p->truncate = 4.0f;
-  p->alpha = 125.f; p->beta = 46.f; p->gain = 0.6f; p->offset = 128.f;
-  p->in_scale = 255.f; p->in_bias = 1.f;
-  p->blur = LLIE_BLUR_PYRAMID;
-  p->finish = LLIE_FINISH_NONE;
-  p->finish_k = 2.0f;
+  const uint32_t sz = p->struct_size;
+  LLIE_REQUIRE(sz >= kMsrcrParamsV1 && sz <= sizeof(*p), LLIE_E_ARG,
+               "llie_msrcr_params.struct_size %u: set it to sizeof(llie_msrcr_params) (%zu; at least %zu) before the call",
+               sz, sizeof(*p), kMsrcrParamsV1);
+  llie_msrcr_params d;
+  msrcr_defaults(&d);
+  d.struct_size = sz;
+  memcpy(p, &d, sz);
   return LLIE_OK;
 }
 
 int llie_dce_default_params(llie_dce_params* p) {
   LLIE_REQUIRE(p, LLIE_E_ARG, "null params");
-  p->struct_size = sizeof(*p);
+  LLIE_REQUIRE(p->struct_size == sizeof(*p), LLIE_E_ARG,
+               "llie_dce_params.struct_size %u: set it to sizeof(llie_dce_params) (%zu) before the call", p->struct_size,
+               sizeof(*p));
   p->iters = 8;
   p->curve_sign = 1;
   p->precision = LLIE_F32;
@@ -148,8 +183,11 @@ int llie_create(llie_ctx** out, int device) {
 
 int llie_destroy(llie_ctx* ctx) {
   if (!ctx) return LLIE_OK;
+  delete ctx->worker;  // joins the ctx's host thread (it is idle: calls are synchronous)
+  ctx->worker = nullptr;
   DeviceGuard g(ctx->device);
   cudaDeviceSynchronize();
+  sharded_release(ctx);
   for (auto& kv : ctx->bufs) cudaFree(kv.second.first);
   msrcr_plan_free(ctx->plan);
   dce_weights_free(ctx->dce);
@@ -225,8 +263,6 @@ int llie_profile_end(llie_ctx* ctx, char* buf, size_t buflen) {
 
 static int check_msrcr_params(const llie_msrcr_params* p) {
   LLIE_REQUIRE(p, LLIE_E_ARG, "null params");
-  LLIE_REQUIRE(p->struct_size == sizeof(llie_msrcr_params), LLIE_E_ARG, "llie_msrcr_params.struct_size %u != %zu",
-               p->struct_size, sizeof(llie_msrcr_params));
   LLIE_REQUIRE(p->n_scales >= 1 && p->n_scales <= LLIE_MAX_SCALES, LLIE_E_ARG, "n_scales %d out of range", p->n_scales);
   for (int s = 0; s < p->n_scales; ++s)
     LLIE_REQUIRE(p->sigma[s] > 0.f && p->sigma[s] <= 4096.f, LLIE_E_ARG, "sigma[%d]=%g out of range", s, p->sigma[s]);
@@ -247,6 +283,9 @@ int llie_msrcr_f32(llie_ctx* ctx, const float* in, float* out, int n, int h, int
                    const llie_msrcr_params* params, void* stream) {
   LLIE_REQUIRE(ctx, LLIE_E_ARG, "null ctx");
   LLIE_TRY(check_batch(in, out, n, h, w, layout));
+  llie_msrcr_params full;
+  LLIE_TRY(msrcr_params_normalise(params, &full));
+  params = &full;
   LLIE_TRY(check_msrcr_params(params));
   if (n == 0) return LLIE_OK;
   DeviceGuard g(ctx->device);
@@ -263,6 +302,9 @@ static int msrcr_int(llie_ctx* ctx, const void* in, void* out, int iot, int n, i
                      const llie_msrcr_params* params, void* stream) {
   LLIE_REQUIRE(ctx, LLIE_E_ARG, "null ctx");
   LLIE_TRY(check_batch(in, out, n, h, w, layout));
+  llie_msrcr_params full;
+  LLIE_TRY(msrcr_params_normalise(params, &full));
+  params = &full;
   LLIE_TRY(check_msrcr_params(params));
   LLIE_REQUIRE(params->blur == LLIE_BLUR_PYRAMID, LLIE_E_DTYPE, "integer images are supported by the pyramid blur only");
   LLIE_REQUIRE(params->finish == LLIE_FINISH_NONE, LLIE_E_DTYPE, "global-statistics finishers need fp32 images");

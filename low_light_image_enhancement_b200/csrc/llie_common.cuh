@@ -6,11 +6,15 @@
 #include <cuda_runtime.h>
 #include <cuda_bf16.h>
 
+#include <condition_variable>
 #include <cstdarg>
 #include <cstdint>
 #include <cstdio>
+#include <functional>
 #include <map>
+#include <mutex>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "../../include/llie.h"
@@ -57,8 +61,61 @@ inline ImgView make_view(int layout, int c, int h, int w) {
   return v;
 }
 
+// One persistent host thread per ctx for the multi-device entry points (llie_enhance_sharded, llie_msrcr_tiled):
+// the ~15-25 launches and copies a device needs per call must be issued concurrently with the other devices',
+// and spawning a std::thread per call costs more than a whole 8-GPU tiled step.  Jobs run one at a time.
+class HostWorker {
+ public:
+  HostWorker() : th_([this] { loop(); }) {}
+  ~HostWorker() {
+    {
+      std::lock_guard<std::mutex> lk(mu_);
+      quit_ = true;
+    }
+    cv_.notify_all();
+    th_.join();
+  }
+  void post(std::function<void()> job) {
+    {
+      std::lock_guard<std::mutex> lk(mu_);
+      job_ = std::move(job);
+      pending_ = true;
+      done_ = false;
+    }
+    cv_.notify_all();
+  }
+  void wait() {
+    std::unique_lock<std::mutex> lk(mu_);
+    cv_.wait(lk, [this] { return done_; });
+  }
+
+ private:
+  void loop() {
+    std::unique_lock<std::mutex> lk(mu_);
+    for (;;) {
+      cv_.wait(lk, [this] { return pending_ || quit_; });
+      if (quit_) return;
+      std::function<void()> job = std::move(job_);
+      pending_ = false;
+      lk.unlock();
+      job();
+      lk.lock();
+      done_ = true;
+      cv_.notify_all();
+    }
+  }
+  std::mutex mu_;
+  std::condition_variable cv_;
+  std::function<void()> job_;
+  bool pending_ = false, done_ = true, quit_ = false;
+  std::thread th_;  // last member: the thread starts after everything above is constructed
+};
+
+const char* last_error_text();  // this thread's llie_last_error() text (llie_api.cu)
+
 struct MsrcrPlan;   // msrcr_pyramid.cu
 struct DceWeights;  // dce_weights.cu
+struct DceTcPack;   // dce_tc.cu: packed weight tiles and activation workspace geometry of the tensor-core path
 
 }  // namespace llie
 
@@ -70,6 +127,7 @@ struct llie_ctx {
   std::map<std::string, std::pair<void*, size_t>> bufs;  // named workspaces, grown on demand
   llie::MsrcrPlan* plan = nullptr;
   llie::DceWeights* dce = nullptr;
+  llie::DceTcPack* tc = nullptr;
   // optional per-kernel timing (llie_profile_begin/end): one event pair per launch
   bool profiling = false;
   struct ProfRec { const char* name; cudaEvent_t e0, e1; };
@@ -78,6 +136,14 @@ struct llie_ctx {
   cudaEvent_t tile_event = nullptr;  // "my level-C rows are ready" (row-tiled MSRCR)
   cudaEvent_t tile_t0 = nullptr, tile_t1 = nullptr;  // device-side span of this shard in the last tiled call
   float tile_ms = -1.f;
+  llie::HostWorker* worker = nullptr;  // created on first multi-device use
+  // batch sharder (llie_enhance_sharded): copy streams, per-slot events, pinned stages, last device-side span
+  cudaStream_t sh_h2d = nullptr, sh_d2h = nullptr;
+  cudaEvent_t sh_ev[3][3] = {{nullptr, nullptr, nullptr}, {nullptr, nullptr, nullptr}, {nullptr, nullptr, nullptr}};
+  cudaEvent_t sh_t0 = nullptr, sh_t1 = nullptr;
+  void* sh_pin[2][3] = {{nullptr, nullptr, nullptr}, {nullptr, nullptr, nullptr}};
+  size_t sh_pin_bytes[2][3] = {{0, 0, 0}, {0, 0, 0}};
+  float shard_ms = -1.f;
 
   // Returns a device buffer of at least `bytes` under `name`; reallocates only when growing.
   int workspace(const char* name, size_t bytes, void** out);
@@ -145,6 +211,13 @@ int msrcr_plan_detail(float sigma, float truncate, double* l1, double* edge, dou
 void msrcr_plan_free(MsrcrPlan* p);
 int msrcr_tiled_run(llie_ctx* const* ctxs, int n_dev, const float* const* in, float* const* out, const int* row0,
                     const int* rows, int H, int W, const llie_msrcr_params& p);
+
+int msrcr_params_normalise(const llie_msrcr_params* p, llie_msrcr_params* full);  // llie_api.cu
+inline HostWorker* ctx_worker(llie_ctx* ctx) {
+  if (!ctx->worker) ctx->worker = new HostWorker;
+  return ctx->worker;
+}
+void sharded_release(llie_ctx* ctx);  // llie_sharded.cu
 
 int dce_weights_upload(llie_ctx* ctx, const float* host_packed, size_t count);
 void dce_weights_free(DceWeights* w);

@@ -13,8 +13,9 @@ extern "C" int llie_msrcr_tiled(llie_ctx* const* ctxs, int n_dev, const float* c
                                 const int* row0, const int* rows, int h_total, int w, const llie_msrcr_params* params) {
   LLIE_REQUIRE(ctxs && in_shard && out_shard && row0 && rows && params, LLIE_E_ARG, "null argument");
   LLIE_REQUIRE(n_dev >= 1 && n_dev <= 64, LLIE_E_ARG, "n_dev %d out of range [1,64]", n_dev);
-  LLIE_REQUIRE(params->struct_size == sizeof(llie_msrcr_params), LLIE_E_ARG, "llie_msrcr_params.struct_size %u != %zu",
-               params->struct_size, sizeof(llie_msrcr_params));
+  llie_msrcr_params full;
+  LLIE_TRY(msrcr_params_normalise(params, &full));
+  params = &full;
   LLIE_REQUIRE(params->blur == LLIE_BLUR_PYRAMID, LLIE_E_ARG, "row-tiled MSRCR uses the pyramid blur only");
   LLIE_REQUIRE(params->finish != LLIE_FINISH_PERCENTILE, LLIE_E_ARG,
                "row-tiled MSRCR supports the minmax and meanstd finishers only (no cross-device radix select)");

@@ -39,8 +39,54 @@ def test_version_and_defaults(lib_built):
     assert d["alpha"] == 125.0 and d["beta"] == 46.0 and abs(d["gain"] - 0.6) < 1e-7 and d["offset"] == 128.0
     assert L.default_dce_params()["iters"] == 8
     p = _lib.DceParams()
+    p.struct_size = C.sizeof(_lib.DceParams)
     _lib.check(lib_built.llie_dce_default_params(C.byref(p)))
     assert (p.struct_size, p.iters, p.curve_sign) == (C.sizeof(_lib.DceParams), 8, 1)
+
+
+def _integration_blocks():
+    src = open(os.path.join(ROOT, "INTEGRATION.md")).read()
+    sec = src[src.index("## 3. The ctypes stub"):src.index("## 4. The operator")]
+    return re.findall(r"```python\n(.*?)```", sec, flags=re.S)
+
+
+def test_integration_stub_runs_verbatim(lib_built):
+    """the documented stub stopped at `blur` (104 bytes) while the library memset all 112.  Execute the
+    first block of INTEGRATION.md section 3 as it stands (binding + default parameters; needs no GPU)."""
+    blocks = _integration_blocks()
+    assert len(blocks) == 2
+    ns = {}
+    cwd = os.getcwd()
+    os.chdir(ROOT)
+    try:
+        exec(compile(blocks[0], "INTEGRATION.md#3a", "exec"), ns)
+    finally:
+        os.chdir(cwd)
+    P, p = ns["MsrcrParams"], ns["p"]
+    assert C.sizeof(P) == C.sizeof(_lib.MsrcrParams) == 112
+    assert [f[0] for f in P._fields_] == [f[0] for f in _lib.MsrcrParams._fields_]
+    assert p.n_scales == 3 and tuple(p.sigma[:3]) == (15.0, 80.0, 250.0) and p.finish == 0 and p.finish_k == 2.0
+
+
+def test_default_params_honour_the_callers_struct_size(lib_built):
+    """The library writes min(struct_size, sizeof) bytes and rejects sizes it does not know (0 included)."""
+    class V1(C.Structure):   # the first published layout: through `blur`, 104 bytes
+        _fields_ = _lib.MsrcrParams._fields_[:-2] + [("guard", C.c_uint8 * 16)]
+    v1 = V1()
+    C.memset(C.byref(v1), 0xAB, C.sizeof(V1))
+    v1.struct_size = 104
+    fn = lib_built.llie_msrcr_default_params
+    assert fn(C.cast(C.byref(v1), C.POINTER(_lib.MsrcrParams))) == 0
+    assert v1.struct_size == 104 and v1.n_scales == 3 and v1.blur == 0 and abs(v1.gain - 0.6) < 1e-7
+    assert bytes(v1.guard) == b"\xab" * 16          # nothing written beyond the caller's 104 bytes
+    for bad in (0, 4, 103, 113, 4096):
+        q = _lib.MsrcrParams()
+        q.struct_size = bad
+        assert fn(C.byref(q)) == _lib.E_ARG, bad
+    d = _lib.DceParams()
+    assert lib_built.llie_dce_default_params(C.byref(d)) == _lib.E_ARG     # struct_size 0
+    d.struct_size = C.sizeof(_lib.DceParams)
+    assert lib_built.llie_dce_default_params(C.byref(d)) == 0 and d.iters == 8
 
 
 def test_struct_sizes_match_header_layout():

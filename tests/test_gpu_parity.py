@@ -683,3 +683,135 @@ def test_msrcr_tiled_real_devices_peer_copies():
             outs = L.msrcr_tiled(shards, prm)
             y = np.concatenate([o.cpu().numpy() for o in outs], 0)
             assert np.abs(y - ref).max() <= 2e-6, (finish, rep)
+
+
+# ---------------------------------------------------------------- batch sharder
+def _frames(n, h, w, dtype, seed=40):
+    xs = np.stack([oracle.synth_lowlight(h, w, seed + i) * (1.0 + i) for i in range(n)]).clip(0, 1).astype(np.float32)
+    if dtype == np.uint8:
+        return oracle.to_u8(xs)
+    return xs
+
+
+@pytest.mark.parametrize("method,dtype,parts", [("msrcr", np.float32, 3), ("msrcr", np.uint8, 2), ("zero_dce", np.float32, 4),
+                                                 ("zero_dce", np.uint8, 2)])
+def test_enhance_sharded_resident_equals_enhance(method, dtype, parts, blob):
+    """One C call drives `parts` ctxs (virtual devices on one GPU): every shard equals enhance() of it, bitwise."""
+    prm = dict(weights=blob, precision="bf16") if method == "zero_dce" else {}
+    xs = torch.from_numpy(_frames(7, 130, 212, dtype)).cuda()
+    sl = [L.shard_slice(7, d, parts) for d in range(parts)]
+    shards = [xs[s].contiguous() for s in sl]
+    outs = L.enhance(shards, method, prm, devices=[0] * parts)
+    assert len(outs) == parts
+    ref = L.enhance(xs, method, prm)
+    for s, y in zip(sl, outs):
+        assert y.dtype == xs.dtype and torch.equal(y, ref[s])
+    ms = L.shard_last_ms([0] * parts)
+    assert len(ms) == parts and all(m > 0 for m in ms)
+
+
+@pytest.mark.parametrize("pinned", [False, True])
+@pytest.mark.parametrize("method", ["msrcr", "zero_dce"])
+def test_enhance_sharded_host_equals_enhance(method, pinned, blob):
+    """Host batches: split over the device slots, streamed through three staging slots per device inside one C call."""
+    prm = dict(weights=blob, precision="bf16") if method == "zero_dce" else {}
+    x = torch.from_numpy(_frames(11, 96, 160, np.float32))
+    if pinned:
+        x = x.pin_memory()
+        out = torch.empty_like(x).pin_memory()
+        y = L.enhance(x, method, prm, devices=[0, 0, 0], out=out)
+        assert y.data_ptr() == out.data_ptr()
+    else:
+        y = L.enhance(x.numpy(), method, prm, devices=[0, 0])
+        assert isinstance(y, np.ndarray)
+        y = torch.from_numpy(y)
+    ref = L.enhance(x.cuda(), method, prm).cpu()
+    assert torch.equal(y, ref)
+
+
+def test_enhance_sharded_many_chunks_and_empty_shards():
+    """More chunks than staging slots (slot reuse ordered by events), and more device slots than frames."""
+    x = _frames(2, 1100, 1900, np.float32)          # 25 MB per frame: 48 MiB chunks hold one frame each
+    xs = np.concatenate([x] * 4)                     # 8 frames -> 4 per slot -> 4 chunks through 3 slots
+    y = L.enhance(xs, "msrcr", devices=[0, 0])
+    ref = L.enhance(torch.from_numpy(x).cuda(), "msrcr").cpu().numpy()
+    for i in range(8):
+        assert np.array_equal(y[i], ref[i % 2]), i
+    y = L.enhance(x, "msrcr", devices=[0, 0, 0, 0])  # two of the four slots get no frame
+    assert np.array_equal(y, ref)
+
+
+def test_enhance_sharded_errors(blob):
+    x = _frames(4, 64, 96, np.float32)
+    with pytest.raises(ValueError):
+        L.enhance(torch.from_numpy(x).cuda(), "msrcr", devices=[0, 0])      # one CUDA tensor cannot be split
+    with pytest.raises(ValueError):
+        L.enhance(x, "zero_dce", dict(weights=blob, return_maps=True), devices=[0, 0])
+    with pytest.raises(L.LlieError):
+        L.enhance(x, "msrcr", dict(sigmas=(3.0,), weights=(1.0,)), devices=[0, 0])   # the worker's error reaches the caller
+    with pytest.raises(TypeError):
+        L.enhance([torch.from_numpy(x)], "msrcr")
+
+
+def test_enhance_sharded_real_devices(blob):
+    g = torch.cuda.device_count()
+    if g < 2:
+        pytest.skip("needs at least 2 GPUs")
+    g = min(g, 8)
+    x = _frames(2 * g + 1, 270, 480, np.float32)
+    for method, prm in (("msrcr", {}), ("zero_dce", dict(weights=blob, precision="bf16"))):
+        ref = L.enhance(torch.from_numpy(x).cuda(0), method, prm).cpu().numpy()
+        y = L.enhance(x, method, prm, devices=list(range(g)))
+        assert np.array_equal(y, ref), method
+        sl = [L.shard_slice(len(x), d, g) for d in range(g)]
+        outs = L.enhance([torch.from_numpy(x[s]).cuda(d) for d, s in enumerate(sl)], method, prm)
+        assert all(o.device.index == d for d, o in enumerate(outs))
+        assert np.array_equal(np.concatenate([o.cpu().numpy() for o in outs]), ref), method
+
+
+def test_two_threads_two_ctxs_zero_dce(blob):
+    """the tensor-core path kept its per-ctx state in an unguarded process-wide map.  It now lives in
+    the ctx; two host threads, each with its own Enhancer, run Zero-DCE concurrently (ctypes releases the GIL)."""
+    import threading
+    x = torch.from_numpy(_frames(3, 120, 200, np.float32)).cuda()
+    ref = L.enhance(x, "zero_dce", dict(weights=blob, precision="bf16"))
+    errs = []
+
+    def work(seed):
+        try:
+            e = L.Enhancer(0)
+            w = oracle.pack_weights(oracle.init_weights(0))
+            st = torch.cuda.Stream()
+            with torch.cuda.stream(st):
+                for _ in range(20):
+                    y = e.enhance(x, "zero_dce", dict(weights=w, precision="bf16"))
+                    st.synchronize()
+                    if not torch.equal(y, ref):
+                        errs.append("mismatch")
+            e.close()
+        except Exception as ex:  # noqa: BLE001
+            errs.append(repr(ex))
+
+    th = [threading.Thread(target=work, args=(i,)) for i in range(2)]
+    [t.start() for t in th]
+    [t.join() for t in th]
+    assert not errs, errs[:3]
+
+
+def test_integration_stub_gpu_call():
+    """INTEGRATION.md section 3, both code blocks, executed as they stand."""
+    import re
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    src = open(os.path.join(root, "INTEGRATION.md")).read()
+    sec = src[src.index("## 3. The ctypes stub"):src.index("## 4. The operator")]
+    blocks = re.findall(r"```python\n(.*?)```", sec, flags=re.S)
+    ns = {}
+    cwd = os.getcwd()
+    os.chdir(root)
+    try:
+        for i, b in enumerate(blocks):
+            exec(compile(b, f"INTEGRATION.md#3.{i}", "exec"), ns)
+    finally:
+        os.chdir(cwd)
+    x, y = ns["x"], ns["y"]
+    assert float((y - L.enhance(x, "msrcr")).abs().max()) == 0.0
