@@ -25,6 +25,7 @@ repository holds no code: /root/reference/README.md:1-2) on the host cores inste
 from __future__ import annotations
 
 import argparse
+import datetime
 import json
 import os
 import sys
@@ -34,6 +35,12 @@ import time
 ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
+
+# torch.distributed.run exports OMP_NUM_THREADS=1 to its workers, which would put the CPU oracle legs (BLAS, the
+# scipy.fft pool) on one thread: set the thread count explicitly, before NumPy loads its BLAS.
+CPU_THREADS = os.cpu_count() or 1
+for _v in ("OMP_NUM_THREADS", "OPENBLAS_NUM_THREADS", "MKL_NUM_THREADS"):
+    os.environ[_v] = str(CPU_THREADS)
 
 import numpy as np  # noqa: E402
 
@@ -63,18 +70,43 @@ MSRCR_KERNEL_BYTES_PER_PX_U8 = {"down4_rows_kernel": 3 + 3.0, "msrcr_final_kerne
 MSRCR_NORTH_STAR_BYTES_PER_PX_U8 = 3 + 36 + 36 + 3 + 3   # the same two-pass data flow with uint8 image I/O
 
 
-# DRAM bytes per pixel (dram__bytes_read.sum + dram__bytes_write.sum) of each kernel from the committed
-# `ncu --set full` captures: profiles/r01_ncu_full_dce_chain_16x1080p.md (16 x 1080p) and
-# profiles/r01_ncu_full_msrcr_8x4k_v2.md (8 x 4K).  `roofline.traffic` = this x the pixels one launch processes.
-NCU_DRAM_BYTES_PER_PX = {"dce_chain_c123_kernel": 6.92e9 / (16 * 1920 * 1080), "dce_chain_c45_kernel": 4.40e9 / (16 * 1920 * 1080),
-                         "dce_chain_c67_kernel": 7.70e9 / (16 * 1920 * 1080), "msrcr_final_kernel": 1750.8e6 / (8 * 3840 * 2160),
-                         "down4_rows_kernel": 1077.9e6 / (8 * 3840 * 2160)}
-MSRCR_NCU_DRAM_BYTES_PER_PX = 3310.9e6 / (8 * 3840 * 2160)   # all 15 launches of one MSRCR call: 49.9 B/px
+def csrc_hash():
+    """Stamp of the kernel sources this build was made from (the GPU box has no .git): sha256 over csrc/*.cu*."""
+    import hashlib
+    d = os.path.join(ROOT, "low_light_image_enhancement_b200", "csrc")
+    hsh = hashlib.sha256()
+    for f in sorted(os.listdir(d)):
+        if f.endswith((".cu", ".cuh")):
+            hsh.update(f.encode())
+            hsh.update(open(os.path.join(d, f), "rb").read())
+    return hsh.hexdigest()[:16]
+
+
+_TRAFFIC = None
+
+
+def load_traffic():
+    """profiles/ncu_traffic.json: DRAM bytes per pixel (dram__bytes_read.sum + dram__bytes_write.sum) of every
+    kernel from one `ncu --set full` capture, written by tools/ncu_traffic.py together with the hash of the kernel
+    sources it was captured from.  `roofline.traffic` comes from here and says whether the stamp matches this build."""
+    global _TRAFFIC
+    if _TRAFFIC is None:
+        p = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+        _TRAFFIC = json.load(open(p)) if os.path.exists(p) else {"kernels": {}, "source_hash": None, "capture": None}
+        _TRAFFIC["stale"] = _TRAFFIC.get("source_hash") != csrc_hash()
+    return _TRAFFIC
 
 
 def ncu_traffic(kernel, px_per_step, steps, launches, io="f32"):
-    b = NCU_DRAM_BYTES_PER_PX.get(kernel)
-    return None if b is None or io != "f32" else int(b * px_per_step * steps / max(launches, 1))
+    t = load_traffic()
+    b = t["kernels"].get(kernel if io == "f32" else kernel + ":" + io)
+    return None if b is None else int(b * px_per_step * steps / max(launches, 1))
+
+
+def traffic_source():
+    t = load_traffic()
+    return {"file": "profiles/ncu_traffic.json", "capture": t.get("capture"), "source_hash": t.get("source_hash"),
+            "matches_this_build": not t["stale"]}
 
 
 def load_peaks():
@@ -246,7 +278,8 @@ def tc_roofline(prof, px_per_step, steps, peaks, split=False):
     chain = (3 if split else 1) * DCE_TENSOR_FLOP_PER_PX * px_per_step * steps / (chain_ms * 1e-3) / 1e12
     peak = peaks["tc_sustained"]
     return {"bound": "tensor", "kernel": dom, "achieved": round(ach, 2), "peak": peak, "unit": "TFLOP/s",
-            "frac": round(ach / peak, 4), "traffic": ncu_traffic(dom, px_per_step, steps, tc[dom][0]), "peak_source": f"{peaks['source']} bf16 sustained",
+            "frac": round(ach / peak, 4), "traffic": ncu_traffic(dom, px_per_step, steps, tc[dom][0]), "traffic_source": traffic_source(),
+            "peak_source": f"{peaks['source']} bf16 sustained",
             "launches": tc[dom][0], "avg_launch_ms": round(tc[dom][1] / tc[dom][0], 4),
             "conv2to7_chain": {"achieved": round(chain, 2), "frac": round(chain / peak, 4),
                                "frac_of_burst": round(chain / peaks["tc_burst"], 4)},
@@ -256,27 +289,59 @@ def tc_roofline(prof, px_per_step, steps, peaks, split=False):
 
 
 def hbm_roofline(prof, px_per_step, steps, peaks, total_ms_per_step, u8=False):
+    """Dominant kernel against its own algorithmic bytes, and the whole step (a) at the DRAM bytes ncu measured for
+    it and (b) at the one-touch lower bound (image read once + written once)."""
     kbytes = MSRCR_KERNEL_BYTES_PER_PX_U8 if u8 else MSRCR_KERNEL_BYTES_PER_PX
-    ns_bytes = MSRCR_NORTH_STAR_BYTES_PER_PX_U8 if u8 else MSRCR_NORTH_STAR_BYTES_PER_PX
     cand = {k: v for k, v in prof.items() if k in kbytes}
     if not cand:
         return None
     dom = max(cand, key=lambda k: cand[k][1])
     cnt, ms = cand[dom]
     ach = kbytes[dom] * px_per_step * steps / (ms * 1e-3) / 1e9
-    ns = ns_bytes * px_per_step / (total_ms_per_step * 1e-3) / 1e9
+    step_s = total_ms_per_step * 1e-3
+    bound_b = 6 if u8 else 24
+    whole = {"at_one_touch_bound": {"bytes_per_px": bound_b, "achieved": round(bound_b * px_per_step / step_s / 1e9, 1),
+                                    "frac": round(bound_b * px_per_step / step_s / 1e9 / peaks["hbm"], 4)}}
+    meas = load_traffic().get("msrcr_step_bytes_per_px_u8" if u8 else "msrcr_step_bytes_per_px")
+    if meas:
+        whole["at_measured_dram_bytes"] = {"bytes_per_px": round(meas, 2), "achieved": round(meas * px_per_step / step_s / 1e9, 1),
+                                           "frac": round(meas * px_per_step / step_s / 1e9 / peaks["hbm"], 4)}
     return {"bound": "hbm", "kernel": dom, "achieved": round(ach, 1), "peak": peaks["hbm"], "unit": "GB/s",
             "frac": round(ach / peaks["hbm"], 4), "traffic": ncu_traffic(dom, px_per_step, steps, cnt, "u8" if u8 else "f32"),
-            "peak_source": f"{peaks['source']} copy",
-            **({} if u8 else {"whole_msrcr_at_ncu_dram_bytes": {
-                "bytes_per_px": round(MSRCR_NCU_DRAM_BYTES_PER_PX, 1),
-                "achieved": round(MSRCR_NCU_DRAM_BYTES_PER_PX * px_per_step / (total_ms_per_step * 1e-3) / 1e9, 1),
-                "frac": round(MSRCR_NCU_DRAM_BYTES_PER_PX * px_per_step / (total_ms_per_step * 1e-3) / 1e9 / peaks["hbm"], 4),
-                "note": "the cascade moves ~50 B/px through DRAM (ncu), not the 108 B/px of the two-pass data flow"}}),
-            "kernel_bytes_per_px": kbytes[dom],
-            "launches": cnt, "avg_launch_ms": round(ms / cnt, 4),
-            f"whole_msrcr_at_{ns_bytes}B_per_px": {"achieved": round(ns, 1), "frac": round(ns / peaks["hbm"], 4)},
+            "traffic_source": traffic_source(), "peak_source": f"{peaks['source']} copy",
+            "kernel_bytes_per_px": kbytes[dom], "launches": cnt, "avg_launch_ms": round(ms / cnt, 4),
+            "whole_step": whole,
             "kernel_ms_per_step": {k: round(v[1] / steps, 4) for k, v in sorted(prof.items())}}
+
+
+def link_ceiling(dist, mib=256, iters=6):
+    """What the host link gives this job with NO kernels: every rank copies `mib` MiB host -> device and `mib` MiB
+    device -> host at the same time (pinned memory, two streams), `iters` times.  Returns aggregate GB/s per
+    direction over all ranks -- the ceiling any end-to-end figure of this box is measured against."""
+    torch = dist.torch
+    n = mib << 20
+    hp_in = torch.empty(n, dtype=torch.uint8, pin_memory=True)
+    hp_out = torch.empty(n, dtype=torch.uint8, pin_memory=True)
+    d_in = torch.empty(n, dtype=torch.uint8, device=dist.device)
+    d_out = torch.zeros(n, dtype=torch.uint8, device=dist.device)
+    s1, s2 = torch.cuda.Stream(dist.device), torch.cuda.Stream(dist.device)
+
+    def go(k):
+        for _ in range(k):
+            with torch.cuda.stream(s1):
+                d_in.copy_(hp_in, non_blocking=True)
+            with torch.cuda.stream(s2):
+                hp_out.copy_(d_out, non_blocking=True)
+        s1.synchronize()
+        s2.synchronize()
+    go(2)
+    dist.barrier()
+    t0 = time.perf_counter()
+    go(iters)
+    dt = time.perf_counter() - t0
+    dist.barrier()
+    dt = dist.reduce(dt, "max")
+    return round(dist.world * n * iters / dt / 1e9, 2)
 
 
 def gpu_workload(dist, name, steps, warmup, peaks, with_e2e=True, with_cpu=True, io="f32"):
@@ -334,10 +399,15 @@ def gpu_workload(dist, name, steps, warmup, peaks, with_e2e=True, with_cpu=True,
         yh = torch.empty(x.shape, dtype=x.dtype, pin_memory=True)
         e2e_steps = max(1, min(steps, 5))
         ms_e = run_e2e(dist, lambda: enh.enhance(xh, method, params, out=yh), e2e_steps, warmup)
+        bytes_dir = int(xh.numel() * xh.element_size() * world)
+        ceil = link_ceiling(dist)
         res["e2e"] = {"value": round(px_total / ms_e / 1e3, 1), "unit": "Mpixel/s", "ms_per_step": round(ms_e, 3),
-                      "h2d_bytes_per_step": int(xh.numel() * xh.element_size() * world),
-                      "d2h_bytes_per_step": int(yh.numel() * yh.element_size() * world),
-                      "steps": e2e_steps, "api": "enhance(pinned torch CPU tensor, out=pinned) -> staged 3-stream pipeline"}
+                      "h2d_bytes_per_step": bytes_dir, "d2h_bytes_per_step": bytes_dir,
+                      "steps": e2e_steps, "api": "enhance(pinned torch CPU tensor, out=pinned) -> staged 3-stream pipeline",
+                      "link_gbs_per_direction": round(bytes_dir / ms_e / 1e6, 2), "link_ceiling_gbs": ceil,
+                      "frac_of_link": round(bytes_dir / ms_e / 1e6 / ceil, 4),
+                      "link_ceiling_how": f"{world} rank(s) x 256 MiB pinned H2D + D2H at once, plain copies, no kernels; aggregate per direction",
+                      "device_resident_ms_per_step": round(ms, 3)}
         if not torch.equal(yh, y.cpu()):
             res["e2e"]["warning"] = "host-path result differs from device-path result"
         if io == "u8":   # the same frames one by one through the streaming front-end
@@ -361,10 +431,23 @@ def gpu_workload(dist, name, steps, warmup, peaks, with_e2e=True, with_cpu=True,
     return res
 
 
-def c4_workload(dist, steps, warmup, peaks):
+def _c4_windows(H, W, parts, win=128):
+    """four corners, mid-edges, one interior window and a window straddling every seam row --
+    the shard boundaries of THIS run and the rows 2048 k of the 8-GPU partition."""
+    wins = [(0, 0), (0, W - win), (H - win, 0), (H - win, W - win), (0, W // 2), (H // 2, 0), (H // 2 - 37, W - win),
+            (H - win, W // 3), (5000, 9000)]
+    seams = sorted({r0 for r0, _ in parts[1:]} | {2048 * k for k in range(1, 8) if 2048 * k < H})
+    for i, r in enumerate(seams):
+        wins.append((r - win // 2, (1237 * (i + 1)) % (W - win)))
+    return wins
+
+
+def c4_workload(dist, steps, warmup, peaks, check=True):
     """BASELINE configs[4]: one 16384 x 16384 image, rows tiled over the N GPUs of this node, image
-    pre-sharded in HBM, halo exchange inside the timed region.  Time per step = max over devices of
-    the device-side span (CUDA events on each shard's stream after a common host barrier)."""
+    pre-sharded in HBM, halo exchange inside the timed region.  Rank 0 drives all N devices through
+    llie_msrcr_tiled.  Two times per step: the host wall clock around the (synchronous) call -- the latency a
+    caller sees, and the headline -- and the max over devices of the device-side span.  The result is compared
+    with the windowed float64 oracle on >= 16 windows including every seam row (outside the timed region)."""
     import torch
     import low_light_image_enhancement_b200 as L
     from low_light_image_enhancement_b200.api import msrcr_tiled_last_ms, _tile_enhancer
@@ -376,6 +459,7 @@ def c4_workload(dist, steps, warmup, peaks):
         from torch.distributed.distributed_c10d import _get_default_store
         store = _get_default_store()
     res = None
+    dist.barrier()
     if rank == 0:
         parts = L.tile_rows(H, world)
         shards, outs = [], []
@@ -385,6 +469,7 @@ def c4_workload(dist, steps, warmup, peaks):
                      for b0 in range(0, r, 2048)]
             shards.append(torch.cat(bands, 0).contiguous())
             outs.append(torch.empty_like(shards[-1]))
+            del bands
         for _ in range(warmup):
             L.msrcr_tiled(shards, outs=outs)
         enh = [_tile_enhancer(d, 0) for d in range(world)]
@@ -397,26 +482,120 @@ def c4_workload(dist, steps, warmup, peaks):
                 wall.append((time.perf_counter() - t0) * 1e3)
                 per_dev.append(msrcr_tiled_last_ms(shards))
         launches = sum(e.launch_count() for e in enh) - l0
-        ms = float(np.mean([max(p) for p in per_dev]))
+        ms_dev = float(np.mean([max(p) for p in per_dev]))
+        ms_wall = float(np.mean(wall))
         px = H * W
-        ach = MSRCR_NORTH_STAR_BYTES_PER_PX * px / (ms * 1e-3) / 1e9
-        ok = all(bool(torch.isfinite(o[::512, ::64]).all()) and 0.0 <= float(o[::512, ::64].min()) for o in outs)
+        parity = None
+        if check:
+            import oracle
+            row0 = [r0 for r0, _ in parts]
+
+            def rows_of(ts, y0, y1, x0, x1):   # rows [y0, y1) x columns [x0, x1) of the sharded image, on the host
+                out = []
+                for d, (r0, r) in enumerate(parts):
+                    lo, hi = max(y0, r0), min(y1, r0 + r)
+                    if lo < hi:
+                        out.append(ts[d][lo - r0:hi - r0, x0:x1].cpu())
+                return torch.cat(out, 0).numpy()
+            worst, worst_at, n_seam = 0.0, None, 0
+            t0 = time.perf_counter()
+            wins = _c4_windows(H, W, parts)
+            for (y0, x0) in wins:
+                cy0, cy1, cx0, cx1 = max(0, y0 - 1000), min(H, y0 + 128 + 1000), max(0, x0 - 1000), min(W, x0 + 128 + 1000)
+                ref = oracle.msrcr(rows_of(shards, cy0, cy1, cx0, cx1))[y0 - cy0:y0 - cy0 + 128, x0 - cx0:x0 - cx0 + 128]
+                got = rows_of(outs, y0, y0 + 128, x0, x0 + 128)
+                d_ = float(np.abs(got.astype(np.float64) - ref).max())
+                n_seam += any(y0 < r < y0 + 128 for r in row0[1:])
+                if d_ >= worst:
+                    worst, worst_at = d_, (y0, x0)
+            parity = {"parity_max_abs": worst, "tolerance": 1e-4, "ok": worst <= 1e-4, "windows": len(wins),
+                      "windows_on_a_seam_of_this_run": int(n_seam), "worst_window_yx": worst_at, "window": "128x128",
+                      "oracle": "float64 NumPy MSRCR on the window's 1000-px-grown crop (SURVEY.md 9.4)",
+                      "oracle_seconds": round(time.perf_counter() - t0, 1)}
         res = {"workload": f"MSRCR sigma=15/80/250, one 16384x16384 image row-tiled over {world} GPU(s) (BASELINE configs[4])",
-               "ms_per_step": round(ms, 4), "value": round(px / ms / 1e3, 1), "scaling": "strong", "dtype": "f32",
+               "ms_per_step": round(ms_wall, 4), "value": round(px / ms_wall / 1e3, 1), "scaling": "strong", "dtype": "f32",
+               "timing": "host wall clock around the synchronous llie_msrcr_tiled call (what a caller waits for)",
+               "device_span_ms_per_step": round(ms_dev, 4), "value_at_device_span": round(px / ms_dev / 1e3, 1),
+               "host_wall_over_device_span": round(ms_wall / ms_dev, 3),
                "frames_total": 1, "frames_this_rank": 1, "clocks": clk.summary(), "gpu_launches": int(launches),
                "l2": "3.2 GB image per step exceeds the 126 MB L2",
-               "host_wall_ms_per_step": round(float(np.mean(wall)), 3),
                "per_device_ms": [round(float(np.mean([p[d] for p in per_dev])), 4) for d in range(world)],
-               "output_sane": ok,
-               "roofline": {"bound": "hbm", "kernel": "whole tiled MSRCR (all devices)", "achieved": round(ach, 1),
-                            "peak": round(peaks["hbm"] * world, 1), "unit": "GB/s", "frac": round(ach / (peaks["hbm"] * world), 4),
+               "parity": parity,
+               "roofline": {"bound": "hbm", "kernel": "whole tiled MSRCR (all devices)",
+                            "achieved": round(24 * px / (ms_wall * 1e-3) / 1e9, 1), "peak": round(peaks["hbm"] * world, 1),
+                            "unit": "GB/s", "frac": round(24 * px / (ms_wall * 1e-3) / 1e9 / (peaks["hbm"] * world), 4),
                             "traffic": None, "peak_source": f"{peaks['source']} copy x {world} GPUs",
-                            "bytes_per_px": MSRCR_NORTH_STAR_BYTES_PER_PX,
+                            "bytes_per_px": 24, "bytes_per_px_is": "one-touch bound: image read once, written once",
                             "exchange": "16 raw rows + level-C (stride-4) rows per neighbour via cudaMemcpyPeerAsync"}}
+        del shards, outs
+        torch.cuda.empty_cache()
         if store is not None:
             store.set("c4_done", "1")
     elif store is not None:
-        store.wait(["c4_done"])
+        store.wait(["c4_done"], datetime.timedelta(seconds=3600))
+    dist.barrier()
+    return res
+
+
+def sharded_one_process(dist, steps, warmup, peaks):
+    """the batch sharder driven from ONE process -- rank 0 calls enhance(..., devices=[0..N-1])
+    (llie_enhance_sharded: one C call, one host thread per device, no exchange) on c3's frames, device-resident and
+    from pinned host memory; the other ranks idle.  Reported beside the one-process-per-GPU numbers."""
+    import torch
+    import low_light_image_enhancement_b200 as L
+    from low_light_image_enhancement_b200.synth import synth_lowlight_batch
+    world, rank = dist.world, dist.rank
+    store = None
+    if world > 1:
+        from torch.distributed.distributed_c10d import _get_default_store
+        store = _get_default_store()
+    res = None
+    dist.barrier()
+    if rank == 0:
+        devs = list(range(world))
+        n_dev_frames = 16
+        xs = [synth_lowlight_batch(8, H4K, W4K, seed=3000 + d, device=torch.device("cuda", d)).repeat(2, 1, 1, 1).contiguous()
+              for d in devs]
+        outs = [torch.empty_like(t) for t in xs]
+        px = world * n_dev_frames * H4K * W4K
+        for _ in range(warmup):
+            L.enhance(xs, "msrcr", out=outs)
+        wall, dev_ms = [], []
+        for _ in range(steps):
+            t0 = time.perf_counter()
+            L.enhance(xs, "msrcr", out=outs)
+            wall.append((time.perf_counter() - t0) * 1e3)
+            dev_ms.append(max(L.shard_last_ms(devs)))
+        ref = L.enhance(xs[0][:2].contiguous(), "msrcr")
+        ok = bool(torch.equal(ref, outs[0][:2]))
+        xh = torch.empty((world * n_dev_frames, H4K, W4K, 3), dtype=torch.uint8, pin_memory=True)
+        for d in devs:
+            xh[d * n_dev_frames:(d + 1) * n_dev_frames].copy_((xs[d] * 255.0).round().clamp(0, 255).to(torch.uint8))
+        del xs, outs
+        torch.cuda.empty_cache()
+        yh = torch.empty(xh.shape, dtype=torch.uint8, pin_memory=True)
+        for _ in range(2):
+            L.enhance(xh, "msrcr", devices=devs, out=yh)
+        hw = []
+        for _ in range(max(2, min(steps, 4))):
+            t0 = time.perf_counter()
+            L.enhance(xh, "msrcr", devices=devs, out=yh)
+            hw.append((time.perf_counter() - t0) * 1e3)
+        ms_w, ms_d, ms_h = float(np.mean(wall)), float(np.mean(dev_ms)), float(np.mean(hw))
+        res = {"workload": f"MSRCR 3840x2160, {n_dev_frames} frames per GPU, ONE process driving {world} GPU(s) through "
+                           "enhance(..., devices=[...]) -> llie_enhance_sharded",
+               "resident": {"value": round(px / ms_w / 1e3, 1), "unit": "Mpixel/s", "ms_per_step": round(ms_w, 3),
+                            "timing": "host wall clock around the synchronous call", "max_device_span_ms": round(ms_d, 3),
+                            "bit_equal_to_enhance": ok},
+               "host_u8": {"value": round(px / ms_h / 1e3, 1), "unit": "Mpixel/s", "ms_per_step": round(ms_h, 3),
+                           "h2d_bytes_per_step": int(xh.numel()), "d2h_bytes_per_step": int(yh.numel()),
+                           "api": "enhance(pinned uint8 batch, devices=[...], out=pinned): 3 slots x 3 streams per device inside one C call"}}
+        del xh, yh
+        if store is not None:
+            store.set("sh_done", "1")
+    elif store is not None:
+        store.wait(["sh_done"], datetime.timedelta(seconds=3600))
+    dist.barrier()
     return res
 
 
@@ -446,13 +625,23 @@ def _oracle_desc(name):
             "c4": "fp64 NumPy MSRCR, scipy.fft surround (all cores) on a 3840-px-wide crop of the 16384^2 image (extrapolated)"}[name]
 
 
+def cpu_threads_used():
+    """Threads the oracle's native pools really run with (BLAS via threadpoolctl; scipy.fft uses workers=-1 = all)."""
+    try:
+        from threadpoolctl import threadpool_info
+        return {"blas": max([p.get("num_threads", 1) for p in threadpool_info()] or [1]), "scipy_fft_workers": CPU_THREADS,
+                "OMP_NUM_THREADS": os.environ.get("OMP_NUM_THREADS")}
+    except Exception:  # noqa: BLE001
+        return {"OMP_NUM_THREADS": os.environ.get("OMP_NUM_THREADS")}
+
+
 def cpu_baseline(name, frame_hwc, params):
     rows = min(_oracle_rows(name), frame_hwc.shape[0])
     t0 = time.perf_counter()
     px = _oracle_step(name, frame_hwc, params, rows)
     dt = time.perf_counter() - t0
-    return {"value": round(px / dt / 1e6, 4), "unit": "Mpixel/s", "cores": os.cpu_count(), "kind": "port",
-            "seconds": round(dt, 2),
+    return {"value": round(px / dt / 1e6, 4), "unit": "Mpixel/s", "cores": CPU_THREADS, "threads": cpu_threads_used(),
+            "kind": "port", "seconds": round(dt, 2),
             "sample": f"top {rows} rows of frame 0 ({px / 1e6:.3f} Mpixel), {_oracle_desc(name)}; "
                       "self-written oracle (the reference repository ships no code)"}
 
@@ -490,7 +679,8 @@ def reference_arm(args):
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(dt * 1e3 / args.steps, 2),
             "higher_is_better": True, "scaling": "strong" if name in ("c2", "c4") else "weak", "vs_baseline": None,
             "dtype": "f64", "data": "synthetic", "config": {"workload": workload_label(name, args.gpus)},
-            "cpu_baseline": {"value": val, "unit": "Mpixel/s", "cores": os.cpu_count(), "kind": "port", "sample": sample},
+            "cpu_baseline": {"value": val, "unit": "Mpixel/s", "cores": CPU_THREADS, "threads": cpu_threads_used(),
+                             "kind": "port", "sample": sample},
             "e2e": {"value": val, "unit": "Mpixel/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0,
             "note": "the reference repository holds only README.md; this arm is the self-written NumPy oracle on the host cores"}
@@ -532,7 +722,8 @@ def main():
                     "data": "synthetic (device-generated low-light image, pre-sharded in HBM)",
                     "config": {"workload": main_res["workload"], "l2": main_res["l2"], "peaks": peaks},
                     "roofline": main_res["roofline"], "clocks": main_res["clocks"], "gpu_launches": main_res["gpu_launches"],
-                    "detail": {k: main_res[k] for k in ("host_wall_ms_per_step", "per_device_ms", "output_sane")}}
+                    "detail": {k: main_res[k] for k in ("timing", "device_span_ms_per_step", "value_at_device_span",
+                                                        "host_wall_over_device_span", "per_device_ms", "parity")}}
             print(json.dumps(line), flush=True)
         dist.close()
         return
@@ -540,11 +731,16 @@ def main():
     also = {}
     if not args.no_also and args.workload == "c2":
         for other in ("c3", "c1"):
-            r = gpu_workload(dist, other, max(3, args.steps // 2), 3, peaks, with_e2e=False, with_cpu=(dist.world == 1))
+            r = gpu_workload(dist, other, max(3, args.steps // 2), 3, peaks, with_e2e=(other == "c3"), with_cpu=(dist.world == 1))
             also[other] = r
         # the same two workloads on 8-bit images, end to end from pinned host memory
         for other in ("c2", "c3"):
             also[other + "_u8"] = gpu_workload(dist, other, 3, 3, peaks, with_e2e=True, with_cpu=False, io="u8")
+        dist.torch.cuda.empty_cache()
+        # BASELINE configs[4] at this N (rank 0 drives all N devices), oracle-checked on the seams; then the batch
+        # sharder driven from one process
+        also["c4"] = c4_workload(dist, 5, 3, peaks)
+        also["c3_one_process"] = sharded_one_process(dist, 4, 2, peaks)
     if dist.rank == 0:
         line = {"metric": "Mpixel/s", "value": main_res["value"], "unit": "Mpixel/s", "n_gpus": dist.world,
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": main_res["ms_per_step"],
@@ -556,7 +752,14 @@ def main():
                 "e2e": main_res.get("e2e"), "clocks": main_res["clocks"], "gpu_launches": main_res["gpu_launches"]}
         if also:
             line["also"] = also
-        print(json.dumps(line), flush=True)
+        out = json.dumps(line)
+        try:   # the full line also goes to gpurun_out/ (a terminal may truncate 20 KB of JSON)
+            os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
+            with open(os.path.join(ROOT, "gpurun_out", f"bench_last_n{dist.world}.json"), "w") as f:
+                f.write(out + "\n")
+        except OSError:
+            pass
+        print(out, flush=True)
     dist.close()
 
 
