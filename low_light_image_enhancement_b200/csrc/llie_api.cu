@@ -267,7 +267,10 @@ static int check_msrcr_params(const llie_msrcr_params* p) {
   for (int s = 0; s < p->n_scales; ++s)
     LLIE_REQUIRE(p->sigma[s] > 0.f && p->sigma[s] <= 4096.f, LLIE_E_ARG, "sigma[%d]=%g out of range", s, p->sigma[s]);
   LLIE_REQUIRE(p->truncate > 0.f && p->truncate <= 8.f, LLIE_E_ARG, "truncate %g out of range", p->truncate);
-  LLIE_REQUIRE(p->in_bias > 0.f && p->in_scale >= 0.f, LLIE_E_ARG, "in_scale/in_bias must keep I = scale*x+bias positive");
+  // I = in_scale x + in_bias must be a positive NORMAL fp32 number with room for the products the kernels form
+  // (the epilogue takes lg2.approx.ftz, which flushes denormals to zero)
+  LLIE_REQUIRE(p->in_bias >= 1e-30f && p->in_bias <= 1e30f && p->in_scale >= 0.f && p->in_scale <= 1e30f, LLIE_E_ARG,
+               "in_bias must lie in [1e-30, 1e30] and in_scale in [0, 1e30] (got %g, %g)", p->in_bias, p->in_scale);
   LLIE_REQUIRE(p->blur == LLIE_BLUR_PYRAMID || p->blur == LLIE_BLUR_DIRECT, LLIE_E_ARG, "unknown blur mode %d", p->blur);
   LLIE_REQUIRE(p->finish >= LLIE_FINISH_NONE && p->finish <= LLIE_FINISH_PERCENTILE, LLIE_E_ARG, "unknown finish mode %d", p->finish);
   LLIE_REQUIRE(p->finish == LLIE_FINISH_NONE || p->blur == LLIE_BLUR_PYRAMID, LLIE_E_ARG,

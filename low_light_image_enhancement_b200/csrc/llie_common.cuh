@@ -199,6 +199,12 @@ size_t msrcr_finish_partial_size();
 int msrcr_finish_stats(llie_ctx* ctx, cudaStream_t st, const float* out, int n, int h, int w, int layout, void* d_part);
 int msrcr_finish_apply(llie_ctx* ctx, cudaStream_t st, float* out, int n, int h, int w, int layout, const void* d_part,
                        int nparts, double npx, const llie_msrcr_params& p, void* d_li);
+size_t msrcr_select_hist_bytes();
+size_t msrcr_select_state_bytes();
+int msrcr_select_hist(llie_ctx* ctx, cudaStream_t st, const float* band, int h, int w, int pass, const void* d_state, void* d_hist);
+int msrcr_select_scan(llie_ctx* ctx, cudaStream_t st, int pass, const void* d_hist_gather, int nsrc, void* d_state, void* d_li,
+                      long long npx_total, float k);
+int msrcr_stretch(llie_ctx* ctx, cudaStream_t st, float* band, int h, int w, const void* d_li);
 int msrcr_pyramid_run_io(llie_ctx* ctx, const void* in, void* out, int iot, int n, int h, int w, int layout,
                          const llie_msrcr_params& p, cudaStream_t st);
 int dce_forward_int(llie_ctx* ctx, const void* in, void* out, int iot, float* maps, int n, int h, int w, int layout,
@@ -218,6 +224,7 @@ inline HostWorker* ctx_worker(llie_ctx* ctx) {
   return ctx->worker;
 }
 void sharded_release(llie_ctx* ctx);  // llie_sharded.cu
+int sharded_ensure_streams(llie_ctx* ctx);  // creates the ctx's copy streams and slot events on first use
 
 int dce_weights_upload(llie_ctx* ctx, const float* host_packed, size_t count);
 void dce_weights_free(DceWeights* w);

@@ -155,6 +155,8 @@ int run_host_shard(llie_ctx* ctx, const ShardJob& j) {
 
 }  // namespace
 
+int sharded_ensure_streams(llie_ctx* ctx) { return ensure_streams(ctx); }
+
 void sharded_release(llie_ctx* ctx) {
   for (int dir = 0; dir < 2; ++dir)
     for (int s = 0; s < kSlots; ++s)

@@ -164,9 +164,10 @@ msrcr_select_hist_kernel(const float* __restrict__ v, ImgView iv, int H, int W, 
 }
 
 // one warp per (channel, target): find the bin holding the wanted rank, extend the prefix, keep the rank inside it
+// hist: nsrc histograms src_stride elements apart (one per device band on the row-tiled path), summed on the fly
 template <int PASS>
-__global__ void msrcr_select_scan_kernel(const unsigned* __restrict__ hist, SelState* __restrict__ state,
-                                         float2* __restrict__ lo_inv, long long npx, float k) {
+__global__ void msrcr_select_scan_kernel(const unsigned* __restrict__ hist, int nsrc, long long src_stride,
+                                         SelState* __restrict__ state, float2* __restrict__ lo_inv, long long npx, float k) {
   constexpr int kShift = PASS == 0 ? 21 : (PASS == 1 ? 10 : 0);
   const int img = blockIdx.x, lane = threadIdx.x & 31, wrp = threadIdx.x >> 5;  // 6 warps
   const int c = wrp >> 1, t = wrp & 1;
@@ -180,17 +181,22 @@ __global__ void msrcr_select_scan_kernel(const unsigned* __restrict__ hist, SelS
   } else {
     rank = state[img].rank[c][t]; prefix = state[img].prefix[c][t];
   }
-  const unsigned* h = hist + (long long)img * (3 * 2 * kSelBins) + (c * 2 + (PASS == 0 ? 0 : t)) * kSelBins;
+  const unsigned* h0 = hist + (long long)img * (3 * 2 * kSelBins) + (c * 2 + (PASS == 0 ? 0 : t)) * kSelBins;
+  auto bin = [&](int b) {
+    unsigned n = 0;
+    for (int e = 0; e < nsrc; ++e) n += h0[e * src_stride + b];
+    return n;
+  };
   constexpr int kPer = kSelBins / 32;
   unsigned mine = 0;
-  for (int i = 0; i < kPer; ++i) mine += h[lane * kPer + i];
+  for (int i = 0; i < kPer; ++i) mine += bin(lane * kPer + i);
   unsigned incl = mine;
   for (int o = 1; o < 32; o <<= 1) { const unsigned n = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += n; }
   const unsigned excl = incl - mine;
   const bool has = rank >= excl && rank < incl;   // exactly one lane (the counts sum to more than rank)
   if (has) {
     unsigned acc = excl; int b = lane * kPer;
-    for (;; ++b) { const unsigned n = h[b]; if (rank < acc + n) break; acc += n; }
+    for (;; ++b) { const unsigned n = bin(b); if (rank < acc + n) break; acc += n; }
     prefix |= (unsigned)b << kShift; rank -= acc;
     state[img].prefix[c][t] = prefix; state[img].rank[c][t] = rank;
     if (PASS == 2) sh_val[c][t] = sel_value(prefix);
@@ -211,11 +217,45 @@ int select_pass(llie_ctx* ctx, cudaStream_t st, const float* out, const ImgView&
   LLIE_LAUNCH(ctx, st, "msrcr_select_hist_kernel",
               (msrcr_select_hist_kernel<PASS><<<dim3(kStatBlocks, n), kStatThreads, 0, st>>>(out, v, h, w, d_state, d_hist)));
   LLIE_LAUNCH(ctx, st, "msrcr_select_scan_kernel",
-              (msrcr_select_scan_kernel<PASS><<<n, 192, 0, st>>>(d_hist, d_state, d_li, (long long)h * w, k)));
+              (msrcr_select_scan_kernel<PASS><<<n, 192, 0, st>>>(d_hist, 1, 0, d_state, d_li, (long long)h * w, k)));
   return LLIE_OK;
 }
 
 }  // namespace
+
+// Percentile finisher across row shards (msrcr_tiled_run): per pass, every device histograms its own band
+// (msrcr_select_hist), the histograms are all-gathered by peer copies, and every device runs the same scan over their
+// sum (msrcr_select_scan) -- identical prefixes, hence identical (lo, 1/(hi-lo)), everywhere.
+size_t msrcr_select_hist_bytes() { return (size_t)3 * 2 * kSelBins * sizeof(unsigned); }
+size_t msrcr_select_state_bytes() { return sizeof(SelState); }
+
+int msrcr_select_hist(llie_ctx* ctx, cudaStream_t st, const float* band, int h, int w, int pass, const void* d_state,
+                      void* d_hist) {
+  const ImgView v = make_view(LLIE_NHWC, 3, h, w);
+  LLIE_CUDA_OK(cudaMemsetAsync(d_hist, 0, msrcr_select_hist_bytes(), st));
+  const dim3 grid(kStatBlocks, 1);
+  if (pass == 0) LLIE_LAUNCH(ctx, st, "msrcr_select_hist_kernel", (msrcr_select_hist_kernel<0><<<grid, kStatThreads, 0, st>>>(band, v, h, w, (const SelState*)d_state, (unsigned*)d_hist)));
+  if (pass == 1) LLIE_LAUNCH(ctx, st, "msrcr_select_hist_kernel", (msrcr_select_hist_kernel<1><<<grid, kStatThreads, 0, st>>>(band, v, h, w, (const SelState*)d_state, (unsigned*)d_hist)));
+  if (pass == 2) LLIE_LAUNCH(ctx, st, "msrcr_select_hist_kernel", (msrcr_select_hist_kernel<2><<<grid, kStatThreads, 0, st>>>(band, v, h, w, (const SelState*)d_state, (unsigned*)d_hist)));
+  return LLIE_OK;
+}
+
+int msrcr_select_scan(llie_ctx* ctx, cudaStream_t st, int pass, const void* d_hist_gather, int nsrc, void* d_state,
+                      void* d_li, long long npx_total, float k) {
+  const long long stride = (long long)(msrcr_select_hist_bytes() / sizeof(unsigned));
+  if (pass == 0) LLIE_LAUNCH(ctx, st, "msrcr_select_scan_kernel", (msrcr_select_scan_kernel<0><<<1, 192, 0, st>>>((const unsigned*)d_hist_gather, nsrc, stride, (SelState*)d_state, (float2*)d_li, npx_total, k)));
+  if (pass == 1) LLIE_LAUNCH(ctx, st, "msrcr_select_scan_kernel", (msrcr_select_scan_kernel<1><<<1, 192, 0, st>>>((const unsigned*)d_hist_gather, nsrc, stride, (SelState*)d_state, (float2*)d_li, npx_total, k)));
+  if (pass == 2) LLIE_LAUNCH(ctx, st, "msrcr_select_scan_kernel", (msrcr_select_scan_kernel<2><<<1, 192, 0, st>>>((const unsigned*)d_hist_gather, nsrc, stride, (SelState*)d_state, (float2*)d_li, npx_total, k)));
+  return LLIE_OK;
+}
+
+int msrcr_stretch(llie_ctx* ctx, cudaStream_t st, float* band, int h, int w, const void* d_li) {
+  const ImgView v = make_view(LLIE_NHWC, 3, h, w);
+  const long long npx = (long long)h * w;
+  LLIE_LAUNCH(ctx, st, "msrcr_stretch_kernel",
+              (msrcr_stretch_kernel<<<dim3((unsigned)((npx + 255) / 256), 1), 256, 0, st>>>(band, v, h, w, (const float2*)d_li)));
+  return LLIE_OK;
+}
 
 // The two halves of the min/max and mean/std finishers, also used by the row-tiled path (msrcr_tiled_run), where the
 // partials of every device's band are gathered before the fold.

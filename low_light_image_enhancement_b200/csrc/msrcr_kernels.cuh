@@ -303,9 +303,16 @@ constexpr int kUpGroups = 16;
 __host__ __device__ inline int up_bc_y_chunks(int c0, int c1) {
   return (((c1 - 1 - kPC + 4) >> 2) - ((c0 - kPC + 4) >> 2)) / kUpGroups + 1;
 }
+// All stride-16 scales of a call share ONE level-C map M = prod_k S_k^(e_k), e_k = weight_k / weight_ref, because the
+// epilogue only needs sum_k weight_k lg S_k = weight_ref lg M.  With equal weights e_k = 1 and M is the plain product.
+// The surrounds are smooth at this resolution (sigma >= 40 against a stride of 4), so interpolating M instead of
+// every S_k moves the result by < 1e-6 -- and the final kernel upsamples two maps instead of three.  One launch
+// upsamples NSRC (1 or 2) scales and writes their product once; further scales multiply in (accumulate = 1).
+struct UpSrc { const float* t2[2]; float expo[2]; };
+template <int NSRC>
 __global__ void __launch_bounds__(128)
-up_bc_y_kernel(const float* __restrict__ T2, float* __restrict__ SC, int hB, int hC, int wC, int c0, int c1,
-               const __grid_constant__ UpWeights uw) {
+up_bc_y_kernel(const __grid_constant__ UpSrc srcs, float* __restrict__ SC, int hB, int hC, int wC, int c0, int c1,
+               const __grid_constant__ UpWeights uw, int accumulate) {
   const long long plane = blockIdx.z;
   const int xx = blockIdx.x * 128 + threadIdx.x;
   if (xx >= wC) return;
@@ -313,20 +320,33 @@ up_bc_y_kernel(const float* __restrict__ T2, float* __restrict__ SC, int hB, int
   const int q0 = q_lo + blockIdx.y * kUpGroups;
   if (q0 > q_hi) return;
   const int q1 = min(q0 + kUpGroups - 1, q_hi);
-  const float* src = T2 + plane * (long long)hB * wC + xx;
-  float* dst = SC + plane * (long long)hC * wC + xx;
-  float win[10], o[4];
+  const float* src[NSRC];
 #pragma unroll
-  for (int t = 1; t < 10; ++t) win[t] = __ldg(src + (long long)min(max(q0 + kPB - 6 + t, 0), hB - 1) * wC);
+  for (int k = 0; k < NSRC; ++k) src[k] = srcs.t2[k] + plane * (long long)hB * wC + xx;
+  float* dst = SC + plane * (long long)hC * wC + xx;
+  float win[NSRC][10], o[NSRC][4];
+#pragma unroll
+  for (int k = 0; k < NSRC; ++k)
+#pragma unroll
+    for (int t = 1; t < 10; ++t) win[k][t] = __ldg(src[k] + (long long)min(max(q0 + kPB - 6 + t, 0), hB - 1) * wC);
   for (int q = q0; q <= q1; ++q) {
 #pragma unroll
-    for (int t = 0; t < 9; ++t) win[t] = win[t + 1];
-    win[9] = __ldg(src + (long long)min(max(q + kPB + 4, 0), hB - 1) * wC);
-    up_bc_group(win, uw, o);
+    for (int k = 0; k < NSRC; ++k) {
+#pragma unroll
+      for (int t = 0; t < 9; ++t) win[k][t] = win[k][t + 1];
+      win[k][9] = __ldg(src[k] + (long long)min(max(q + kPB + 4, 0), hB - 1) * wC);
+      up_bc_group(win[k], uw, o[k]);
+    }
 #pragma unroll
     for (int ph = 0; ph < 4; ++ph) {
       const int jc = 4 * q + ph + kPC - 4;
-      if (jc >= c0 && jc < c1) dst[(long long)jc * wC] = o[ph];
+      if (jc >= c0 && jc < c1) {
+        float v = 1.f;
+#pragma unroll
+        for (int k = 0; k < NSRC; ++k) v *= srcs.expo[k] != 1.f ? exp2f(srcs.expo[k] * __log2f(o[k][ph])) : o[k][ph];
+        float* d = dst + (long long)jc * wC;
+        *d = accumulate ? *d * v : v;
+      }
     }
   }
 }

@@ -15,6 +15,7 @@
 #include "msrcr_kernels.cuh"
 
 #include <algorithm>
+#include <atomic>
 #include <cmath>
 #include <cstring>
 #include <condition_variable>
@@ -382,7 +383,9 @@ int plan_scale(double sigma, double truncate, ScalePlan* out) {
   std::vector<double> best = half(kg);
   KernelErr best_err = kernel_errors(level, h, best, kor);
   // candidate 2: weighted least squares with a few more taps than the oracle's radius covers
-  const int rl_ls = (ro + s - 1) / s + (level ? 5 : 2);
+  // a few more taps than the oracle's radius covers: stride 16 costs nothing (1/256 of the pixels); at stride 4
+  // one extra tap keeps the FIR at the same number of 8-tap steps as the radius itself (2 r + 8 rounded up to 8)
+  const int rl_ls = (ro + s - 1) / s + (level ? 5 : 1);
   if (rl_ls <= kMaxLsRadius) {
     std::vector<double> x;
     if (plan_taps_ls(level, rl_ls, h, kor, &x)) {
@@ -436,6 +439,14 @@ struct MsrcrPlan {
   llie_msrcr_params key;
   std::vector<ScalePlan> scales;
   std::vector<int> order;   // scale indices, level-C (six-tap) scales first
+  // level-C maps the final kernel reads: one per stride-4 scale, then ONE for all stride-16 scales together
+  // (up_bc_y_kernel: M = prod S_k^(weight_k / weight_ref), stored in the slot of the first stride-16 scale)
+  struct FinalMap { int slot; float weight; bool four_tap; };
+  std::vector<FinalMap> maps;
+  std::vector<float> expo;  // per scale: exponent in M (stride-16 scales), 1 otherwise
+  std::vector<int> accum;   // per scale: multiply into M (not the first stride-16 scale)
+  double sum_e = 0;         // sum of the exponents inside M
+  bool combined = false;    // false: every scale keeps its own map (M could leave the fp32 range)
   float* d_taps = nullptr;  // per-scale low-res taps
   std::vector<int> tap_off;
   UpWeights uw;
@@ -489,6 +500,33 @@ static int ensure_plan(llie_ctx* ctx, const llie_msrcr_params& p, cudaStream_t s
   for (int lv = 0; lv < 2; ++lv)
     for (int k = 0; k < p.n_scales; ++k)
       if (pl->scales[k].level == lv) pl->order.push_back(k);
+  pl->expo.assign(p.n_scales, 1.f);
+  pl->accum.assign(p.n_scales, 0);
+  int kb0 = -1;
+  float w_ref = 0.f;
+  for (int k = 0; k < p.n_scales; ++k)
+    if (pl->scales[k].level == 1) {
+      if (kb0 < 0) kb0 = k;
+      if (std::fabs(p.weight[k]) > std::fabs(w_ref)) w_ref = p.weight[k];
+    }
+  double sum_e = 0;
+  for (int k = 0; k < p.n_scales; ++k)
+    if (pl->scales[k].level == 1) sum_e += w_ref != 0.f ? std::fabs((double)p.weight[k] / w_ref) : 0.0;
+  // M must stay a normal fp32 number: every surround lies in [in_bias, in_scale + in_bias]
+  const bool combine = kb0 >= 0 && sum_e * std::fabs(std::log10((double)p.in_scale + p.in_bias)) <= 30.0 &&
+                       sum_e * std::fabs(std::log10((double)p.in_bias)) <= 30.0;
+  for (int k = 0; k < p.n_scales; ++k) {
+    if (pl->scales[k].level == 0 || !combine) pl->maps.push_back({k, p.weight[k], false});
+    else {
+      pl->expo[k] = w_ref != 0.f ? p.weight[k] / w_ref : 0.f;
+      pl->accum[k] = k != kb0;
+    }
+  }
+  if (combine) {
+    pl->maps.push_back({kb0, w_ref, true});
+    pl->sum_e = sum_e;
+  }
+  pl->combined = combine;
   for (int ph = 0; ph < 4; ++ph) {
     double w[2 * kTU + 1];
     up_weights(ph, w);
@@ -543,9 +581,9 @@ void launch_fir_y8(bool param, dim3 grid, size_t smem, cudaStream_t st, A... a) 
 
 template <int N6, int N4>
 void launch_final(dim3 grid, cudaStream_t st, const void* x, void* out, int iot, ImgView v, int io, int W, int in_row0,
-                  int row_begin, int row_end, int rps, const FinalParams& fp) {
-  // equal weights over the scales of this launch and values bounded so that their product cannot overflow
-  bool eq = fp.in_scale * fmaxf(255.f, io_levels(iot)) + fp.in_bias <= 1e9f && fp.in_bias >= 1e-9f;
+                  int row_begin, int row_end, int rps, const FinalParams& fp, bool eq) {
+  // eq: equal weights over the maps of this launch and values bounded so that their product stays a normal fp32
+  // number (decided by final_passes, which knows the exponents inside the combined stride-16 map)
   for (int i = 1; i < N6 + N4; ++i) eq = eq && fp.w2[i] == fp.w2[0];
   if (iot == kIoU16) {
     if (eq) msrcr_final_kernel<N6, N4, uint16_t, true><<<grid, 128, 0, st>>>((const uint16_t*)x, (uint16_t*)out, v, io, W, in_row0, row_begin, row_end, rps, fp);
@@ -582,27 +620,59 @@ int final_passes(llie_ctx* ctx, cudaStream_t st, const MsrcrPlan* pl, const llie
   fp.offset255 = p.offset / 255.f;
   fp.in_scale = p.in_scale / io_levels(iot); fp.in_bias = p.in_bias;  // integer images are read as raw 0..255 / 0..65535
   fp.no_clip = (iot == kIoF32 && p.finish != LLIE_FINISH_NONE) ? 1 : 0;
-  int n6 = 0;
-  for (auto& sc : pl->scales) n6 += (sc.level == 0);
-  if (p.n_scales == 3 && n6 == 1) {
-    for (int i = 0; i < 3; ++i) {
-      const int k = pl->order[i];
-      fp.map[i] = dSC + (size_t)k * c_elems;
-      fp.w2[i] = (float)(ln2 * p.weight[k]);
+  const int nm = (int)pl->maps.size();
+  // one MUFU.LG2 of the PRODUCT of a launch's maps is only taken while that product provably stays a normal fp32
+  // number: every surround lies in [in_bias, in_scale + in_bias], the combined map carries sum_e of them
+  const double lmax = std::log10((double)p.in_scale + p.in_bias), lmin = std::log10((double)p.in_bias);
+  auto product_ok = [&](int k0, int cnt) {
+    double e = 0;
+    for (int i = 0; i < cnt; ++i) e += pl->maps[k0 + i].four_tap ? pl->sum_e : 1.0;
+    return e * std::max(lmax, 0.0) <= 36.0 && e * std::min(lmin, 0.0) >= -36.0;
+  };
+  if (nm == 2 && !pl->maps[0].four_tap && pl->maps[1].four_tap) {
+    // the default shape (one stride-4 scale + the combined stride-16 map): 6-tap + 4-tap upsample in one pass
+    for (int i = 0; i < 2; ++i) {
+      fp.map[i] = dSC + (size_t)pl->maps[i].slot * c_elems;
+      fp.w2[i] = (float)(ln2 * pl->maps[i].weight);
     }
-    LLIE_LAUNCH(ctx, st, "msrcr_final_kernel", (launch_final<1, 2>(grid, st, in, out, iot, v, io, w, in_row0, row_begin, row_end, rps, fp)));
+    LLIE_LAUNCH(ctx, st, "msrcr_final_kernel", (launch_final<1, 1>(grid, st, in, out, iot, v, io, w, in_row0, row_begin, row_end, rps, fp, product_ok(0, 2))));
   } else {
-    for (int k0 = 0; k0 < p.n_scales; k0 += 3) {
-      const int cnt = std::min(3, p.n_scales - k0);
+    for (int k0 = 0; k0 < nm; k0 += 3) {
+      const int cnt = std::min(3, nm - k0);
       for (int i = 0; i < cnt; ++i) {
-        fp.map[i] = dSC + (size_t)(k0 + i) * c_elems;
-        fp.w2[i] = (float)(ln2 * p.weight[k0 + i]);
+        fp.map[i] = dSC + (size_t)pl->maps[k0 + i].slot * c_elems;
+        fp.w2[i] = (float)(ln2 * pl->maps[k0 + i].weight);
       }
       fp.acc_in = k0 > 0 ? (const float*)dAcc : nullptr;
-      fp.acc_out = k0 + cnt < p.n_scales ? dAcc : nullptr;
-      if (cnt == 1) LLIE_LAUNCH(ctx, st, "msrcr_final_kernel", (launch_final<1, 0>(grid, st, in, out, iot, v, io, w, in_row0, row_begin, row_end, rps, fp)));
-      if (cnt == 2) LLIE_LAUNCH(ctx, st, "msrcr_final_kernel", (launch_final<2, 0>(grid, st, in, out, iot, v, io, w, in_row0, row_begin, row_end, rps, fp)));
-      if (cnt == 3) LLIE_LAUNCH(ctx, st, "msrcr_final_kernel", (launch_final<3, 0>(grid, st, in, out, iot, v, io, w, in_row0, row_begin, row_end, rps, fp)));
+      fp.acc_out = k0 + cnt < nm ? dAcc : nullptr;
+      if (cnt == 1) LLIE_LAUNCH(ctx, st, "msrcr_final_kernel", (launch_final<1, 0>(grid, st, in, out, iot, v, io, w, in_row0, row_begin, row_end, rps, fp, product_ok(k0, cnt))));
+      if (cnt == 2) LLIE_LAUNCH(ctx, st, "msrcr_final_kernel", (launch_final<2, 0>(grid, st, in, out, iot, v, io, w, in_row0, row_begin, row_end, rps, fp, product_ok(k0, cnt))));
+      if (cnt == 3) LLIE_LAUNCH(ctx, st, "msrcr_final_kernel", (launch_final<3, 0>(grid, st, in, out, iot, v, io, w, in_row0, row_begin, row_end, rps, fp, product_ok(k0, cnt))));
+    }
+  }
+  return LLIE_OK;
+}
+
+// B -> C upsample (y pass) of the stride-16 scales listed in `ks`: one launch per pair writes / multiplies their
+// (powered) product into the combined map, or -- without combination -- every scale into its own slot.
+int launch_up_bc_y(llie_ctx* ctx, cudaStream_t st, const MsrcrPlan* pl, const std::vector<int>& ks, const float* t2_base,
+                   size_t t2_elems, float* sc_base, size_t c_elems, int hB, int hC, int wC, int c0, int c1, int planes) {
+  dim3 uy(ceil_div(wC, 128), up_bc_y_chunks(c0, c1), planes);
+  if (!pl->combined) {
+    for (size_t i = 0; i < ks.size(); ++i) {
+      UpSrc u{{t2_base + i * t2_elems, nullptr}, {1.f, 1.f}};
+      LLIE_LAUNCH(ctx, st, "up_bc_y_kernel", (up_bc_y_kernel<1><<<uy, 128, 0, st>>>(u, sc_base + (size_t)ks[i] * c_elems, hB, hC, wC, c0, c1, pl->uw, 0)));
+    }
+    return LLIE_OK;
+  }
+  float* dst = sc_base + (size_t)pl->maps.back().slot * c_elems;
+  for (size_t i = 0; i < ks.size(); i += 2) {
+    if (i + 1 < ks.size()) {
+      UpSrc u{{t2_base + i * t2_elems, t2_base + (i + 1) * t2_elems}, {pl->expo[ks[i]], pl->expo[ks[i + 1]]}};
+      LLIE_LAUNCH(ctx, st, "up_bc_y_kernel", (up_bc_y_kernel<2><<<uy, 128, 0, st>>>(u, dst, hB, hC, wC, c0, c1, pl->uw, i > 0)));
+    } else {
+      UpSrc u{{t2_base + i * t2_elems, nullptr}, {pl->expo[ks[i]], 1.f}};
+      LLIE_LAUNCH(ctx, st, "up_bc_y_kernel", (up_bc_y_kernel<1><<<uy, 128, 0, st>>>(u, dst, hB, hC, wC, c0, c1, pl->uw, i > 0)));
     }
   }
   return LLIE_OK;
@@ -638,9 +708,9 @@ int msrcr_pyramid_run_io(llie_ctx* ctx, const void* in, void* out, int iot, int 
     LLIE_TRY(ctx->workspace("msrcr.B", b_elems * 4, &dB));
     LLIE_TRY(ctx->workspace("msrcr.B.tmp", b_elems * 4, &dBt));
     LLIE_TRY(ctx->workspace("msrcr.SB", b_elems * 4, &dSB));
-    LLIE_TRY(ctx->workspace("msrcr.T2", (size_t)planes * hB * wC * 4, &dT2));
+    LLIE_TRY(ctx->workspace("msrcr.T2", (size_t)n_b * planes * hB * wC * 4, &dT2));
   }
-  if (p.n_scales > 3) LLIE_TRY(ctx->workspace("msrcr.acc", (size_t)n * h * w * 3 * 4, &dAcc));
+  if (pl->maps.size() > 3) LLIE_TRY(ctx->workspace("msrcr.acc", (size_t)n * h * w * 3 * 4, &dAcc));
 
   const ImgView v = make_view(layout, 3, h, w);
   const bool vec = (w % 4 == 0) && ((reinterpret_cast<uintptr_t>(in) | reinterpret_cast<uintptr_t>(out)) % (iot == kIoU8 ? 4 : (iot == kIoU16 ? 8 : 16)) == 0);
@@ -691,6 +761,8 @@ int msrcr_pyramid_run_io(llie_ctx* ctx, const void* in, void* out, int iot, int 
     LLIE_LAUNCH(ctx, st, "decim4_y_kernel", decim4_y_kernel<<<dim3(ceil_div(wB, 128), ceil_div(hB, kDecQ), planes), 128, 0, st>>>((const float*)dTB, (float*)dB, hC, hB, wB, 0, hB));
   }
   (void)CS;
+  std::vector<int> b_scales;  // stride-16 scales in T2 order
+  const size_t t2_elems = (size_t)planes * hB * wC;
   for (int k = 0; k < p.n_scales; ++k) {
     const ScalePlan& sp = pl->scales[k];
     const float* taps = pl->d_taps + pl->tap_off[k];
@@ -707,11 +779,13 @@ int msrcr_pyramid_run_io(llie_ctx* ctx, const void* in, void* out, int iot, int 
       dim3 gx((unsigned)((long long)planes * hB), ceil_div(wB, kFirX8Tile)), gy(ceil_div(wB, 128), ceil_div(hB, kFir8), planes);
       LLIE_LAUNCH(ctx, st, "fir_x_kernel", (launch_fir_x8(tp, gx, smx, st, (const float*)dB, (float*)dBt, taps, r, wB, planes * hB, 0, 0, ft)));
       LLIE_LAUNCH(ctx, st, "fir_y_kernel", (launch_fir_y8(tp, gy, smy, st, (const float*)dBt, (float*)dSB, taps, r, hB, wB, 0, hB, 0, hB, 0, hB, ft)));
-      dim3 ux(ceil_div((long long)hB * up_bc_x_groups(wC), 256), 1, planes), uy(ceil_div(wC, 128), up_bc_y_chunks(0, hC), planes);
-      LLIE_LAUNCH(ctx, st, "up_bc_x_kernel", up_bc_x_kernel<<<ux, 256, 0, st>>>((const float*)dSB, (float*)dT2, hB, wB, wC, 0, hB, pl->uw));
-      LLIE_LAUNCH(ctx, st, "up_bc_y_kernel", up_bc_y_kernel<<<uy, 128, 0, st>>>((const float*)dT2, sc, hB, hC, wC, 0, hC, pl->uw));
+      dim3 ux(ceil_div((long long)hB * up_bc_x_groups(wC), 256), 1, planes);
+      LLIE_LAUNCH(ctx, st, "up_bc_x_kernel", up_bc_x_kernel<<<ux, 256, 0, st>>>((const float*)dSB, (float*)dT2 + b_scales.size() * t2_elems, hB, wB, wC, 0, hB, pl->uw));
+      b_scales.push_back(k);
     }
   }
+  if (!b_scales.empty())
+    LLIE_TRY(launch_up_bc_y(ctx, st, pl, b_scales, (const float*)dT2, t2_elems, (float*)dSC, c_elems, hB, hC, wC, 0, hC, planes));
   LLIE_TRY(final_passes(ctx, st, pl, p, in, out, v, vec, nhwc, n, h, w, 0, 0, h, hC, wC, (const float*)dSC, c_elems,
                         (float*)dAcc, iot));
   return LLIE_OK;
@@ -789,7 +863,7 @@ namespace {
 
 struct TileBufs {
   float *V, *C, *Ct, *SC, *TB, *B, *Bt, *SB, *T2, *band_top, *band_bot;
-  void *fin_part = nullptr, *fin_gather = nullptr, *fin_li = nullptr;  // global-statistics finisher
+  void *fin_part = nullptr, *fin_gather = nullptr, *fin_li = nullptr, *fin_state = nullptr;  // global-statistics finisher
 };
 
 constexpr int kBandTopRows = 48, kBandBotRows = 64, kHaloRaw = 16;
@@ -858,62 +932,104 @@ int tiled_phase_b(llie_ctx* ctx, int d, int n_dev, llie_ctx* const* ctxs, const 
   const MsrcrPlan* pl = ctx->plan;
   const int hC = level_c_size(H), wC = level_c_size(W), hB = level_b_size(H), wB = level_b_size(W);
   const size_t c_elems = (size_t)3 * hC * wC;
+  // Foreign C rows.  The rows the stride-4 scales reach (c0 range: a few rows beyond the shard) are fetched on the
+  // compute stream; the far rows only the stride-16 branch needs travel on the ctx's copy stream underneath the
+  // stride-4 FIRs (order the work so that the copies overlap it) and are joined before decim4_x.
+  cudaStream_t far = ctx->sh_h2d ? ctx->sh_h2d : st;
+  bool far_used = false;
+  auto fetch = [&](int e, int lo, int hi, cudaStream_t s2) -> int {
+    if (lo >= hi) return LLIE_OK;
+    for (int pln = 0; pln < 3; ++pln) {
+      const size_t off = ((size_t)pln * hC + lo) * wC;
+      LLIE_TRY(copy_dev(b.C + off, ctx->device, bufs[e].C + off, ctxs[e]->device, (size_t)(hi - lo) * wC * sizeof(float), s2));
+    }
+    return LLIE_OK;
+  };
   for (int e = 0; e < n_dev; ++e) {
     if (e == d) continue;
     const int lo = std::max(g.cn_lo, geo[e].own_lo), hi = std::min(g.cn_hi, geo[e].own_hi);
     if (lo >= hi) continue;
+    const int nlo = std::max(lo, g.c0_lo), nhi = std::min(hi, g.c0_hi);  // near part (may be empty)
     LLIE_CUDA_OK(cudaStreamWaitEvent(st, ev_c[e], 0));
-    for (int pln = 0; pln < 3; ++pln) {
-      const size_t off = ((size_t)pln * hC + lo) * wC;
-      LLIE_TRY(copy_dev(b.C + off, ctx->device, bufs[e].C + off, ctxs[e]->device, (size_t)(hi - lo) * wC * sizeof(float), st));
-    }
-  }
-  int n_b = 0;
-  for (auto& sp : pl->scales) n_b += sp.level;
-  if (n_b) {
-    LLIE_LAUNCH(ctx, st, "decim4_x_kernel", decim4_x_kernel<<<dim3(ceil_div(wB, kDecXTile), g.c1_hi - g.c1_lo, 3), 128, 0, st>>>(b.C, b.TB, hC, wC, wB, g.c1_lo, g.c1_hi));
-    LLIE_LAUNCH(ctx, st, "decim4_y_kernel", decim4_y_kernel<<<dim3(ceil_div(wB, 128), ceil_div(g.bb_hi - g.bb_lo, kDecQ), 3), 128, 0, st>>>(b.TB, b.B, hC, hB, wB, g.bb_lo, g.bb_hi));
-  }
-  for (int k = 0; k < p.n_scales; ++k) {
-    const ScalePlan& sp = pl->scales[k];
-    const float* taps = pl->d_taps + pl->tap_off[k];
-    const int r = sp.radius_low;
-    const size_t smx = fir_x8_smem(r), smy = (size_t)fir8_steps(r) * sizeof(float);
-    bool tp;
-    const FirTaps ft = make_fir_taps(sp, &tp);
-    float* sc = b.SC + (size_t)k * c_elems;
-    if (sp.level == 0) {
-      const int x0 = clampi(g.s_lo - r, 0, hC), x1 = clampi(g.s_hi + r, 0, hC);
-      dim3 gx(3 * (x1 - x0), ceil_div(wC, kFirX8Tile)), gy(ceil_div(wC, 128), ceil_div(g.s_hi - g.s_lo, kFir8), 3);
-      LLIE_LAUNCH(ctx, st, "fir_x_kernel", (launch_fir_x8(tp, gx, smx, st, b.C, b.Ct, taps, r, wC, x1 - x0, hC, x0, ft)));
-      LLIE_LAUNCH(ctx, st, "fir_y_kernel", (launch_fir_y8(tp, gy, smy, st, b.Ct, sc, taps, r, hC, wC, 0, hC, g.s_lo, g.s_hi - g.s_lo, g.s_lo, hC, ft)));
+    if (nlo < nhi) {
+      LLIE_TRY(fetch(e, nlo, nhi, st));
+      if (far != st && (lo < nlo || nhi < hi)) {
+        LLIE_CUDA_OK(cudaStreamWaitEvent(far, ev_c[e], 0));
+        far_used = true;
+      }
+      LLIE_TRY(fetch(e, lo, nlo, far));
+      LLIE_TRY(fetch(e, nhi, hi, far));
     } else {
-      const int x0 = clampi(g.t_lo - r, 0, hB), x1 = clampi(g.t_hi + r, 0, hB);
-      dim3 gx(3 * (x1 - x0), ceil_div(wB, kFirX8Tile)), gy(ceil_div(wB, 128), ceil_div(g.t_hi - g.t_lo, kFir8), 3);
-      LLIE_LAUNCH(ctx, st, "fir_x_kernel", (launch_fir_x8(tp, gx, smx, st, b.B, b.Bt, taps, r, wB, x1 - x0, hB, x0, ft)));
-      LLIE_LAUNCH(ctx, st, "fir_y_kernel", (launch_fir_y8(tp, gy, smy, st, b.Bt, b.SB, taps, r, hB, wB, 0, hB, g.t_lo, g.t_hi - g.t_lo, g.t_lo, hB, ft)));
-      dim3 ux(ceil_div((long long)(g.t_hi - g.t_lo) * up_bc_x_groups(wC), 256), 1, 3), uy(ceil_div(wC, 128), up_bc_y_chunks(g.s_lo, g.s_hi), 3);
-      LLIE_LAUNCH(ctx, st, "up_bc_x_kernel", up_bc_x_kernel<<<ux, 256, 0, st>>>(b.SB, b.T2, hB, wB, wC, g.t_lo, g.t_hi, pl->uw));
-      LLIE_LAUNCH(ctx, st, "up_bc_y_kernel", up_bc_y_kernel<<<uy, 128, 0, st>>>(b.T2, sc, hB, hC, wC, g.s_lo, g.s_hi, pl->uw));
+      if (far != st) {
+        LLIE_CUDA_OK(cudaStreamWaitEvent(far, ev_c[e], 0));
+        far_used = true;
+      }
+      LLIE_TRY(fetch(e, lo, hi, far));
     }
   }
+  if (far_used) LLIE_CUDA_OK(cudaEventRecord(ctx->sh_ev[0][0], far));
+  // stride-4 scales first: they need the near rows only
+  std::vector<int> b_scales;
+  const size_t t2_elems = (size_t)3 * hB * wC;
+  for (int pass = 0; pass < 2; ++pass) {
+    if (pass == 1) {
+      if (far_used) LLIE_CUDA_OK(cudaStreamWaitEvent(st, ctx->sh_ev[0][0], 0));
+      int n_b = 0;
+      for (auto& sp : pl->scales) n_b += sp.level;
+      if (n_b) {
+        LLIE_LAUNCH(ctx, st, "decim4_x_kernel", decim4_x_kernel<<<dim3(ceil_div(wB, kDecXTile), g.c1_hi - g.c1_lo, 3), 128, 0, st>>>(b.C, b.TB, hC, wC, wB, g.c1_lo, g.c1_hi));
+        LLIE_LAUNCH(ctx, st, "decim4_y_kernel", decim4_y_kernel<<<dim3(ceil_div(wB, 128), ceil_div(g.bb_hi - g.bb_lo, kDecQ), 3), 128, 0, st>>>(b.TB, b.B, hC, hB, wB, g.bb_lo, g.bb_hi));
+      }
+    }
+    for (int k = 0; k < p.n_scales; ++k) {
+      const ScalePlan& sp = pl->scales[k];
+      if (sp.level != pass) continue;
+      const float* taps = pl->d_taps + pl->tap_off[k];
+      const int r = sp.radius_low;
+      const size_t smx = fir_x8_smem(r), smy = (size_t)fir8_steps(r) * sizeof(float);
+      bool tp;
+      const FirTaps ft = make_fir_taps(sp, &tp);
+      float* sc = b.SC + (size_t)k * c_elems;
+      if (sp.level == 0) {
+        const int x0 = clampi(g.s_lo - r, 0, hC), x1 = clampi(g.s_hi + r, 0, hC);
+        dim3 gx(3 * (x1 - x0), ceil_div(wC, kFirX8Tile)), gy(ceil_div(wC, 128), ceil_div(g.s_hi - g.s_lo, kFir8), 3);
+        LLIE_LAUNCH(ctx, st, "fir_x_kernel", (launch_fir_x8(tp, gx, smx, st, b.C, b.Ct, taps, r, wC, x1 - x0, hC, x0, ft)));
+        LLIE_LAUNCH(ctx, st, "fir_y_kernel", (launch_fir_y8(tp, gy, smy, st, b.Ct, sc, taps, r, hC, wC, 0, hC, g.s_lo, g.s_hi - g.s_lo, g.s_lo, hC, ft)));
+      } else {
+        const int x0 = clampi(g.t_lo - r, 0, hB), x1 = clampi(g.t_hi + r, 0, hB);
+        dim3 gx(3 * (x1 - x0), ceil_div(wB, kFirX8Tile)), gy(ceil_div(wB, 128), ceil_div(g.t_hi - g.t_lo, kFir8), 3);
+        LLIE_LAUNCH(ctx, st, "fir_x_kernel", (launch_fir_x8(tp, gx, smx, st, b.B, b.Bt, taps, r, wB, x1 - x0, hB, x0, ft)));
+        LLIE_LAUNCH(ctx, st, "fir_y_kernel", (launch_fir_y8(tp, gy, smy, st, b.Bt, b.SB, taps, r, hB, wB, 0, hB, g.t_lo, g.t_hi - g.t_lo, g.t_lo, hB, ft)));
+        dim3 ux(ceil_div((long long)(g.t_hi - g.t_lo) * up_bc_x_groups(wC), 256), 1, 3);
+        LLIE_LAUNCH(ctx, st, "up_bc_x_kernel", up_bc_x_kernel<<<ux, 256, 0, st>>>(b.SB, b.T2 + b_scales.size() * t2_elems, hB, wB, wC, g.t_lo, g.t_hi, pl->uw));
+        b_scales.push_back(k);
+      }
+    }
+  }
+  if (!b_scales.empty())
+    LLIE_TRY(launch_up_bc_y(ctx, st, pl, b_scales, b.T2, t2_elems, b.SC, c_elems, hB, hC, wC, g.s_lo, g.s_hi, 3));
   const ImgView v = make_view(LLIE_NHWC, 3, g.R1 - g.R0, W);
   const bool vec = (W % 4 == 0) && ((reinterpret_cast<uintptr_t>(in[d]) | reinterpret_cast<uintptr_t>(out[d])) % 16 == 0);
   return final_passes(ctx, st, pl, p, in[d], out[d], v, vec, true, 1, g.R1 - g.R0, W, g.R0, g.R0, g.R1, hC, wC, b.SC, c_elems,
                       nullptr);
 }
 
-// Reusable rendezvous of the per-device host threads.
+// Reusable rendezvous of the per-device host threads.  The threads are dedicated (one per ctx) and the sections
+// between rendezvous last tens of microseconds, so they spin (a futex wake costs more than a whole section) and
+// only yield when a peer is late.
 struct HostBarrier {
-  std::mutex mu;
-  std::condition_variable cv;
-  int n, waiting = 0, generation = 0;
+  std::atomic<int> waiting{0}, generation{0};
+  int n;
   explicit HostBarrier(int n_) : n(n_) {}
   void wait() {
-    std::unique_lock<std::mutex> lk(mu);
-    const int gen = generation;
-    if (++waiting == n) { waiting = 0; ++generation; cv.notify_all(); }
-    else cv.wait(lk, [&] { return gen != generation; });
+    const int gen = generation.load(std::memory_order_acquire);
+    if (waiting.fetch_add(1, std::memory_order_acq_rel) + 1 == n) {
+      waiting.store(0, std::memory_order_relaxed);
+      generation.fetch_add(1, std::memory_order_release);
+    } else {
+      for (int spins = 0; generation.load(std::memory_order_acquire) == gen; ++spins)
+        if (spins > 20000) std::this_thread::yield();
+    }
   }
 };
 
@@ -937,16 +1053,21 @@ int msrcr_tiled_run(llie_ctx* const* ctxs, int n_dev, const float* const* in, fl
   for (int d = 0; d < n_dev; ++d) geo[d] = tile_geometry(d, n_dev, row0, rows, H, r0_max, rb_max, any_b);
   std::vector<TileBufs> bufs(n_dev);
   std::vector<cudaEvent_t> ev_c(n_dev, nullptr);
-  std::vector<int> rc(n_dev, LLIE_OK);
+  std::vector<int> rc_a(n_dev, LLIE_OK), rc(n_dev, LLIE_OK);
   std::vector<std::string> msg(n_dev);
   HostBarrier bar(n_dev);
+  const bool percentile = p.finish == LLIE_FINISH_PERCENTILE;
+  const size_t hb = msrcr_select_hist_bytes();
 
-  // One host thread per device: launch latency of ~25 operations per device must not serialise.
+  // One PERSISTENT host thread per device (the ctx's HostWorker; the caller's thread drives shard 0): the ~25
+  // launches and copies of a device must not serialise behind the other devices', and spawning threads per call
+  // cost more than the whole 8-GPU step.  One rendezvous per call: "every device's C-ready event is recorded".
   auto worker = [&](int d) {
     llie_ctx* ctx = ctxs[d];
-    auto body_a = [&]() -> int {
+    auto setup = [&]() -> int {
       LLIE_CUDA_OK(cudaSetDevice(ctx->device));
       LLIE_TRY(ensure_plan(ctx, p, ctx->stream));
+      LLIE_TRY(sharded_ensure_streams(ctx));  // the copy stream + its event (shared with the batch sharder)
       TileBufs& b = bufs[d];
       const size_t c_bytes = (size_t)3 * hC * wC * 4, b_bytes = (size_t)3 * hB * wB * 4;
       void* q;
@@ -958,13 +1079,14 @@ int msrcr_tiled_run(llie_ctx* const* ctxs, int n_dev, const float* const* in, fl
       LLIE_TRY(ctx->workspace("tile.B", b_bytes, &q)); b.B = (float*)q;
       LLIE_TRY(ctx->workspace("tile.Bt", b_bytes, &q)); b.Bt = (float*)q;
       LLIE_TRY(ctx->workspace("tile.SB", b_bytes, &q)); b.SB = (float*)q;
-      LLIE_TRY(ctx->workspace("tile.T2", (size_t)3 * hB * wC * 4, &q)); b.T2 = (float*)q;
+      LLIE_TRY(ctx->workspace("tile.T2", (size_t)3 * 3 * hB * wC * 4, &q)); b.T2 = (float*)q;  // one per scale (<= 3)
       LLIE_TRY(ctx->workspace("tile.band_top", (size_t)kBandTopRows * RW * 4, &q)); b.band_top = (float*)q;
       LLIE_TRY(ctx->workspace("tile.band_bot", (size_t)kBandBotRows * RW * 4, &q)); b.band_bot = (float*)q;
       if (p.finish != LLIE_FINISH_NONE) {
-        LLIE_TRY(ctx->workspace("tile.finish.partials", msrcr_finish_partials_bytes(), &b.fin_part));
-        LLIE_TRY(ctx->workspace("tile.finish.gather", msrcr_finish_partials_bytes() * n_dev, &b.fin_gather));
+        LLIE_TRY(ctx->workspace("tile.finish.partials", std::max(msrcr_finish_partials_bytes(), hb), &b.fin_part));
+        LLIE_TRY(ctx->workspace("tile.finish.gather", std::max(msrcr_finish_partials_bytes(), 3 * hb) * n_dev, &b.fin_gather));
         LLIE_TRY(ctx->workspace("tile.finish.lo_inv", 3 * sizeof(float2), &b.fin_li));
+        LLIE_TRY(ctx->workspace("tile.finish.state", msrcr_select_state_bytes(), &b.fin_state));
       }
       if (!ctx->tile_event) {
         LLIE_CUDA_OK(cudaEventCreateWithFlags(&ctx->tile_event, cudaEventDisableTiming));
@@ -973,70 +1095,80 @@ int msrcr_tiled_run(llie_ctx* const* ctxs, int n_dev, const float* const* in, fl
       }
       ev_c[d] = ctx->tile_event;
       ctx->tile_ms = -1.f;
-      return LLIE_OK;
-    };
-    auto body_a2 = [&]() -> int {
       LLIE_CUDA_OK(cudaEventRecord(ctx->tile_t0, ctx->stream));
       LLIE_TRY(tiled_phase_a(ctx, d, n_dev, ctxs, in, rows, geo[d], bufs[d], H, W, p));
       LLIE_CUDA_OK(cudaEventRecord(ev_c[d], ctx->stream));
       return LLIE_OK;
     };
-    rc[d] = body_a();
-    bar.wait();  // common start: plans and workspaces exist everywhere (first-call costs stay outside the timed span)
-    if (rc[d] == LLIE_OK) rc[d] = body_a2();
-    if (rc[d] != LLIE_OK) msg[d] = llie_last_error();
-    bar.wait();  // every device's C-ready event is recorded (or its phase failed)
-    bool all_ok = true;
-    for (int e = 0; e < n_dev; ++e) all_ok = all_ok && rc[e] == LLIE_OK;
-    bar.wait();  // rc[] is read by everyone before anyone writes it again
-    if (all_ok) {
-      rc[d] = tiled_phase_b(ctx, d, n_dev, ctxs, in, out, geo, bufs, ev_c, H, W, p);
-      if (rc[d] != LLIE_OK) msg[d] = llie_last_error();
-    }
+    auto fail = [&](int code) {
+      if (rc[d] == LLIE_OK && code != LLIE_OK) {
+        rc[d] = code;
+        msg[d] = last_error_text();
+      }
+    };
+    rc_a[d] = setup();
+    fail(rc_a[d]);
+    bar.wait();  // every device's buffers exist and its C-ready event is recorded (or its phase failed)
+    bool ok = true;  // rc_a[] is final after the rendezvous; rc[] is only read by its owner until the end
+    for (int e = 0; e < n_dev; ++e) ok = ok && rc_a[e] == LLIE_OK;
+    if (ok) fail(tiled_phase_b(ctx, d, n_dev, ctxs, in, out, geo, bufs, ev_c, H, W, p));
     if (p.finish != LLIE_FINISH_NONE) {
       // Global-statistics finisher across the shards ("one tiny all-reduce"): every device
-      // reduces its own band to 256 partials and pushes them into every device's gather buffer (an all-gather of
-      // 16 KB blocks by peer copies); each device then folds all partials in the same order -- identical (lo, 1/(hi-lo))
-      // everywhere -- and stretches its band in place.
-      const size_t pb = msrcr_finish_partials_bytes();
+      // reduces its own band to partials and pushes them into every device's gather buffer (an all-gather of
+      // 16-48 KB blocks by peer copies); each device then folds all partials in the same order -- identical
+      // (lo, 1/(hi-lo)) everywhere -- and stretches its band in place.  The percentile finisher does this three
+      // times (one radix-select pass each: 11 + 11 + 10 bits) on per-band histograms.
+      // Every round: [reduce, push, record] -> rendezvous -> [wait, fold]; a second rendezvous separates "everybody
+      // has enqueued its waits" from the next round's re-recording of the events.
       const int band_rows = geo[d].R1 - geo[d].R0;
-      auto stage1 = [&]() -> int {
-        LLIE_TRY(msrcr_finish_stats(ctx, ctx->stream, out[d], 1, band_rows, W, LLIE_NHWC, bufs[d].fin_part));
-        for (int e = 0; e < n_dev; ++e)
-          LLIE_TRY(copy_dev((char*)bufs[e].fin_gather + (size_t)d * pb, ctxs[e]->device, bufs[d].fin_part, ctx->device, pb, ctx->stream));
-        LLIE_CUDA_OK(cudaEventRecord(ev_c[d], ctx->stream));
-        return LLIE_OK;
-      };
-      auto stage2 = [&]() -> int {
-        for (int e = 0; e < n_dev; ++e)
-          if (e != d) LLIE_CUDA_OK(cudaStreamWaitEvent(ctx->stream, ev_c[e], 0));
-        return msrcr_finish_apply(ctx, ctx->stream, out[d], 1, band_rows, W, LLIE_NHWC, bufs[d].fin_gather,
-                                  n_dev * (int)(pb / msrcr_finish_partial_size()), (double)H * W, p, bufs[d].fin_li);
-      };
-      bar.wait();  // every device has enqueued its phase-B waits on ev_c before anyone records it again
-      const bool ok_b = all_ok && rc[d] == LLIE_OK;
-      if (ok_b) { rc[d] = stage1(); if (rc[d] != LLIE_OK) msg[d] = llie_last_error(); }
-      bar.wait();  // all partial pushes are enqueued and their events recorded
-      bool all_ok2 = all_ok;
-      for (int e = 0; e < n_dev; ++e) all_ok2 = all_ok2 && rc[e] == LLIE_OK;
-      bar.wait();
-      if (all_ok2) { rc[d] = stage2(); if (rc[d] != LLIE_OK) msg[d] = llie_last_error(); }
+      const int rounds = percentile ? 3 : 1;
+      std::vector<int> okv(n_dev);
+      for (int round = 0; round < rounds; ++round) {
+        const size_t pb = percentile ? hb : msrcr_finish_partials_bytes();
+        auto stage1 = [&]() -> int {
+          if (percentile) LLIE_TRY(msrcr_select_hist(ctx, ctx->stream, out[d], band_rows, W, round, bufs[d].fin_state, bufs[d].fin_part));
+          else LLIE_TRY(msrcr_finish_stats(ctx, ctx->stream, out[d], 1, band_rows, W, LLIE_NHWC, bufs[d].fin_part));
+          for (int e = 0; e < n_dev; ++e)
+            LLIE_TRY(copy_dev((char*)bufs[e].fin_gather + ((size_t)round * n_dev + d) * pb, ctxs[e]->device, bufs[d].fin_part,
+                              ctx->device, pb, ctx->stream));
+          LLIE_CUDA_OK(cudaEventRecord(ev_c[d], ctx->stream));
+          return LLIE_OK;
+        };
+        auto stage2 = [&]() -> int {
+          for (int e = 0; e < n_dev; ++e)
+            if (e != d) LLIE_CUDA_OK(cudaStreamWaitEvent(ctx->stream, ev_c[e], 0));
+          const char* gather = (const char*)bufs[d].fin_gather + (size_t)round * n_dev * pb;
+          if (percentile) {
+            LLIE_TRY(msrcr_select_scan(ctx, ctx->stream, round, gather, n_dev, bufs[d].fin_state, bufs[d].fin_li, (long long)H * W, p.finish_k));
+            if (round == 2) LLIE_TRY(msrcr_stretch(ctx, ctx->stream, out[d], band_rows, W, bufs[d].fin_li));
+            return LLIE_OK;
+          }
+          return msrcr_finish_apply(ctx, ctx->stream, out[d], 1, band_rows, W, LLIE_NHWC, gather,
+                                    n_dev * (int)(pb / msrcr_finish_partial_size()), (double)H * W, p, bufs[d].fin_li);
+        };
+        bar.wait();  // every device has enqueued its waits on the events before anyone records them again
+        if (ok && rc[d] == LLIE_OK) fail(stage1());
+        rc_a[d] = rc[d];
+        bar.wait();  // all pushes are enqueued and their events recorded
+        for (int e = 0; e < n_dev; ++e) ok = ok && rc_a[e] == LLIE_OK;
+        if (ok) fail(stage2());
+      }
     }
-    if (all_ok && rc[d] == LLIE_OK) cudaEventRecord(ctx->tile_t1, ctx->stream);
+    if (ok && rc[d] == LLIE_OK) cudaEventRecord(ctx->tile_t1, ctx->stream);
     cudaError_t e = cudaStreamSynchronize(ctx->stream);
-    if (e == cudaSuccess && all_ok && rc[d] == LLIE_OK) cudaEventElapsedTime(&ctx->tile_ms, ctx->tile_t0, ctx->tile_t1);
+    if (e == cudaSuccess && ctx->sh_h2d) e = cudaStreamSynchronize(ctx->sh_h2d);
+    if (e == cudaSuccess && ok && rc[d] == LLIE_OK) cudaEventElapsedTime(&ctx->tile_ms, ctx->tile_t0, ctx->tile_t1);
     if (e != cudaSuccess && rc[d] == LLIE_OK) {
       rc[d] = LLIE_E_CUDA;
       msg[d] = std::string("tiled MSRCR: device ") + std::to_string(ctx->device) + ": " + cudaGetErrorString(e);
     }
-    bar.wait();  // nobody frees / reuses a C buffer a neighbour may still be copying from
   };
   int prev_dev = 0;
   cudaGetDevice(&prev_dev);
-  std::vector<std::thread> th;
-  for (int d = 1; d < n_dev; ++d) th.emplace_back(worker, d);
+  for (int d = 1; d < n_dev; ++d) ctx_worker(ctxs[d])->post([&worker, d] { worker(d); });
   worker(0);
-  for (auto& t : th) t.join();
+  // nobody returns (and no C buffer is reused) before every device has finished copying from its neighbours
+  for (int d = 1; d < n_dev; ++d) ctxs[d]->worker->wait();
   cudaSetDevice(prev_dev);
   for (int d = 0; d < n_dev; ++d)
     if (rc[d] != LLIE_OK) {

@@ -17,15 +17,16 @@ extern "C" int llie_msrcr_tiled(llie_ctx* const* ctxs, int n_dev, const float* c
   LLIE_TRY(msrcr_params_normalise(params, &full));
   params = &full;
   LLIE_REQUIRE(params->blur == LLIE_BLUR_PYRAMID, LLIE_E_ARG, "row-tiled MSRCR uses the pyramid blur only");
-  LLIE_REQUIRE(params->finish != LLIE_FINISH_PERCENTILE, LLIE_E_ARG,
-               "row-tiled MSRCR supports the minmax and meanstd finishers only (no cross-device radix select)");
-  LLIE_REQUIRE(params->finish >= LLIE_FINISH_NONE && params->finish <= LLIE_FINISH_MEANSTD, LLIE_E_ARG, "unknown finish mode %d",
+  LLIE_REQUIRE(params->finish >= LLIE_FINISH_NONE && params->finish <= LLIE_FINISH_PERCENTILE, LLIE_E_ARG, "unknown finish mode %d",
                params->finish);
+  LLIE_REQUIRE(params->finish != LLIE_FINISH_PERCENTILE || (params->finish_k >= 0.f && params->finish_k < 50.f), LLIE_E_ARG,
+               "finish_k %g out of range [0, 50) percent", params->finish_k);
   LLIE_REQUIRE(params->finish != LLIE_FINISH_MEANSTD || (params->finish_k > 0.f && params->finish_k <= 16.f), LLIE_E_ARG,
                "finish_k %g out of range (0, 16]", params->finish_k);
   LLIE_REQUIRE(params->n_scales >= 1 && params->n_scales <= 3, LLIE_E_ARG, "row-tiled MSRCR supports 1..3 scales (got %d)",
                params->n_scales);
-  LLIE_REQUIRE(params->truncate > 0.f && params->truncate <= 8.f && params->in_bias > 0.f && params->in_scale >= 0.f,
+  LLIE_REQUIRE(params->truncate > 0.f && params->truncate <= 8.f && params->in_bias >= 1e-30f && params->in_bias <= 1e30f &&
+                   params->in_scale >= 0.f && params->in_scale <= 1e30f,
                LLIE_E_ARG, "bad MSRCR parameters");
   LLIE_REQUIRE(h_total > 0 && w > 0 && (long long)h_total * w <= (1ll << 31), LLIE_E_SHAPE, "bad image size %d x %d",
                h_total, w);
