@@ -66,6 +66,7 @@ int llie_ctx::workspace(const char* name, size_t bytes, void** out) {
     return e == cudaErrorMemoryAllocation ? LLIE_E_NOMEM : LLIE_E_CUDA;
   }
   bufs[name] = {p, want};
+  ++ws_generation;
   *out = p;
   return LLIE_OK;
 }
@@ -192,6 +193,8 @@ int llie_destroy(llie_ctx* ctx) {
   msrcr_plan_free(ctx->plan);
   dce_weights_free(ctx->dce);
   dce_tc_release(ctx);
+  for (auto& gs : ctx->g_tile)
+    if (gs.exec) cudaGraphExecDestroy(gs.exec);
   if (ctx->tile_event) { cudaEventDestroy(ctx->tile_event); cudaEventDestroy(ctx->tile_t0); cudaEventDestroy(ctx->tile_t1); }
   if (ctx->stream) cudaStreamDestroy(ctx->stream);
   delete ctx;

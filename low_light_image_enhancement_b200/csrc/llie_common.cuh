@@ -6,6 +6,7 @@
 #include <cuda_runtime.h>
 #include <cuda_bf16.h>
 
+#include <atomic>
 #include <condition_variable>
 #include <cstdarg>
 #include <cstdint>
@@ -70,7 +71,7 @@ class HostWorker {
   ~HostWorker() {
     {
       std::lock_guard<std::mutex> lk(mu_);
-      quit_ = true;
+      quit_.store(true, std::memory_order_release);
     }
     cv_.notify_all();
     th_.join();
@@ -79,35 +80,58 @@ class HostWorker {
     {
       std::lock_guard<std::mutex> lk(mu_);
       job_ = std::move(job);
-      pending_ = true;
-      done_ = false;
+      done_.store(false, std::memory_order_relaxed);
+      pending_.store(true, std::memory_order_release);
     }
     cv_.notify_all();
   }
+  // Both sides spin briefly before they sleep: a condition-variable wake-up costs 30-60 us, which is most of what a
+  // caller of the 8-GPU row-tiled step (0.7 ms of device work) would otherwise wait on top of the devices.
   void wait() {
+    for (int i = 0; i < kSpin; ++i) {
+      if (done_.load(std::memory_order_acquire)) return;
+      relax();
+    }
     std::unique_lock<std::mutex> lk(mu_);
-    cv_.wait(lk, [this] { return done_; });
+    cv_.wait(lk, [this] { return done_.load(std::memory_order_acquire); });
   }
 
  private:
+  static constexpr int kSpin = 6000;  // ~0.2-0.3 ms of pause instructions
+  static void relax() {
+#if defined(__x86_64__) || defined(__i386__)
+    __builtin_ia32_pause();
+#else
+    std::this_thread::yield();
+#endif
+  }
   void loop() {
-    std::unique_lock<std::mutex> lk(mu_);
     for (;;) {
-      cv_.wait(lk, [this] { return pending_ || quit_; });
-      if (quit_) return;
-      std::function<void()> job = std::move(job_);
-      pending_ = false;
-      lk.unlock();
+      bool got = false;
+      for (int i = 0; i < kSpin && !got; ++i) {
+        got = pending_.load(std::memory_order_acquire) || quit_.load(std::memory_order_acquire);
+        if (!got) relax();
+      }
+      std::function<void()> job;
+      {
+        std::unique_lock<std::mutex> lk(mu_);
+        cv_.wait(lk, [this] { return pending_.load(std::memory_order_acquire) || quit_.load(std::memory_order_acquire); });
+        if (quit_.load(std::memory_order_acquire)) return;
+        job = std::move(job_);
+        pending_.store(false, std::memory_order_relaxed);
+      }
       job();
-      lk.lock();
-      done_ = true;
+      {
+        std::lock_guard<std::mutex> lk(mu_);
+        done_.store(true, std::memory_order_release);
+      }
       cv_.notify_all();
     }
   }
   std::mutex mu_;
   std::condition_variable cv_;
   std::function<void()> job_;
-  bool pending_ = false, done_ = true, quit_ = false;
+  std::atomic<bool> pending_{false}, done_{true}, quit_{false};
   std::thread th_;  // last member: the thread starts after everything above is constructed
 };
 
@@ -125,6 +149,7 @@ struct llie_ctx {
   cudaStream_t stream = nullptr;
   uint64_t launches = 0;
   std::map<std::string, std::pair<void*, size_t>> bufs;  // named workspaces, grown on demand
+  uint64_t ws_generation = 0;  // bumped whenever a workspace is (re)allocated: captured graphs hold their addresses
   llie::MsrcrPlan* plan = nullptr;
   llie::DceWeights* dce = nullptr;
   llie::DceTcPack* tc = nullptr;
@@ -144,6 +169,10 @@ struct llie_ctx {
   void* sh_pin[2][3] = {{nullptr, nullptr, nullptr}, {nullptr, nullptr, nullptr}};
   size_t sh_pin_bytes[2][3] = {{0, 0, 0}, {0, 0, 0}};
   float shard_ms = -1.f;
+  // CUDA graphs of the row-tiled path's launch sequences (phase A; the local tail of phase B), replayed while the
+  // key -- pointers, geometry, parameters, workspace generation -- stays the same
+  struct GraphSlot { uint64_t key = 0; cudaGraphExec_t exec = nullptr; uint64_t launches = 0; };
+  GraphSlot g_tile[2];
 
   // Returns a device buffer of at least `bytes` under `name`; reallocates only when growing.
   int workspace(const char* name, size_t bytes, void** out);
@@ -217,6 +246,38 @@ int msrcr_plan_detail(float sigma, float truncate, double* l1, double* edge, dou
 void msrcr_plan_free(MsrcrPlan* p);
 int msrcr_tiled_run(llie_ctx* const* ctxs, int n_dev, const float* const* in, float* const* out, const int* row0,
                     const int* rows, int H, int W, const llie_msrcr_params& p);
+
+// Runs body(stream) -- a pure sequence of launches / copies -- as a CUDA graph: captured on first use (or when `key`
+// changes) and replayed afterwards, so that ~10-20 dependent small launches cost one graph launch on the host and
+// run back to back on the device.  Profiling runs (per-kernel events) bypass the graph.
+template <class F>
+int run_as_graph(llie_ctx* ctx, llie_ctx::GraphSlot& slot, uint64_t key, cudaStream_t st, F&& body) {
+  if (ctx->profiling) return body(st);
+  if (!slot.exec || slot.key != key) {
+    if (slot.exec) { cudaGraphExecDestroy(slot.exec); slot.exec = nullptr; }
+    const uint64_t l0 = ctx->launches;
+    LLIE_CUDA_OK(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+    const int rc = body(st);
+    cudaGraph_t graph = nullptr;
+    const cudaError_t e = cudaStreamEndCapture(st, &graph);
+    slot.launches = ctx->launches - l0;
+    ctx->launches = l0;
+    if (rc != LLIE_OK) { if (graph) cudaGraphDestroy(graph); return rc; }
+    if (e != cudaSuccess) { (void)cudaGetLastError(); set_error("graph capture failed: %s", cudaGetErrorString(e)); return LLIE_E_CUDA; }
+    const cudaError_t e2 = cudaGraphInstantiate(&slot.exec, graph, 0);
+    cudaGraphDestroy(graph);
+    if (e2 != cudaSuccess) { (void)cudaGetLastError(); slot.exec = nullptr; set_error("graph instantiate failed: %s", cudaGetErrorString(e2)); return LLIE_E_CUDA; }
+    slot.key = key;
+  }
+  LLIE_CUDA_OK(cudaGraphLaunch(slot.exec, st));
+  ctx->launches += slot.launches;
+  return LLIE_OK;
+}
+inline uint64_t fnv1a(const void* data, size_t n, uint64_t h = 1469598103934665603ull) {
+  const unsigned char* p = static_cast<const unsigned char*>(data);
+  for (size_t i = 0; i < n; ++i) { h ^= p[i]; h *= 1099511628211ull; }
+  return h;
+}
 
 int msrcr_params_normalise(const llie_msrcr_params* p, llie_msrcr_params* full);  // llie_api.cu
 inline HostWorker* ctx_worker(llie_ctx* ctx) {

@@ -875,9 +875,8 @@ int copy_dev(void* dst, int dst_dev, const void* src, int src_dev, size_t bytes,
 }
 
 // Phase A on device d: raw-row bands from the neighbours, V, and the C rows centred on own pixels.
-int tiled_phase_a(llie_ctx* ctx, int d, int n_dev, llie_ctx* const* ctxs, const float* const* in, const int* rows,
-                  const TileGeom& g, const TileBufs& b, int H, int W, const llie_msrcr_params& p) {
-  cudaStream_t st = ctx->stream;
+int tiled_phase_a_body(llie_ctx* ctx, cudaStream_t st, int d, int n_dev, llie_ctx* const* ctxs, const float* const* in,
+                       const int* rows, const TileGeom& g, const TileBufs& b, int H, int W, const llie_msrcr_params& p) {
   const int RW = 3 * W, hC = level_c_size(H), wC = level_c_size(W);
   const bool vec = (W % 4 == 0) && (reinterpret_cast<uintptr_t>(in[d]) % 16 == 0);
   const bool first = d == 0, last = d == n_dev - 1;
@@ -920,6 +919,24 @@ int tiled_phase_a(llie_ctx* ctx, int d, int n_dev, llie_ctx* const* ctxs, const 
   LLIE_LAUNCH(ctx, st, "down4_cols_kernel",
               down4_cols_kernel<3><<<grid, 128, 0, st>>>(b.V, b.C, RW, W, hC, wC, g.own_lo, p.in_scale, p.in_bias));
   return LLIE_OK;
+}
+
+uint64_t tile_key(llie_ctx* ctx, int d, int n_dev, const void* in_d, const void* in_up, const void* in_dn, const void* out_d,
+                  int rows_up, const TileGeom& g, int H, int W, const llie_msrcr_params& p) {
+  struct { uint64_t gen; const void *a, *b, *c, *o; int d, n, H, W, ru; TileGeom g; llie_msrcr_params p; } k;
+  memset(&k, 0, sizeof(k));
+  k.gen = ctx->ws_generation; k.a = in_d; k.b = in_up; k.c = in_dn; k.o = out_d; k.d = d; k.n = n_dev; k.H = H; k.W = W;
+  k.ru = rows_up; k.g = g; k.p = p;
+  return fnv1a(&k, sizeof(k)) | 1ull;
+}
+
+int tiled_phase_a(llie_ctx* ctx, int d, int n_dev, llie_ctx* const* ctxs, const float* const* in, const int* rows,
+                  const TileGeom& g, const TileBufs& b, int H, int W, const llie_msrcr_params& p) {
+  const uint64_t key = tile_key(ctx, d, n_dev, in[d], d > 0 ? in[d - 1] : nullptr, d + 1 < n_dev ? in[d + 1] : nullptr, nullptr,
+                                d > 0 ? rows[d - 1] : 0, g, H, W, p);
+  return run_as_graph(ctx, ctx->g_tile[0], key, ctx->stream, [&](cudaStream_t st) {
+    return tiled_phase_a_body(ctx, st, d, n_dev, ctxs, in, rows, g, b, H, W, p);
+  });
 }
 
 // Phase B on device d: fetch the foreign C rows, then everything downstream, locally.
@@ -968,22 +985,14 @@ int tiled_phase_b(llie_ctx* ctx, int d, int n_dev, llie_ctx* const* ctxs, const 
     }
   }
   if (far_used) LLIE_CUDA_OK(cudaEventRecord(ctx->sh_ev[0][0], far));
-  // stride-4 scales first: they need the near rows only
-  std::vector<int> b_scales;
+  // Stride-4 scales first (plain launches): they need the near rows only, and the far copies run underneath.  The
+  // rest -- decimation to stride 16, the stride-16 scales, both upsamplers and the final kernel: ~11 dependent
+  // launches -- is one CUDA graph.
   const size_t t2_elems = (size_t)3 * hB * wC;
-  for (int pass = 0; pass < 2; ++pass) {
-    if (pass == 1) {
-      if (far_used) LLIE_CUDA_OK(cudaStreamWaitEvent(st, ctx->sh_ev[0][0], 0));
-      int n_b = 0;
-      for (auto& sp : pl->scales) n_b += sp.level;
-      if (n_b) {
-        LLIE_LAUNCH(ctx, st, "decim4_x_kernel", decim4_x_kernel<<<dim3(ceil_div(wB, kDecXTile), g.c1_hi - g.c1_lo, 3), 128, 0, st>>>(b.C, b.TB, hC, wC, wB, g.c1_lo, g.c1_hi));
-        LLIE_LAUNCH(ctx, st, "decim4_y_kernel", decim4_y_kernel<<<dim3(ceil_div(wB, 128), ceil_div(g.bb_hi - g.bb_lo, kDecQ), 3), 128, 0, st>>>(b.TB, b.B, hC, hB, wB, g.bb_lo, g.bb_hi));
-      }
-    }
+  auto scale_launches = [&](cudaStream_t s2, int level, std::vector<int>* b_scales) -> int {
     for (int k = 0; k < p.n_scales; ++k) {
       const ScalePlan& sp = pl->scales[k];
-      if (sp.level != pass) continue;
+      if (sp.level != level) continue;
       const float* taps = pl->d_taps + pl->tap_off[k];
       const int r = sp.radius_low;
       const size_t smx = fir_x8_smem(r), smy = (size_t)fir8_steps(r) * sizeof(float);
@@ -993,25 +1002,39 @@ int tiled_phase_b(llie_ctx* ctx, int d, int n_dev, llie_ctx* const* ctxs, const 
       if (sp.level == 0) {
         const int x0 = clampi(g.s_lo - r, 0, hC), x1 = clampi(g.s_hi + r, 0, hC);
         dim3 gx(3 * (x1 - x0), ceil_div(wC, kFirX8Tile)), gy(ceil_div(wC, 128), ceil_div(g.s_hi - g.s_lo, kFir8), 3);
-        LLIE_LAUNCH(ctx, st, "fir_x_kernel", (launch_fir_x8(tp, gx, smx, st, b.C, b.Ct, taps, r, wC, x1 - x0, hC, x0, ft)));
-        LLIE_LAUNCH(ctx, st, "fir_y_kernel", (launch_fir_y8(tp, gy, smy, st, b.Ct, sc, taps, r, hC, wC, 0, hC, g.s_lo, g.s_hi - g.s_lo, g.s_lo, hC, ft)));
+        LLIE_LAUNCH(ctx, s2, "fir_x_kernel", (launch_fir_x8(tp, gx, smx, s2, b.C, b.Ct, taps, r, wC, x1 - x0, hC, x0, ft)));
+        LLIE_LAUNCH(ctx, s2, "fir_y_kernel", (launch_fir_y8(tp, gy, smy, s2, b.Ct, sc, taps, r, hC, wC, 0, hC, g.s_lo, g.s_hi - g.s_lo, g.s_lo, hC, ft)));
       } else {
         const int x0 = clampi(g.t_lo - r, 0, hB), x1 = clampi(g.t_hi + r, 0, hB);
         dim3 gx(3 * (x1 - x0), ceil_div(wB, kFirX8Tile)), gy(ceil_div(wB, 128), ceil_div(g.t_hi - g.t_lo, kFir8), 3);
-        LLIE_LAUNCH(ctx, st, "fir_x_kernel", (launch_fir_x8(tp, gx, smx, st, b.B, b.Bt, taps, r, wB, x1 - x0, hB, x0, ft)));
-        LLIE_LAUNCH(ctx, st, "fir_y_kernel", (launch_fir_y8(tp, gy, smy, st, b.Bt, b.SB, taps, r, hB, wB, 0, hB, g.t_lo, g.t_hi - g.t_lo, g.t_lo, hB, ft)));
+        LLIE_LAUNCH(ctx, s2, "fir_x_kernel", (launch_fir_x8(tp, gx, smx, s2, b.B, b.Bt, taps, r, wB, x1 - x0, hB, x0, ft)));
+        LLIE_LAUNCH(ctx, s2, "fir_y_kernel", (launch_fir_y8(tp, gy, smy, s2, b.Bt, b.SB, taps, r, hB, wB, 0, hB, g.t_lo, g.t_hi - g.t_lo, g.t_lo, hB, ft)));
         dim3 ux(ceil_div((long long)(g.t_hi - g.t_lo) * up_bc_x_groups(wC), 256), 1, 3);
-        LLIE_LAUNCH(ctx, st, "up_bc_x_kernel", up_bc_x_kernel<<<ux, 256, 0, st>>>(b.SB, b.T2 + b_scales.size() * t2_elems, hB, wB, wC, g.t_lo, g.t_hi, pl->uw));
-        b_scales.push_back(k);
+        LLIE_LAUNCH(ctx, s2, "up_bc_x_kernel", up_bc_x_kernel<<<ux, 256, 0, s2>>>(b.SB, b.T2 + b_scales->size() * t2_elems, hB, wB, wC, g.t_lo, g.t_hi, pl->uw));
+        b_scales->push_back(k);
       }
     }
-  }
-  if (!b_scales.empty())
-    LLIE_TRY(launch_up_bc_y(ctx, st, pl, b_scales, b.T2, t2_elems, b.SC, c_elems, hB, hC, wC, g.s_lo, g.s_hi, 3));
-  const ImgView v = make_view(LLIE_NHWC, 3, g.R1 - g.R0, W);
-  const bool vec = (W % 4 == 0) && ((reinterpret_cast<uintptr_t>(in[d]) | reinterpret_cast<uintptr_t>(out[d])) % 16 == 0);
-  return final_passes(ctx, st, pl, p, in[d], out[d], v, vec, true, 1, g.R1 - g.R0, W, g.R0, g.R0, g.R1, hC, wC, b.SC, c_elems,
-                      nullptr);
+    return LLIE_OK;
+  };
+  LLIE_TRY(scale_launches(st, 0, nullptr));
+  if (far_used) LLIE_CUDA_OK(cudaStreamWaitEvent(st, ctx->sh_ev[0][0], 0));
+  const uint64_t key = tile_key(ctx, d, n_dev, in[d], nullptr, nullptr, out[d], 0, g, H, W, p);
+  return run_as_graph(ctx, ctx->g_tile[1], key, st, [&](cudaStream_t s2) -> int {
+    int n_b = 0;
+    for (auto& sp : pl->scales) n_b += sp.level;
+    if (n_b) {
+      LLIE_LAUNCH(ctx, s2, "decim4_x_kernel", decim4_x_kernel<<<dim3(ceil_div(wB, kDecXTile), g.c1_hi - g.c1_lo, 3), 128, 0, s2>>>(b.C, b.TB, hC, wC, wB, g.c1_lo, g.c1_hi));
+      LLIE_LAUNCH(ctx, s2, "decim4_y_kernel", decim4_y_kernel<<<dim3(ceil_div(wB, 128), ceil_div(g.bb_hi - g.bb_lo, kDecQ), 3), 128, 0, s2>>>(b.TB, b.B, hC, hB, wB, g.bb_lo, g.bb_hi));
+    }
+    std::vector<int> b_scales;
+    LLIE_TRY(scale_launches(s2, 1, &b_scales));
+    if (!b_scales.empty())
+      LLIE_TRY(launch_up_bc_y(ctx, s2, pl, b_scales, b.T2, t2_elems, b.SC, c_elems, hB, hC, wC, g.s_lo, g.s_hi, 3));
+    const ImgView v = make_view(LLIE_NHWC, 3, g.R1 - g.R0, W);
+    const bool vec = (W % 4 == 0) && ((reinterpret_cast<uintptr_t>(in[d]) | reinterpret_cast<uintptr_t>(out[d])) % 16 == 0);
+    return final_passes(ctx, s2, pl, p, in[d], out[d], v, vec, true, 1, g.R1 - g.R0, W, g.R0, g.R0, g.R1, hC, wC, b.SC, c_elems,
+                        nullptr);
+  });
 }
 
 // Reusable rendezvous of the per-device host threads.  The threads are dedicated (one per ctx) and the sections
