@@ -60,14 +60,13 @@ FLOP_PER_PX.update({"dce_split_k32_kernel": 3 * 3 * (2 * 32 * 32 * 9),          
                     "dce_split_k64_kernel": 2 * 3 * (2 * 64 * 32 * 9),             # conv5, conv6
                     "dce_split_last_kernel": 3 * (2 * 64 * 24 * 9)})               # conv7
 DCE_TENSOR_FLOP_PER_PX = 156672          # conv2..conv7
-MSRCR_NORTH_STAR_BYTES_PER_PX = 108      # two-pass separable data flow
 # per-kernel algorithmic HBM bytes per full-resolution pixel of the decimated cascade (DESIGN.md "Kernels"):
 #   down4_rows_kernel : reads x (12 B), writes the stride-4 (vertical) partial V (12/4 B)
-#   msrcr_final_kernel: reads x (12 B), writes out (12 B), reads 3 scales x 3 ch of stride-4 surround (36/16 B)
-MSRCR_KERNEL_BYTES_PER_PX = {"down4_rows_kernel": 12 + 3.0, "msrcr_final_kernel": 12 + 12 + 36 / 16.0}
+#   msrcr_final_kernel: reads x (12 B), writes out (12 B), reads 2 level-C maps x 3 ch of stride-4 surround (24/16 B):
+#                       the sigma = 15 surround and the combined map of the two stride-16 scales
+MSRCR_KERNEL_BYTES_PER_PX = {"down4_rows_kernel": 12 + 3.0, "msrcr_final_kernel": 12 + 12 + 24 / 16.0}
 # the same kernels on 8-bit images: the image costs 1 byte per sample
-MSRCR_KERNEL_BYTES_PER_PX_U8 = {"down4_rows_kernel": 3 + 3.0, "msrcr_final_kernel": 3 + 3 + 36 / 16.0}
-MSRCR_NORTH_STAR_BYTES_PER_PX_U8 = 3 + 36 + 36 + 3 + 3   # the same two-pass data flow with uint8 image I/O
+MSRCR_KERNEL_BYTES_PER_PX_U8 = {"down4_rows_kernel": 3 + 3.0, "msrcr_final_kernel": 3 + 3 + 24 / 16.0}
 
 
 def csrc_hash():

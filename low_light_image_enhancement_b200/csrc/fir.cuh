@@ -183,18 +183,29 @@ __global__ void __launch_bounds__(128) fir_y8_kernel(const float* __restrict__ i
   const int y0 = out_row0 + yb;            // its level row
   const long long plane = blockIdx.z;
   const float* src = in + plane * (long long)in_rows * RW + j;
-  float acc[kFir8], k[kFir8];
+  float acc[kFir8], k[kFir8], v[8], vn[8];
 #pragma unroll
   for (int q = 0; q < kFir8; ++q) acc[q] = 0.f, k[q] = 0.f;
-  for (int u0 = 0; u0 < n_steps; u0 += 8) {
+  // The eight samples of the NEXT block are requested before the 64 FFMAs of the current one (the loads come from
+  // L2: without the look-ahead every block of a warp waited out a full round trip with nothing else to issue).
+  auto load8 = [&](float (&d)[8], int u0) {
 #pragma unroll
     for (int s = 0; s < 8; ++s) {
       const int y = min(max(y0 - r + u0 + s, 0), H - 1) - in_row0;
-      const float v = __ldg(src + (long long)y * RW);
+      d[s] = __ldg(src + (long long)y * RW);
+    }
+  };
+  load8(v, 0);
+  for (int u0 = 0; u0 < n_steps; u0 += 8) {
+    if (u0 + 8 < n_steps) load8(vn, u0 + 8);
+#pragma unroll
+    for (int s = 0; s < 8; ++s) {
       k[s] = kParamTaps ? ft.t[u0 + s] : stap[u0 + s];
 #pragma unroll
-      for (int q = 0; q < kFir8; ++q) acc[q] = fmaf(k[(s - q) & 7], v, acc[q]);
+      for (int q = 0; q < kFir8; ++q) acc[q] = fmaf(k[(s - q) & 7], v[s], acc[q]);
     }
+#pragma unroll
+    for (int s = 0; s < 8; ++s) v[s] = vn[s];
   }
   float* dst = out + (plane * (long long)out_plane_rows + out_buf_row0) * RW + j;
 #pragma unroll

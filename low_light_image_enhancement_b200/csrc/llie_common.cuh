@@ -171,7 +171,7 @@ struct llie_ctx {
   float shard_ms = -1.f;
   // CUDA graphs of the row-tiled path's launch sequences (phase A; the local tail of phase B), replayed while the
   // key -- pointers, geometry, parameters, workspace generation -- stays the same
-  struct GraphSlot { uint64_t key = 0; cudaGraphExec_t exec = nullptr; uint64_t launches = 0; };
+  struct GraphSlot { uint64_t key = 0; cudaGraphExec_t exec = nullptr; uint64_t launches = 0; int seen = 0; };
   GraphSlot g_tile[2];
 
   // Returns a device buffer of at least `bytes` under `name`; reallocates only when growing.
@@ -253,22 +253,30 @@ int msrcr_tiled_run(llie_ctx* const* ctxs, int n_dev, const float* const* in, fl
 template <class F>
 int run_as_graph(llie_ctx* ctx, llie_ctx::GraphSlot& slot, uint64_t key, cudaStream_t st, F&& body) {
   if (ctx->profiling) return body(st);
-  if (!slot.exec || slot.key != key) {
+  if (slot.key != key) {
+    // A sequence is captured the SECOND time it is seen: the first run is plain, so that every kernel in it has been
+    // loaded (the first launch of a function loads its module lazily, which a capture does not allow) and one-off
+    // shapes never pay for an instantiation.
     if (slot.exec) { cudaGraphExecDestroy(slot.exec); slot.exec = nullptr; }
-    const uint64_t l0 = ctx->launches;
-    LLIE_CUDA_OK(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
-    const int rc = body(st);
-    cudaGraph_t graph = nullptr;
-    const cudaError_t e = cudaStreamEndCapture(st, &graph);
-    slot.launches = ctx->launches - l0;
-    ctx->launches = l0;
-    if (rc != LLIE_OK) { if (graph) cudaGraphDestroy(graph); return rc; }
-    if (e != cudaSuccess) { (void)cudaGetLastError(); set_error("graph capture failed: %s", cudaGetErrorString(e)); return LLIE_E_CUDA; }
-    const cudaError_t e2 = cudaGraphInstantiate(&slot.exec, graph, 0);
-    cudaGraphDestroy(graph);
-    if (e2 != cudaSuccess) { (void)cudaGetLastError(); slot.exec = nullptr; set_error("graph instantiate failed: %s", cudaGetErrorString(e2)); return LLIE_E_CUDA; }
     slot.key = key;
+    slot.seen = 1;
+    return body(st);
   }
+  if (!slot.exec && slot.seen == 1) {
+    slot.seen = 2;  // one attempt per key
+    const uint64_t l0 = ctx->launches;
+    if (cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal) == cudaSuccess) {
+      const int rc = body(st);
+      cudaGraph_t graph = nullptr;
+      const cudaError_t e = cudaStreamEndCapture(st, &graph);
+      slot.launches = ctx->launches - l0;
+      ctx->launches = l0;
+      if (rc == LLIE_OK && e == cudaSuccess && graph && cudaGraphInstantiate(&slot.exec, graph, 0) != cudaSuccess) slot.exec = nullptr;
+      if (graph) cudaGraphDestroy(graph);
+    }
+    (void)cudaGetLastError();  // a failed capture is not an error of the call: the sequence then runs as plain launches
+  }
+  if (!slot.exec) return body(st);
   LLIE_CUDA_OK(cudaGraphLaunch(slot.exec, st));
   ctx->launches += slot.launches;
   return LLIE_OK;

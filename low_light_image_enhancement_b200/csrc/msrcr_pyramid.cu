@@ -1084,7 +1084,7 @@ int msrcr_tiled_run(llie_ctx* const* ctxs, int n_dev, const float* const* in, fl
 
   // One PERSISTENT host thread per device (the ctx's HostWorker; the caller's thread drives shard 0): the ~25
   // launches and copies of a device must not serialise behind the other devices', and spawning threads per call
-  // cost more than the whole 8-GPU step.  One rendezvous per call: "every device's C-ready event is recorded".
+  // cost more than the whole 8-GPU step.  Two spin rendezvous per call: "set up" and "C-ready events recorded".
   auto worker = [&](int d) {
     llie_ctx* ctx = ctxs[d];
     auto setup = [&]() -> int {
@@ -1118,6 +1118,9 @@ int msrcr_tiled_run(llie_ctx* const* ctxs, int n_dev, const float* const* in, fl
       }
       ev_c[d] = ctx->tile_event;
       ctx->tile_ms = -1.f;
+      return LLIE_OK;
+    };
+    auto phase_a = [&]() -> int {
       LLIE_CUDA_OK(cudaEventRecord(ctx->tile_t0, ctx->stream));
       LLIE_TRY(tiled_phase_a(ctx, d, n_dev, ctxs, in, rows, geo[d], bufs[d], H, W, p));
       LLIE_CUDA_OK(cudaEventRecord(ev_c[d], ctx->stream));
@@ -1130,8 +1133,10 @@ int msrcr_tiled_run(llie_ctx* const* ctxs, int n_dev, const float* const* in, fl
       }
     };
     rc_a[d] = setup();
+    bar.wait();  // common start; no device allocates (first call, or a larger image) while another one captures a graph
+    if (rc_a[d] == LLIE_OK) rc_a[d] = phase_a();
     fail(rc_a[d]);
-    bar.wait();  // every device's buffers exist and its C-ready event is recorded (or its phase failed)
+    bar.wait();  // every device's C-ready event is recorded (or its phase failed)
     bool ok = true;  // rc_a[] is final after the rendezvous; rc[] is only read by its owner until the end
     for (int e = 0; e < n_dev; ++e) ok = ok && rc_a[e] == LLIE_OK;
     if (ok) fail(tiled_phase_b(ctx, d, n_dev, ctxs, in, out, geo, bufs, ev_c, H, W, p));
