@@ -117,62 +117,109 @@ constexpr int kFirParamTaps = 160;
 struct FirTaps { float t[kFirParamTaps]; };
 constexpr int kFirX8Tile = 128 * kFir8;  // pixels per CTA of fir_x8_kernel
 __host__ __device__ inline int fir8_steps(int r) { return (2 * r + kFir8 + 7) & ~7; }
+// Row addressing as fir_x_kernel, for the flat row index blockIdx.x * kFirXRows + i < total_rows.  Shared memory: two
+// buffers of the clamped input segment, one pad float after every eight (thread g reads element 8 g + u: bank
+// 9 g + ..., conflict-free), then the zero-padded taps.  A CTA walks kFirXRows rows: the next row's samples are
+// loaded into registers before the current row is filtered (ncu on the one-row version: load -> barrier -> compute
+// with nothing to overlap inside a CTA; issue slots 60 % busy at 90 % occupancy).
+constexpr int kFirXRows = 4;
+constexpr int kFirXStage = (kFirX8Tile + 160 + 127) / 128;  // staged floats per thread and row (tile + longest filter)
 __host__ __device__ inline size_t fir_x8_smem(int r) {
   const int seg = kFirX8Tile + fir8_steps(r);
-  return (size_t)(seg + (seg >> 3) + 1 + fir8_steps(r)) * sizeof(float);
+  return (size_t)(2 * (seg + (seg >> 3) + 1) + 4 * 32 * 9 + fir8_steps(r)) * sizeof(float);
 }
-
-// Row addressing as fir_x_kernel.  Shared memory: the clamped input segment, one pad float after every
-// eight (thread g reads element 8 g + u: bank 9 g + ..., conflict-free), then the zero-padded taps.
-template <bool kParamTaps>
+template <bool kParamTaps, int kSteps>
 __global__ void __launch_bounds__(128) fir_x8_kernel(const float* __restrict__ in, float* __restrict__ out,
                                                      const float* __restrict__ taps, int r, int W,
-                                                     int rows_per_plane, int plane_rows, int row_lo,
+                                                     int rows_per_plane, int plane_rows, int row_lo, int total_rows,
                                                      const __grid_constant__ FirTaps ft) {
-  extern __shared__ float seg[];
+  extern __shared__ float seg_all[];
   const int x0 = blockIdx.y * kFirX8Tile;
-  const int pl = blockIdx.x / rows_per_plane;
-  const long long row = (long long)pl * plane_rows + row_lo + (blockIdx.x - pl * rows_per_plane);
-  const float* src = in + row * (long long)W;
-  const int n_steps = fir8_steps(r);
+  const int n_steps = kSteps > 0 ? kSteps : fir8_steps(r);
   const int tile = min(kFirX8Tile, (W - x0 + 7) & ~7);
   const int seg_px = tile + n_steps;
-  float* stap = seg + seg_px + (seg_px >> 3) + 1;
-  for (int i = threadIdx.x; i < seg_px; i += blockDim.x) seg[i + (i >> 3)] = __ldg(src + min(max(x0 - r + i, 0), W - 1));
+  const int seg_stride = kFirX8Tile + n_steps + ((kFirX8Tile + n_steps) >> 3) + 1;
+  float* sout = seg_all + 2 * seg_stride;  // 4 warps x 32 threads x (8 outputs + 1 pad)
+  float* stap = sout + 4 * 32 * 9;
   if constexpr (!kParamTaps)
     for (int i = threadIdx.x; i < n_steps; i += blockDim.x) stap[i] = (i <= 2 * r) ? __ldg(taps + i) : 0.f;
-  __syncthreads();
+  const int ri0 = blockIdx.x * kFirXRows, ri1 = min(ri0 + kFirXRows, total_rows);
+  auto row_of = [&](int ri) -> long long {
+    const int pl = ri / rows_per_plane;
+    return (long long)pl * plane_rows + row_lo + (ri - pl * rows_per_plane);
+  };
+  float st[kFirXStage];
+  auto fetch = [&](int ri) {
+    const float* src = in + row_of(ri) * (long long)W;
+#pragma unroll
+    for (int k = 0; k < kFirXStage; ++k) {
+      const int i = threadIdx.x + k * 128;
+      if (i < seg_px) st[k] = __ldg(src + min(max(x0 - r + i, 0), W - 1));
+    }
+  };
+  fetch(ri0);
   const int g = threadIdx.x;
-  if (g * kFir8 >= tile) return;
-  float acc[kFir8], k[kFir8];
+  for (int ri = ri0; ri < ri1; ++ri) {
+    float* seg = seg_all + ((ri - ri0) & 1) * seg_stride;
 #pragma unroll
-  for (int q = 0; q < kFir8; ++q) acc[q] = 0.f, k[q] = 0.f;
-  const float* sg = seg + g * 9;  // element 8 g of the padded segment
-  for (int u0 = 0; u0 < n_steps; u0 += 8) {
-    const float* sb = sg + u0 + (u0 >> 3);
+    for (int k = 0; k < kFirXStage; ++k) {
+      const int i = threadIdx.x + k * 128;
+      if (i < seg_px) seg[i + (i >> 3)] = st[k];
+    }
+    __syncthreads();
+    if (ri + 1 < ri1) fetch(ri + 1);
+    if ((g & ~31) * kFir8 < tile) {  // whole warps: the store below is warp-cooperative
+      float acc[kFir8], k[kFir8];
 #pragma unroll
-    for (int s = 0; s < 8; ++s) {
-      const float v = sb[s];
-      k[s] = kParamTaps ? ft.t[u0 + s] : stap[u0 + s];
+      for (int q = 0; q < kFir8; ++q) acc[q] = 0.f, k[q] = 0.f;
+      const float* sg = seg + g * 9;  // element 8 g of the padded segment
+      auto block = [&](int u0) {
+        const float* sb = sg + u0 + (u0 >> 3);
 #pragma unroll
-      for (int q = 0; q < kFir8; ++q) acc[q] = fmaf(k[(s - q) & 7], v, acc[q]);
+        for (int s = 0; s < 8; ++s) {
+          const float v = sb[s];
+          k[s] = kParamTaps ? ft.t[u0 + s] : stap[u0 + s];
+#pragma unroll
+          for (int q = 0; q < kFir8; ++q) acc[q] = fmaf(k[(s - q) & 7], v, acc[q]);
+        }
+      };
+      if constexpr (kSteps > 0) {  // compile-time tap count: taps become constant-bank FFMA operands, offsets immediates
+#pragma unroll
+        for (int u0 = 0; u0 < kSteps; u0 += 8) block(u0);
+      } else {
+        for (int u0 = 0; u0 < n_steps; u0 += 8) block(u0);
+      }
+      // a thread's eight outputs are consecutive, so storing them directly would touch 32 sectors per warp store
+      // (4 bytes each): transpose through the warp's strip of shared memory and store whole 128-byte lines instead
+      float* wst = sout + (threadIdx.x >> 5) * (32 * 9);
+      const int l = threadIdx.x & 31;
+#pragma unroll
+      for (int q = 0; q < kFir8; ++q) wst[l * 9 + q] = acc[q];
+      __syncwarp();
+      float* dst = out + row_of(ri) * (long long)W + x0 + (threadIdx.x & ~31) * kFir8;
+#pragma unroll
+      for (int q = 0; q < kFir8; ++q) {
+        const int o = q * 32 + l;  // output o of this warp's 256: thread o / 8, slot o % 8
+        if (x0 + (threadIdx.x & ~31) * kFir8 + o < W) dst[o] = wst[(o >> 3) * 9 + (o & 7)];
+      }
+      __syncwarp();
     }
   }
-  float* dst = out + row * (long long)W + x0 + g * kFir8;
-#pragma unroll
-  for (int q = 0; q < kFir8; ++q)
-    if (x0 + g * kFir8 + q < W) dst[q] = acc[q];
 }
 
 // Row addressing as fir_y_kernel; 8 consecutive rows per thread, one column per lane (coalesced).
-template <bool kParamTaps>
+// kSteps > 0: the number of 8-tap steps is a compile-time constant, so the tap loop unrolls completely and every tap
+// is a constant-bank operand of its FFMA (ncu on the dynamic loop: 1000 instructions per thread for 320 FFMAs --
+// the tap fetch and the 64-bit clamped row address of every load cost more issue slots than the arithmetic; issue
+// slots 81 % busy).  Threads whose whole window lies inside the level (all but the border rows) step a pointer.
+template <bool kParamTaps, int kSteps>
 __global__ void __launch_bounds__(128) fir_y8_kernel(const float* __restrict__ in, float* __restrict__ out,
                                                      const float* __restrict__ taps, int r, int H, int RW,
                                                      int in_row0, int in_rows, int out_row0, int out_rows,
                                                      int out_buf_row0, int out_plane_rows,
                                                      const __grid_constant__ FirTaps ft) {
   extern __shared__ float stap[];
-  const int n_steps = fir8_steps(r);
+  const int n_steps = kSteps > 0 ? kSteps : fir8_steps(r);
   if constexpr (!kParamTaps) {
     for (int i = threadIdx.x; i < n_steps; i += blockDim.x) stap[i] = (i <= 2 * r) ? __ldg(taps + i) : 0.f;
     __syncthreads();
@@ -186,17 +233,22 @@ __global__ void __launch_bounds__(128) fir_y8_kernel(const float* __restrict__ i
   float acc[kFir8], k[kFir8], v[8], vn[8];
 #pragma unroll
   for (int q = 0; q < kFir8; ++q) acc[q] = 0.f, k[q] = 0.f;
-  // The eight samples of the NEXT block are requested before the 64 FFMAs of the current one (the loads come from
-  // L2: without the look-ahead every block of a warp waited out a full round trip with nothing else to issue).
+  const bool interior = y0 - r >= 0 && y0 - r + n_steps - 1 <= H - 1;
+  const float* p = src + (long long)(y0 - r - in_row0) * RW;
+  // the eight samples of the NEXT block are requested before the 64 FFMAs of the current one
   auto load8 = [&](float (&d)[8], int u0) {
+    if (interior) {
 #pragma unroll
-    for (int s = 0; s < 8; ++s) {
-      const int y = min(max(y0 - r + u0 + s, 0), H - 1) - in_row0;
-      d[s] = __ldg(src + (long long)y * RW);
+      for (int s = 0; s < 8; ++s) { d[s] = __ldg(p); p += RW; }
+    } else {
+#pragma unroll
+      for (int s = 0; s < 8; ++s) {
+        const int y = min(max(y0 - r + u0 + s, 0), H - 1) - in_row0;
+        d[s] = __ldg(src + (long long)y * RW);
+      }
     }
   };
-  load8(v, 0);
-  for (int u0 = 0; u0 < n_steps; u0 += 8) {
+  auto block = [&](int u0) {
     if (u0 + 8 < n_steps) load8(vn, u0 + 8);
 #pragma unroll
     for (int s = 0; s < 8; ++s) {
@@ -206,6 +258,13 @@ __global__ void __launch_bounds__(128) fir_y8_kernel(const float* __restrict__ i
     }
 #pragma unroll
     for (int s = 0; s < 8; ++s) v[s] = vn[s];
+  };
+  load8(v, 0);
+  if constexpr (kSteps > 0) {
+#pragma unroll
+    for (int u0 = 0; u0 < kSteps; u0 += 8) block(u0);
+  } else {
+    for (int u0 = 0; u0 < n_steps; u0 += 8) block(u0);
   }
   float* dst = out + (plane * (long long)out_plane_rows + out_buf_row0) * RW + j;
 #pragma unroll

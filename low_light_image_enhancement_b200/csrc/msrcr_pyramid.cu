@@ -568,15 +568,28 @@ FirTaps make_fir_taps(const ScalePlan& sp, bool* fits) {
     for (size_t i = 0; i < sp.taps.size(); ++i) ft.t[i] = sp.taps[i];
   return ft;
 }
+// The tap count of the default scales' filters (radius 16 at stride 4: 40 steps; 25 and 68 at stride 16: 64 and
+// 144) selects a fully unrolled instantiation; anything else takes the dynamic loop.  `r` is the 4th argument.
 template <class... A>
-void launch_fir_x8(bool param, dim3 grid, size_t smem, cudaStream_t st, A... a) {
-  if (param) fir_x8_kernel<true><<<grid, 128, smem, st>>>(a...);
-  else fir_x8_kernel<false><<<grid, 128, smem, st>>>(a...);
+void launch_fir_x8(bool param, dim3 grid, size_t smem, cudaStream_t st, const float* in, float* out, const float* taps,
+                   int r, int W, int rows_per_plane, int plane_rows, int row_lo, const FirTaps& ft) {
+  const int steps = fir8_steps(r), total = (int)grid.x;  // grid.x arrives as the number of rows
+  grid.x = (total + kFirXRows - 1) / kFirXRows;
+  if (!param) fir_x8_kernel<false, 0><<<grid, 128, smem, st>>>(in, out, taps, r, W, rows_per_plane, plane_rows, row_lo, total, ft);
+  else if (steps == 40) fir_x8_kernel<true, 40><<<grid, 128, smem, st>>>(in, out, taps, r, W, rows_per_plane, plane_rows, row_lo, total, ft);
+  else if (steps == 64) fir_x8_kernel<true, 64><<<grid, 128, smem, st>>>(in, out, taps, r, W, rows_per_plane, plane_rows, row_lo, total, ft);
+  else if (steps == 144) fir_x8_kernel<true, 144><<<grid, 128, smem, st>>>(in, out, taps, r, W, rows_per_plane, plane_rows, row_lo, total, ft);
+  else fir_x8_kernel<true, 0><<<grid, 128, smem, st>>>(in, out, taps, r, W, rows_per_plane, plane_rows, row_lo, total, ft);
 }
 template <class... A>
-void launch_fir_y8(bool param, dim3 grid, size_t smem, cudaStream_t st, A... a) {
-  if (param) fir_y8_kernel<true><<<grid, 128, smem, st>>>(a...);
-  else fir_y8_kernel<false><<<grid, 128, smem, st>>>(a...);
+void launch_fir_y8(bool param, dim3 grid, size_t smem, cudaStream_t st, const float* in, float* out, const float* taps,
+                   int r, A... a) {
+  const int steps = fir8_steps(r);
+  if (!param) fir_y8_kernel<false, 0><<<grid, 128, smem, st>>>(in, out, taps, r, a...);
+  else if (steps == 40) fir_y8_kernel<true, 40><<<grid, 128, smem, st>>>(in, out, taps, r, a...);
+  else if (steps == 64) fir_y8_kernel<true, 64><<<grid, 128, smem, st>>>(in, out, taps, r, a...);
+  else if (steps == 144) fir_y8_kernel<true, 144><<<grid, 128, smem, st>>>(in, out, taps, r, a...);
+  else fir_y8_kernel<true, 0><<<grid, 128, smem, st>>>(in, out, taps, r, a...);
 }
 
 template <int N6, int N4>
