@@ -1,7 +1,7 @@
 """Short, deterministic launch sequence for ncu: W warm-up calls + 1 profiled call of one workload.
 
     python tools/prof_run.py dce [frames]     Zero-DCE bf16 on `frames` 1080p frames (default 8)
-    python tools/prof_run.py msrcr [frames]   MSRCR on `frames` 4K frames (default 8)
+    python tools/prof_run.py msrcr [frames]   MSRCR on `frames` 4K frames (default 8); msrcr_u8: the same on uint8 images
     python tools/prof_run.py dce32            Zero-DCE fp32 on one 1080p frame
 Prints the number of kernel launches per call so that `ncu -s` can skip the warm-up.
 """
@@ -22,8 +22,10 @@ def main():
     warm = int(os.environ.get("PROF_WARMUP", "1"))
     dev = torch.device("cuda", 0)
     enh = _enhancer(0)
-    if what == "msrcr":
+    if what in ("msrcr", "msrcr_u8"):
         x = synth_lowlight_batch(frames, 2160, 3840, seed=3000, device=dev)
+        if what == "msrcr_u8":
+            x = (x * 255.0).round().clamp(0, 255).to(torch.uint8)
         method, params = "msrcr", None
     elif what == "dce32":
         x = synth_lowlight_batch(1, 1080, 1920, seed=1000, device=dev)
