@@ -144,49 +144,73 @@ down4_rows_kernel(const TIn* __restrict__ x, long long plane_stride, int RW, int
 // V[plane][jy][px*CS + c] -> C[(plane*CS + c)][jy][jx] = a * sum_t g[t] V[..][clamp(4(jx-PC)+t-16)] + b.
 // A CTA stages one row segment (edge-clamped) in shared memory; thread jx reads its 33*CS words as
 // aligned 128-bit shared loads (48-byte lane stride for CS = 3: bank-conflict free).
+// A CTA walks kColsRows consecutive V rows; the next row's segment is requested (into registers) before the current
+// one is filtered, and two shared-memory buffers alternate (ncu on the one-row version: load -> barrier -> filter with
+// nothing to overlap inside a CTA; `long_scoreboard` 15.8 warps per issued instruction).
+constexpr int kColsRows = 4;
 template <int CS>
 __global__ void __launch_bounds__(128)
 down4_cols_kernel(const float* __restrict__ V, float* __restrict__ Cout, int RW, int W, int hC, int wC,
-                  int row_begin, float a, float b) {
+                  int row_begin, int row_end, float a, float b) {
   constexpr int kSegPx = 4 * 128 + 2 * kRD + 4;  // pixels staged (a little padding for the last vector)
-  __shared__ __align__(16) float seg[kSegPx * CS];
-  const int jy = row_begin + blockIdx.y;
+  constexpr int kSegVec = kSegPx * CS / 4, kPerThread = (kSegVec + 127) / 128;
+  __shared__ __align__(16) float seg2[2][kSegPx * CS];
+  static_assert((kSegPx * CS) % 4 == 0, "segment must be a whole number of float4");
+  const int jy0 = row_begin + blockIdx.y * kColsRows, jy1 = min(jy0 + kColsRows, row_end);
   const long long plane = blockIdx.z;
   const int jx0 = blockIdx.x * 128;
   const int px0 = 4 * (jx0 - kPC) - kRD;
-  const float* src = V + (plane * hC + jy) * (long long)RW;
-  static_assert((kSegPx * CS) % 4 == 0, "segment must be a whole number of float4");
-  if (px0 >= 0 && px0 + kSegPx <= W && (RW & 3) == 0) {
-    // interior segment: contiguous and 16-byte aligned (px0 * CS is a multiple of 32 floats) -> 128-bit copies
-    const float4* s4 = reinterpret_cast<const float4*>(src + (long long)px0 * CS);
-    for (int i = threadIdx.x; i < kSegPx * CS / 4; i += 128) reinterpret_cast<float4*>(seg)[i] = __ldg(s4 + i);
-  } else {
-    for (int i = threadIdx.x; i < kSegPx * CS; i += 128) {
-      const int px = i / CS, c = i - px * CS;
-      const int xx = min(max(px0 + px, 0), W - 1);
-      seg[i] = __ldg(src + xx * CS + c);
+  // interior segment: contiguous and 16-byte aligned (px0 * CS is a multiple of 32 floats) -> 128-bit copies
+  const bool fast = px0 >= 0 && px0 + kSegPx <= W && (RW & 3) == 0;
+  float4 st[kPerThread];
+  auto fetch = [&](int jy) {
+    const float4* s4 = reinterpret_cast<const float4*>(V + (plane * hC + jy) * (long long)RW + (long long)px0 * CS);
+#pragma unroll
+    for (int k = 0; k < kPerThread; ++k) {
+      const int i = threadIdx.x + k * 128;
+      if (i < kSegVec) st[k] = __ldg(s4 + i);
+    }
+  };
+  if (fast) fetch(jy0);
+  const int jx = jx0 + threadIdx.x;
+  for (int jy = jy0; jy < jy1; ++jy) {
+    float* seg = seg2[(jy - jy0) & 1];
+    if (fast) {
+#pragma unroll
+      for (int k = 0; k < kPerThread; ++k) {
+        const int i = threadIdx.x + k * 128;
+        if (i < kSegVec) reinterpret_cast<float4*>(seg)[i] = st[k];
+      }
+    } else {
+      const float* src = V + (plane * hC + jy) * (long long)RW;
+      for (int i = threadIdx.x; i < kSegPx * CS; i += 128) {
+        const int px = i / CS, c = i - px * CS;
+        const int xx = min(max(px0 + px, 0), W - 1);
+        seg[i] = __ldg(src + xx * CS + c);
+      }
+    }
+    __syncthreads();
+    if (fast && jy + 1 < jy1) fetch(jy + 1);
+    if (jx < wC) {
+      constexpr int kWords = 33 * CS, kVecs = (kWords + 3) / 4;
+      const float4* s4 = reinterpret_cast<const float4*>(seg + 4 * threadIdx.x * CS);
+      float w[kVecs * 4];
+#pragma unroll
+      for (int i = 0; i < kVecs; ++i) {
+        const float4 t = s4[i];
+        w[4 * i] = t.x; w[4 * i + 1] = t.y; w[4 * i + 2] = t.z; w[4 * i + 3] = t.w;
+      }
+      float acc[CS];
+#pragma unroll
+      for (int c = 0; c < CS; ++c) acc[c] = 0.f;
+#pragma unroll
+      for (int t = 0; t <= 2 * kRD; ++t)
+#pragma unroll
+        for (int c = 0; c < CS; ++c) acc[c] = fmaf(gd(t), w[t * CS + c], acc[c]);
+#pragma unroll
+      for (int c = 0; c < CS; ++c) Cout[((plane * CS + c) * hC + jy) * (long long)wC + jx] = fmaf(a, acc[c], b);
     }
   }
-  __syncthreads();
-  const int jx = jx0 + threadIdx.x;
-  if (jx >= wC) return;
-  constexpr int kWords = 33 * CS, kVecs = (kWords + 3) / 4;
-  const float4* s4 = reinterpret_cast<const float4*>(seg + 4 * threadIdx.x * CS);
-  float w[kVecs * 4];
-#pragma unroll
-  for (int i = 0; i < kVecs; ++i) {
-    const float4 t = s4[i];
-    w[4 * i] = t.x; w[4 * i + 1] = t.y; w[4 * i + 2] = t.z; w[4 * i + 3] = t.w;
-  }
-  float acc[CS];
-#pragma unroll
-  for (int c = 0; c < CS; ++c) acc[c] = 0.f;
-#pragma unroll
-  for (int t = 0; t <= 2 * kRD; ++t)
-#pragma unroll
-    for (int c = 0; c < CS; ++c) acc[c] = fmaf(gd(t), w[t * CS + c], acc[c]);
-#pragma unroll
-  for (int c = 0; c < CS; ++c) Cout[((plane * CS + c) * hC + jy) * (long long)wC + jx] = fmaf(a, acc[c], b);
 }
 
 // ---- level C -> level B: prefilter + decimate by 4 (same 33-tap Gaussian, in C samples) ---------
