@@ -558,11 +558,16 @@ __device__ __forceinline__ void final_store(uint16_t* __restrict__ o, const ImgV
 // kEqW: all scale weights are equal (the default 1/3, 1/3, 1/3), so sum_k w lg2 S_k = w lg2(prod_k S_k): one MUFU.LG2
 // per pixel-channel instead of one per scale (13 -> 7 per pixel; the XU pipe, 16 lanes/clk/SM, was ~50 % of the
 // kernel's time).  S_k <= in_scale + in_bias, so the product of up to three stays far inside fp32 range.
-template <int N6, int N4, typename TIO, bool kEqW>
+// kIo >= 0: the I/O layout (kIoNhwcVec / kIoNchwVec) is a compile-time constant and there are no partial sums from /
+// for another pass (the default call: one launch, vector I/O) -- the other layouts' load / store code and the
+// acc_in / acc_out branches leave the row loop.  kIo = -1: everything decided at run time.
+template <int N6, int N4, typename TIO, bool kEqW, int kIo = -1>
 __global__ void __launch_bounds__(128, 5)
-msrcr_final_kernel(const TIO* __restrict__ x, TIO* __restrict__ out, ImgView v, int io, int W, int in_row0,
+msrcr_final_kernel(const TIO* __restrict__ x, TIO* __restrict__ out, ImgView v, int io_rt, int W, int in_row0,
                    int row_begin, int row_end, int rows_per_strip, const __grid_constant__ FinalParams p) {
   constexpr int NV = 3 * (N6 + N4);
+  const int io = kIo >= 0 ? kIo : io_rt;
+  constexpr bool kAcc = kIo < 0;  // partial sums in / out possible
   __shared__ float s_v[2][4][NV][128];
   const int t = threadIdx.x;
   const long long img = blockIdx.z;
@@ -655,7 +660,7 @@ msrcr_final_kernel(const TIO* __restrict__ x, TIO* __restrict__ out, ImgView v, 
         float f[4][3], acc[4][3];
         if (Y + 2 < ye) final_prefetch(x, v, io, img, yl + 2, X0);  // two rows ahead: one row is shorter than the DRAM latency
         final_load(x, v, io, img, yl, X0, W, f);
-        if (p.acc_in) {
+        if (kAcc && p.acc_in) {
           final_load(p.acc_in, v, io, img, yl, X0, W, acc);
         } else {
 #pragma unroll
@@ -710,7 +715,7 @@ msrcr_final_kernel(const TIO* __restrict__ x, TIO* __restrict__ out, ImgView v, 
 #pragma unroll
             for (int c = 0; c < 3; ++c) acc[i][c] = fmaf(p.w2[0], lg2_ge1(prod[i][c]), acc[i][c]);
         }
-        if (p.acc_out) {
+        if (kAcc && p.acc_out) {
           final_store(p.acc_out, v, io, img, yl, X0, W, acc);
         } else {
           float o[4][3];

@@ -598,6 +598,23 @@ void launch_final(dim3 grid, cudaStream_t st, const void* x, void* out, int iot,
   // eq: equal weights over the maps of this launch and values bounded so that their product stays a normal fp32
   // number (decided by final_passes, which knows the exponents inside the combined stride-16 map)
   for (int i = 1; i < N6 + N4; ++i) eq = eq && fp.w2[i] == fp.w2[0];
+  if constexpr (N6 == 1 && N4 == 1) {
+    // the default call (equal weights, one pass, vector I/O): layout-specialised instantiations
+    if (eq && !fp.acc_in && !fp.acc_out && (io == kIoNhwcVec || io == kIoNchwVec)) {
+      const bool nhwc = io == kIoNhwcVec;
+      if (iot == kIoU16) {
+        if (nhwc) msrcr_final_kernel<1, 1, uint16_t, true, kIoNhwcVec><<<grid, 128, 0, st>>>((const uint16_t*)x, (uint16_t*)out, v, io, W, in_row0, row_begin, row_end, rps, fp);
+        else msrcr_final_kernel<1, 1, uint16_t, true, kIoNchwVec><<<grid, 128, 0, st>>>((const uint16_t*)x, (uint16_t*)out, v, io, W, in_row0, row_begin, row_end, rps, fp);
+      } else if (iot == kIoU8) {
+        if (nhwc) msrcr_final_kernel<1, 1, uint8_t, true, kIoNhwcVec><<<grid, 128, 0, st>>>((const uint8_t*)x, (uint8_t*)out, v, io, W, in_row0, row_begin, row_end, rps, fp);
+        else msrcr_final_kernel<1, 1, uint8_t, true, kIoNchwVec><<<grid, 128, 0, st>>>((const uint8_t*)x, (uint8_t*)out, v, io, W, in_row0, row_begin, row_end, rps, fp);
+      } else {
+        if (nhwc) msrcr_final_kernel<1, 1, float, true, kIoNhwcVec><<<grid, 128, 0, st>>>((const float*)x, (float*)out, v, io, W, in_row0, row_begin, row_end, rps, fp);
+        else msrcr_final_kernel<1, 1, float, true, kIoNchwVec><<<grid, 128, 0, st>>>((const float*)x, (float*)out, v, io, W, in_row0, row_begin, row_end, rps, fp);
+      }
+      return;
+    }
+  }
   if (iot == kIoU16) {
     if (eq) msrcr_final_kernel<N6, N4, uint16_t, true><<<grid, 128, 0, st>>>((const uint16_t*)x, (uint16_t*)out, v, io, W, in_row0, row_begin, row_end, rps, fp);
     else msrcr_final_kernel<N6, N4, uint16_t, false><<<grid, 128, 0, st>>>((const uint16_t*)x, (uint16_t*)out, v, io, W, in_row0, row_begin, row_end, rps, fp);
