@@ -868,3 +868,38 @@ def test_tiled_and_sharded_outputs_stay_inside_their_buffers(blob):
         L.enhance(xs, method, prm, devices=[0, 0], out=[y for _, y, _ in gs])
         for i, (buf, y, g) in enumerate(gs):
             _assert_guards(buf, g, f"sharded {method} slot {i}")
+
+
+# ---------------------------------------------------------------- fp32-path corner cases
+@pytest.mark.parametrize("prec", ["fp32", "fp32_simt"])
+def test_dce_fp32_tanh_saturation(prec):
+    """conv7 x 64: most curve maps saturate at +-1, where the epilogue's tanh (1 - 2 / (e^{2v} + 1) with __expf) has
+    to saturate cleanly -- e^{2v} overflows to +inf for v > 44 and must still give exactly 1."""
+    ws = oracle.init_weights(3)
+    ws[6] = (ws[6][0] * np.float32(64.0), ws[6][1] * np.float32(64.0))
+    x = np.clip(oracle.synth_lowlight(96, 144, 8) * 6.0, 0, 1).astype(np.float32)
+    ref, maps = oracle.zero_dce(x, ws, return_maps=True)
+    assert float(np.mean(np.abs(maps) > 0.999)) > 0.2   # the case does saturate
+    y = L.enhance(x, "zero_dce", dict(weights=oracle.pack_weights(ws), precision=prec))
+    assert np.isfinite(y).all()
+    # a saturated map amplifies nothing, but near the knee d tanh / dv = 1 multiplies the (64 x larger) conv7 error
+    assert np.abs(y - ref).max() <= (2e-3 if prec == "fp32" else 2e-4), float(np.abs(y - ref).max())
+    big = np.full((32, 48, 3), 0.5, np.float32)
+    wz = [(np.zeros_like(w), np.zeros_like(b)) for w, b in ws]
+    for bias in (60.0, -60.0):   # alpha = tanh(+-60) = +-1 exactly
+        wz[6] = (wz[6][0], np.full_like(wz[6][1], bias))
+        yb = L.enhance(big, "zero_dce", dict(weights=oracle.pack_weights(wz), precision=prec))
+        assert np.abs(yb - oracle.zero_dce(big, wz)).max() <= 1e-6, bias
+
+
+def test_msrcr_extreme_affine_map():
+    """I = in_scale x + in_bias far from 255 x + 1: the product of the surrounds no longer fits fp32, so the final
+    kernel must take one lg2 per map (product_ok), and the combined stride-16 map must not be formed."""
+    x = oracle.synth_lowlight(120, 168, 9)
+    for in_scale, in_bias in ((3e11, 2e-11), (1e-9, 1e-10), (1e18, 1.0)):
+        prm = dict(in_scale=in_scale, in_bias=in_bias, gain=0.02)
+        y = L.enhance(x, "msrcr", prm)
+        assert np.abs(y - oracle.msrcr(x, prm)).max() <= TOL_F32, (in_scale, in_bias, float(np.abs(y - oracle.msrcr(x, prm)).max()))
+    for bad in (dict(in_bias=1e-35), dict(in_bias=0.0), dict(in_scale=1e35), dict(in_scale=-1.0)):
+        with pytest.raises(L.LlieError):
+            L.enhance(x, "msrcr", bad)
