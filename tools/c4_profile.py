@@ -7,7 +7,8 @@ import torch
 import low_light_image_enhancement_b200 as L
 from low_light_image_enhancement_b200.api import msrcr_tiled_last_ms, _tile_enhancer
 from low_light_image_enhancement_b200.synth import synth_lowlight_batch
-H = W = int(os.environ.get("C4_SIZE", "16384"))
+H = int(os.environ.get("C4_H", "16384"))
+W = int(os.environ.get("C4_W", "16384"))   # C4_H=4096 on 2 GPUs gives the 2048-row shards of the 8-GPU run
 g = torch.cuda.device_count()
 parts = L.tile_rows(H, g)
 shards, outs = [], []
