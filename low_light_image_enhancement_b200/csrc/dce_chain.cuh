@@ -35,6 +35,10 @@ constexpr int kBTile = 96 * 16 * 2;       // weight tile of one (dx, k16): N=96 
 constexpr int kBPlane = 96 * 16;          // bytes between the two K halves of a weight tile
 constexpr int kPadL = 4;                  // activation column of image pixel x is x + kPadL
 constexpr int kMaxStages = 3;
+#ifndef LLIE_OVF
+#define LLIE_OVF 0
+#endif
+constexpr int kOvf = LLIE_OVF;
 constexpr int kFirstEpiWarp = 4;           // issuer warps + producer warps <= 4
 
 // One input of a stage: `ext` = loaded from HBM by a producer warp (chunks = 1: the packed network
@@ -42,11 +46,23 @@ constexpr int kFirstEpiWarp = 4;           // issuer warps + producer warps <= 4
 // stage's epilogue writes (4 chunks).
 struct Src { int ext, chunks, depth; };
 struct Stage { int nsrc; Src src[2]; int first, last; };
-struct Group { int S; Stage st[kMaxStages]; int lag, slots; int split; };
+struct Group { int S; Stage st[kMaxStages]; int lag, slots; int split; int ovf; };
 // split = 1: the fp32-accurate path.  Every activation is stored as TWO bf16 tensors, hi = bf16(v) and
 // lo = bf16(v - hi) (8 chunk planes per 32 channels: hi 0..3, lo 4..7), every weight likewise, and a
 // product a*w is evaluated as a_hi*w_hi + a_lo*w_hi + a_hi*w_lo (three MMAs, fp32 accumulation in TMEM);
 // the dropped terms are O(2^-16) relative per product (measured: 1e-5 max-abs on the output).
+//
+// ovf = 1 (build with -DLLIE_OVF=1): "overflow slots".  With a plain ring of `slots` accumulator slots, the N = 96 MMA
+// of an input row whose three output rows straddle the end of the ring has to be split into two MMAs (measured: 106
+// cycles for the N=64 + N=32 pair against 56 for one N=96; 2 rows in every `slots`).  Instead each stage gets
+// slots + 2 physical slots [P0 | P1 .. P_slots | P_slots+1]; output row y (ABSOLUTE image row) lives in
+// P_{1 + y % slots}, and an MMA centred on input row r always writes the three consecutive physical slots starting at
+// r % slots.  The last tap of a row with y % slots == slots-1 therefore lands in P0 and the first tap of a row with
+// y % slots == 0 in P_slots+1; the epilogue adds the two partial sums of such rows.  Which rows are split depends only
+// on y, so results do not depend on how frames are batched or cut into units.  Slots are keyed by y, so across units
+// their order of use is irregular: the issuer and each epilogue group keep one parity bit per slot, and a slot always
+// belongs to the same epilogue group (rows go to groups by the parity of y; `slots` is even) -- a group that skipped
+// uses of a slot would wait on it with the parity of a phase that has not begun.
 
 // G1 = conv1+conv2+conv3, G2 = conv4+conv5, G3 = conv6+conv7; P* = single layers (same kernel, S=1).
 __host__ __device__ constexpr Group group_cfg(int id) {
@@ -54,17 +70,19 @@ __host__ __device__ constexpr Group group_cfg(int id) {
     case 0: return Group{3, {Stage{1, {Src{1, 1, 8}, Src{0, 0, 0}}, 1, 0}, Stage{1, {Src{0, 4, 6}, Src{0, 0, 0}}, 0, 0},
                              Stage{1, {Src{0, 4, 6}, Src{0, 0, 0}}, 0, 0}}, 3, 5};
     case 1: return Group{2, {Stage{1, {Src{1, 4, 6}, Src{0, 0, 0}}, 0, 0}, Stage{2, {Src{1, 4, 4}, Src{0, 4, 6}}, 0, 0},
-                             Stage{0, {Src{0, 0, 0}, Src{0, 0, 0}}, 0, 0}}, 3, 8};
+                             Stage{0, {Src{0, 0, 0}, Src{0, 0, 0}}, 0, 0}}, 3, kOvf ? 6 : 8, 0, kOvf};
     case 2: return Group{2, {Stage{1, {Src{1, 8, 4}, Src{0, 0, 0}}, 0, 0}, Stage{2, {Src{1, 4, 4}, Src{0, 4, 5}}, 0, 1},
-                             Stage{0, {Src{0, 0, 0}, Src{0, 0, 0}}, 0, 0}}, 2, 8};
+                             Stage{0, {Src{0, 0, 0}, Src{0, 0, 0}}, 0, 0}}, 2, kOvf ? 6 : 8, 0, kOvf};
     case 3: return Group{1, {Stage{1, {Src{1, 1, 8}, Src{0, 0, 0}}, 1, 0}, Stage{0, {Src{0, 0, 0}, Src{0, 0, 0}}, 0, 0},
                              Stage{0, {Src{0, 0, 0}, Src{0, 0, 0}}, 0, 0}}, 2, 16};  // conv1 alone
     case 4: return Group{1, {Stage{1, {Src{1, 4, 8}, Src{0, 0, 0}}, 0, 0}, Stage{0, {Src{0, 0, 0}, Src{0, 0, 0}}, 0, 0},
                              Stage{0, {Src{0, 0, 0}, Src{0, 0, 0}}, 0, 0}}, 2, 16};  // a 32 -> 32 layer alone
     case 5: return Group{1, {Stage{1, {Src{1, 8, 8}, Src{0, 0, 0}}, 0, 0}, Stage{0, {Src{0, 0, 0}, Src{0, 0, 0}}, 0, 0},
-                             Stage{0, {Src{0, 0, 0}, Src{0, 0, 0}}, 0, 0}}, 2, 16};  // a 64 -> 32 layer alone
+                             Stage{0, {Src{0, 0, 0}, Src{0, 0, 0}}, 0, 0}}, 2, kOvf ? 6 : 16, 0, kOvf};  // a 64 -> 32 layer alone (summed as in its chain)
     case 6: return Group{1, {Stage{1, {Src{1, 8, 8}, Src{0, 0, 0}}, 0, 1}, Stage{0, {Src{0, 0, 0}, Src{0, 0, 0}}, 0, 0},
-                             Stage{0, {Src{0, 0, 0}, Src{0, 0, 0}}, 0, 0}}, 2, 16};  // conv7 alone
+                             Stage{0, {Src{0, 0, 0}, Src{0, 0, 0}}, 0, 0}}, 2, kOvf ? 6 : 16, 0, kOvf};  // conv7 alone (as fused)
+    case 11: return Group{1, {Stage{1, {Src{1, 4, 8}, Src{0, 0, 0}}, 0, 0}, Stage{0, {Src{0, 0, 0}, Src{0, 0, 0}}, 0, 0},
+                              Stage{0, {Src{0, 0, 0}, Src{0, 0, 0}}, 0, 0}}, 2, kOvf ? 6 : 16, 0, kOvf};  // conv4 alone (as fused in conv4+5)
     // ---- split (hi/lo) single layers: chunks count hi AND lo planes
     case 7: return Group{1, {Stage{1, {Src{1, 1, 8}, Src{0, 0, 0}}, 1, 0}, Stage{0, {Src{0, 0, 0}, Src{0, 0, 0}}, 0, 0},
                              Stage{0, {Src{0, 0, 0}, Src{0, 0, 0}}, 0, 0}}, 2, 16, 1};  // conv1
@@ -117,6 +135,7 @@ __host__ __device__ constexpr int ring_bar_index(const Group& g, int s, int j) {
   return o;
 }
 __host__ __device__ constexpr int acc_bar_index(const Group& g, int s) { return ring_bar_index(g, g.S, 0) + 2 * g.slots * s; }
+__host__ __device__ constexpr int phys_slots(const Group& g) { return g.slots + (g.ovf ? 2 : 0); }  // per stage, in TMEM
 __host__ __device__ constexpr int n_bars(const Group& g) { return acc_bar_index(g, g.S) + 1; }
 __host__ __device__ constexpr int smem_bytes(const Group& g) { return bar_offset(g) + 8 * n_bars(g) + 16; }
 __host__ __device__ constexpr int producer_index(const Group& g, int s, int j) {  // which producer warp feeds ring (s, j)
@@ -129,8 +148,14 @@ __host__ __device__ constexpr int producer_index(const Group& g, int s, int j) {
   return o;
 }
 __host__ __device__ constexpr int valid_px(const Group& g) { return kTileX - 2 * (g.S - 1); }
-constexpr int kEpiGroups = 2;             // epilogue groups per stage; they alternate output rows
-__host__ __device__ constexpr int n_threads(const Group& g) { return (kFirstEpiWarp + 4 * kEpiGroups * g.S) * 32; }
+// Epilogue groups (of four warps) per stage; they take the output rows round-robin.  Two.  (With overflow slots a
+// slot must always belong to one group: rows go by y % groups and `slots` is a multiple of it.  Three groups were
+// measured with the overflow slots -- 896 threads, 72 registers, small spills -- and were slower: conv4-5 +9 %.)
+#ifndef LLIE_OVF_GROUPS
+#define LLIE_OVF_GROUPS 2
+#endif
+__host__ __device__ constexpr int epi_groups(const Group& g) { return g.ovf ? LLIE_OVF_GROUPS : 2; }
+__host__ __device__ constexpr int n_threads(const Group& g) { return (kFirstEpiWarp + 4 * epi_groups(g) * g.S) * 32; }
 
 struct ChainArgs {
   const __nv_bfloat16* ext[kMaxStages][2][2];  // [stage][src][tensor]: HBM inputs of external rings
@@ -284,7 +309,15 @@ __device__ __forceinline__ void producer_loop(const ChainArgs& a, const Smem<GID
 // ---- MMA issue of stage S_: a software-pipelined walk over (unit, input row) -----------------------
 // oc = output rows of this stage started before the current unit (position in the TMEM slot ring);
 // rc = ring rows consumed so far (the same for every source of a stage); r = absolute input row.
-struct RowIt { int u; StageRows sr; int r; uint32_t oc, rc; bool valid; };
+struct RowIt { int u; StageRows sr; int r; uint32_t oc, rc; bool valid; uint32_t fmask; };
+// (ovf) fmask bit j = parity of the next wait on acc_free[j]; a slot's parity flips each time a row first touches it.
+
+// (ovf) output rows input row r touches for the first time: all of its rows for the first input row of a unit,
+// otherwise the row below it.
+__device__ __forceinline__ void first_touch(const StageRows& sr, int r, int& a, int& b) {
+  a = (r == sr.in_lo) ? max(r - 1, sr.ys) : r + 1;
+  b = min(r + 1, sr.ye - 1);
+}
 
 template <int GID, int S_>
 __device__ __forceinline__ void row_begin_unit(const ChainArgs& a, RowIt& it) {
@@ -298,6 +331,11 @@ __device__ __forceinline__ void row_begin_unit(const ChainArgs& a, RowIt& it) {
 }
 template <int GID, int S_>
 __device__ __forceinline__ void row_advance(const ChainArgs& a, RowIt& it) {
+  if constexpr (group_cfg(GID).ovf != 0) {
+    int fa, fb;
+    first_touch(it.sr, it.r, fa, fb);
+    for (int o = fa; o <= fb; ++o) it.fmask ^= 1u << (o % group_cfg(GID).slots);
+  }
   ++it.rc;
   if (++it.r == it.sr.in_hi) {
     it.oc += it.sr.ye - it.sr.ys;
@@ -322,9 +360,15 @@ __device__ __forceinline__ bool row_ready(const Smem<GID>& sm, const RowIt& it) 
   const int lo = max(rr - 1, 0), hi = min(rr + 1, rows - 1);
   uint64_t* acc_free = sm.template acc_free<S_>();
   bool ok = true;
-  for (int o = (it.r == it.sr.in_lo) ? lo : rr + 1; o <= hi; ++o) {
-    const uint32_t og = it.oc + o;
-    ok = check(&acc_free[og % NS], (og / NS) & 1) && ok;
+  if constexpr (G.ovf != 0) {
+    int fa, fb;
+    first_touch(it.sr, it.r, fa, fb);
+    for (int o = fa; o <= fb; ++o) ok = check(&acc_free[o % NS], (it.fmask >> (o % NS)) & 1) && ok;
+  } else {
+    for (int o = (it.r == it.sr.in_lo) ? lo : rr + 1; o <= hi; ++o) {
+      const uint32_t og = it.oc + o;
+      ok = check(&acc_free[og % NS], (og / NS) & 1) && ok;
+    }
   }
   ok = check(&sm.template ring_full<S_, 0>()[it.rc % kD0], (it.rc / kD0) & 1) && ok;
   if constexpr (T.nsrc > 1) ok = check(&sm.template ring_full<S_, (T.nsrc > 1 ? 1 : 0)>()[it.rc % kD1], (it.rc / kD1) & 1) && ok;
@@ -367,7 +411,7 @@ __device__ __forceinline__ void issue_row(const Smem<GID>& sm, uint32_t tmem, co
     // part 0 = the horizontal tap dx = 0, part 1 = dx = 1, 2 (conv1: its first / remaining MMAs).
     auto issue = [&](uint32_t s0, int cnt, int dyslot, int part) {
       const uint32_t idesc = idesc_bf16_m128(32 * cnt);
-      const uint32_t d = tmem + (S_ * NS + s0) * 32;
+      const uint32_t d = tmem + (S_ * phys_slots(G) + s0) * 32;
       const uint64_t b_row = b_desc0 + (uint64_t)(dyslot * (512 >> 4));
       if constexpr (kFirst) {
         if (part == 0) {
@@ -406,8 +450,9 @@ __device__ __forceinline__ void issue_row(const Smem<GID>& sm, uint32_t tmem, co
         }
       }
     };
-    const uint32_t s0 = (ocnt + lo) % NS;
-    const int cnt = hi - lo + 1, c1 = min(cnt, NS - (int)s0), dyslot = lo - (rr - 1);
+    // ovf: physical slot r % NS + dyslot, three consecutive slots never wrap; else the ring may wrap (two MMAs)
+    const uint32_t s0 = G.ovf ? (uint32_t)(r % NS) + (uint32_t)(lo - (rr - 1)) : (ocnt + lo) % NS;
+    const int cnt = hi - lo + 1, c1 = G.ovf ? cnt : min(cnt, NS - (int)s0), dyslot = lo - (rr - 1);
     issue(s0, c1, dyslot, 0);
     if (c1 < cnt) issue(0, cnt - c1, dyslot + c1, 0);  // the slot ring wrapped
     // short rows (<= 6 MMAs) gain nothing from the early probe (measured: conv1-3 chain 6.8 -> 7.2 ms with it)
@@ -418,8 +463,8 @@ __device__ __forceinline__ void issue_row(const Smem<GID>& sm, uint32_t tmem, co
     mma_commit(&sm.template ring_empty<S_, 0>()[slot0]);
     if constexpr (kNsrc > 1) mma_commit(&sm.template ring_empty<S_, (kNsrc > 1 ? 1 : 0)>()[slot1]);
     // output row rr-1 has now received its last tap; at the bottom image border so has row rr
-    if (rr >= 1) mma_commit(&acc_ready[(ocnt + rr - 1) % NS]);
-    if (r == sr.in_hi - 1 && rr == rows - 1) mma_commit(&acc_ready[(ocnt + rr) % NS]);
+    if (rr >= 1) mma_commit(&acc_ready[G.ovf ? (uint32_t)((r - 1) % NS) : (ocnt + rr - 1) % NS]);
+    if (r == sr.in_hi - 1 && rr == rows - 1) mma_commit(&acc_ready[G.ovf ? (uint32_t)(r % NS) : (ocnt + rr) % NS]);
     if (!nxt_ready) row_ready<GID, S_, true>(sm, nxt);
   }
   __syncwarp();
@@ -439,11 +484,12 @@ __device__ __forceinline__ void epilogue_loop(const ChainArgs& a, const Smem<GID
   uint64_t* acc_ready = sm.template acc_ready<S_>();
   uint64_t* acc_free = sm.template acc_free<S_>();
   const uint32_t lane_base = (uint32_t)(q * 32) << 16;
-  const uint32_t tcol = tmem + lane_base + S_ * NS * 32;
+  constexpr bool kOvfS = G.ovf != 0;
+  const uint32_t tcol = tmem + lane_base + S_ * phys_slots(G) * 32;
   // Accumulator slots start from zero (the bias is added below, from the constant bank); a drained
   // slot is re-zeroed with a single-register tcgen05.st.  Group 0 initialises every slot once.
   if (g == 0) {
-    for (int s = 0; s < NS; ++s) tmem_fill32(tcol + s * 32, 0u);
+    for (int s = 0; s < phys_slots(G); ++s) tmem_fill32(tcol + s * 32, 0u);
     tmem_wait_st();
     tc_fence_before();
     __syncwarp();
@@ -452,6 +498,7 @@ __device__ __forceinline__ void epilogue_loop(const ChainArgs& a, const Smem<GID
   }
   const int m = q * 32 + lane;  // this thread's pixel of the 128-pixel tile
   uint32_t ocnt = 0;            // running output-row counter (same sequence as the issuer's)
+  uint32_t rmask = 0;           // (ovf) bit j = parity of this group's next wait on acc_ready[j] (its own slots only)
   for (int u = blockIdx.x; u < a.units; u += gridDim.x) {
     const Unit un = decode_unit(a, u);
     const StageRows sr = stage_rows(un.ys, un.ye, a.H, L, S_);
@@ -460,15 +507,39 @@ __device__ __forceinline__ void epilogue_loop(const ChainArgs& a, const Smem<GID
     // the strip owns kValid columns of the last stage's output; earlier stages own the same columns
     const bool owned = in_img && m >= (L - S_) && m < (L - S_) + kValid;
     const int rows = sr.ye - sr.ys;
-    for (int i = (g ^ ocnt) & 1; i < rows; i += 2) {  // group g owns the output rows with (counter & 1) == g
+    // plain ring: group g owns the output rows with (counter & 1) == g; ovf: the rows with y % EG == g
+    constexpr int EG = epi_groups(G);
+    static_assert(!kOvfS || NS % EG == 0, "a slot must always belong to the same epilogue group");
+    for (int i = kOvfS ? ((g - sr.ys % EG + EG) % EG) : ((g ^ ocnt) & 1); i < rows; i += EG) {
       const uint32_t og = ocnt + i;
-      const int y = sr.ys + i, s = og % NS;
-      mbar_wait(&acc_ready[s], (og / NS) & 1);
-      tc_fence_after();
+      const int y = sr.ys + i, s = kOvfS ? y % NS : og % NS;
       uint32_t v[32];
-      tmem_ld32(tcol + s * 32, v);
-      tmem_wait_ld();
-      tmem_fill32(tcol + s * 32, 0u);
+      if constexpr (kOvfS) {
+        const uint32_t par = (rmask >> s) & 1;
+        rmask ^= 1u << s;
+        mbar_wait(&acc_ready[s], par);
+        tc_fence_after();
+        tmem_ld32(tcol + (s + 1) * 32, v);
+        if (s == 0 || s == NS - 1) {
+          // the row's first tap (s == 0) / last tap (s == NS-1) went to the overflow slot: add the partial sums
+          const uint32_t xcol = tcol + (s == 0 ? NS + 1 : 0) * 32;
+          uint32_t w[32];
+          tmem_ld32(xcol, w);
+          tmem_wait_ld();
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = __float_as_uint(__uint_as_float(v[j]) + __uint_as_float(w[j]));
+          tmem_fill32(xcol, 0u);
+        } else {
+          tmem_wait_ld();
+        }
+        tmem_fill32(tcol + (s + 1) * 32, 0u);
+      } else {
+        mbar_wait(&acc_ready[s], (og / NS) & 1);
+        tc_fence_after();
+        tmem_ld32(tcol + s * 32, v);
+        tmem_wait_ld();
+        tmem_fill32(tcol + s * 32, 0u);
+      }
       tmem_wait_st();
       tc_fence_before();
       __syncwarp();
@@ -587,7 +658,8 @@ __global__ void __launch_bounds__(n_threads(group_cfg(GID)), 1) dce_chain_kernel
   constexpr Group G = group_cfg(GID);
   constexpr int kS = G.S;
   constexpr int kRingLo = w_offset(G, G.S), kRingHi = bar_offset(G);
-  static_assert(G.S * G.slots * 32 <= 512, "TMEM: stages x slots x 32 columns must fit 512");
+  static_assert(G.S * phys_slots(G) * 32 <= 512, "TMEM: stages x slots x 32 columns must fit 512");
+  static_assert(!G.ovf || (G.slots >= 4 && G.slots <= 30 && G.slots % 2 == 0), "overflow-slot scheme: an even number of 4..30 logical slots");
   static_assert(smem_bytes(G) <= 227 * 1024, "shared memory budget");
   extern __shared__ __align__(128) uint8_t smem_raw[];
   const Smem<GID> sm{smem_raw};
@@ -645,7 +717,7 @@ __global__ void __launch_bounds__(n_threads(group_cfg(GID)), 1) dce_chain_kernel
       constexpr int s = decltype(S)::value;
       if (warp == s) {
         RowIt cur;
-        cur.u = blockIdx.x; cur.oc = 0; cur.rc = 0; cur.r = 0;
+        cur.u = blockIdx.x; cur.oc = 0; cur.rc = 0; cur.r = 0; cur.fmask = 0;
         row_begin_unit<GID, s>(a, cur);
         if (cur.valid) row_ready<GID, s, true>(sm, cur);
         while (cur.valid) {
@@ -672,7 +744,7 @@ __global__ void __launch_bounds__(n_threads(group_cfg(GID)), 1) dce_chain_kernel
     const int grp = (warp - kFirstEpiWarp) >> 2, q = warp & 3;
     for_each_stage<GID>([&](auto S) {
       constexpr int s = decltype(S)::value;
-      if (grp / kEpiGroups == s) epilogue_loop<GID, s>(a, sm, tmem, grp % kEpiGroups, q, lane);
+      if (grp / epi_groups(group_cfg(GID)) == s) epilogue_loop<GID, s>(a, sm, tmem, grp % epi_groups(group_cfg(GID)), q, lane);
     });
   }
   tc_fence_before();

@@ -306,7 +306,7 @@ static int dce_forward_tc(llie_ctx* ctx, const void* in_v, void* out_v, float* m
       single(0, pk.xin, nullptr, x1); LLIE_TRY((launch_chain<3>(ctx, st, a, "dce_conv_tc_first_kernel")));
       single(1, x1, nullptr, x2); LLIE_TRY((launch_chain<4>(ctx, st, a, "dce_conv_tc_k32_kernel")));
       single(2, x2, nullptr, x3); LLIE_TRY((launch_chain<4>(ctx, st, a, "dce_conv_tc_k32_kernel")));
-      single(3, x3, nullptr, x4); LLIE_TRY((launch_chain<4>(ctx, st, a, "dce_conv_tc_k32_kernel")));
+      single(3, x3, nullptr, x4); LLIE_TRY((launch_chain<11>(ctx, st, a, "dce_conv_tc_k32_kernel")));  // summed as inside conv4+5
       single(4, x3, x4, x5); LLIE_TRY((launch_chain<5>(ctx, st, a, "dce_conv_tc_k64_kernel")));
       single(5, x2, x5, x6); LLIE_TRY((launch_chain<5>(ctx, st, a, "dce_conv_tc_k64_kernel")));
       single(6, x1, x6, nullptr); LLIE_TRY((launch_chain<6>(ctx, st, a, "dce_conv_tc_last_kernel")));
