@@ -213,6 +213,105 @@ down4_cols_kernel(const float* __restrict__ V, float* __restrict__ Cout, int RW,
   }
 }
 
+// NHWC (CS = 3), four adjacent outputs per thread.  The windows of adjacent outputs overlap by 29 of 33 pixels, so a
+// thread reads its 45 pixels x 3 channels once (34 LDS.128) for 396 FFMAs, where one output per thread needed 25
+// LDS.128 per 99 (ncu on that version: shared-memory LSU wavefronts 72 % of peak, `mio_throttle` the top stall).  A
+// thread's first pixel is 16 t, i.e. float 48 t: one pad float4 after every 12 makes the lane stride 13 float4
+// (conflict-free quarter-warps).  Every output still sums its taps in the order t = 0..32 -- the same bits as
+// down4_cols_kernel.  Stores go through a per-warp transpose (a thread's four outputs are consecutive).
+constexpr int kCols4Out = 4 * 128;                          // outputs per CTA and row
+constexpr int kCols4Px = 4 * kCols4Out + 2 * kRD;           // pixels staged: 4 * 511 + 33 (+ 3: the last float4), in 16-pixel blocks
+constexpr int kCols4Vec = kCols4Px * 3 / 4;                 // float4 per segment (a multiple of 12)
+constexpr int kCols4Pad = kCols4Vec + kCols4Vec / 12;       // ... with the pads
+constexpr int kCols4Stage = (kCols4Vec + 127) / 128;        // float4 per thread and row in flight
+static_assert(kCols4Px % 16 == 0 && kCols4Vec % 12 == 0, "segment must be whole 16-pixel (12 float4) blocks");
+__global__ void __launch_bounds__(128)
+down4_cols4_kernel(const float* __restrict__ V, float* __restrict__ Cout, int RW, int W, int hC, int wC,
+                   int row_begin, int row_end, float a, float b) {
+  __shared__ __align__(16) float4 seg[kCols4Pad];
+  __shared__ float sout[4][32 * 5];
+  const int jy0 = row_begin + blockIdx.y * kColsRows, jy1 = min(jy0 + kColsRows, row_end);
+  const long long plane = blockIdx.z;
+  const int jx0 = blockIdx.x * kCols4Out;
+  const int px0 = 4 * (jx0 - kPC) - kRD;
+  // float4 i of the segment holds floats px0 * 3 + 4 i ..: a 128-bit load where it lies inside the row (px0 * 3 is a
+  // multiple of 4), element-wise edge clamping where it does not (with 512 outputs per CTA EVERY CTA touches a border
+  // on 4K frames, so there is no separate "interior" kernel path)
+  const bool vec_ok = (RW & 3) == 0;
+  float4 st[kCols4Stage];
+  auto inside = [&](int i) { const int f0 = px0 * 3 + 4 * i; return vec_ok && f0 >= 0 && f0 + 3 < 3 * W; };
+  auto fetch = [&](int jy) {   // the 128-bit loads of the next row, in flight while the current one is filtered
+    const float* src = V + (plane * hC + jy) * (long long)RW + px0 * 3;
+#pragma unroll
+    for (int k = 0; k < kCols4Stage; ++k) {
+      const int i = threadIdx.x + k * 128;
+      if (i < kCols4Vec && inside(i)) st[k] = __ldg(reinterpret_cast<const float4*>(src) + i);
+    }
+  };
+  fetch(jy0);
+  const int t = threadIdx.x, l = t & 31;
+  for (int jy = jy0; jy < jy1; ++jy) {
+    __syncthreads();  // the previous row's reads of seg are done
+#pragma unroll
+    for (int k = 0; k < kCols4Stage; ++k) {
+      const int i = t + k * 128;
+      if (i < kCols4Vec && inside(i)) seg[i + i / 12] = st[k];
+    }
+    {  // the few float4 that straddle a border of the row: element-wise edge clamp, not prefetched
+      const float* src = V + (plane * hC + jy) * (long long)RW;
+#pragma unroll 1
+      for (int i = t; i < kCols4Vec; i += 128) {
+        if (inside(i)) continue;
+        float e[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const int f = px0 * 3 + 4 * i + j, px = (f + 3 * 64) / 3 - 64, c = f - 3 * px;   // floor division for f >= -192
+          e[j] = __ldg(src + min(max(px, 0), W - 1) * 3 + c);
+        }
+        seg[i + i / 12] = make_float4(e[0], e[1], e[2], e[3]);
+      }
+    }
+    __syncthreads();
+    if (jy + 1 < jy1) fetch(jy + 1);
+    float acc[4][3];
+#pragma unroll
+    for (int q = 0; q < 4; ++q)
+#pragma unroll
+      for (int c = 0; c < 3; ++c) acc[q][c] = 0.f;
+    const float4* s4 = seg + 13 * t;   // float4 12 t of the segment, padded
+#pragma unroll
+    for (int k = 0; k < 34; ++k) {
+      const float4 v4 = s4[k + k / 12];
+      const float v[4] = {v4.x, v4.y, v4.z, v4.w};
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const int f = 4 * k + e, u = f / 3, c = f - 3 * u;   // pixel u of the window (0..44), channel c
+        if (u <= 44) {
+#pragma unroll
+          for (int q = 0; q < 4; ++q)
+            if (u - 4 * q >= 0 && u - 4 * q <= 2 * kRD) acc[q][c] = fmaf(gd(u - 4 * q), v[e], acc[q][c]);
+        }
+      }
+    }
+    // per-warp transpose: lane l holds outputs 4 l .. 4 l + 3 of the warp's 128; store them as four 128-byte lines
+    float* wst = sout[t >> 5];
+    const int jxw = jx0 + (t & ~31) * 4;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+#pragma unroll
+      for (int q = 0; q < 4; ++q) wst[l * 5 + q] = fmaf(a, acc[q][c], b);
+      __syncwarp();
+      float* dst = Cout + ((plane * 3 + c) * hC + jy) * (long long)wC + jxw;
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const int o = q * 32 + l;
+        if (jxw + o < wC) dst[o] = wst[(o >> 2) * 5 + (o & 3)];
+      }
+      __syncwarp();
+    }
+  }
+}
+
 // ---- level C -> level B: prefilter + decimate by 4 (same 33-tap Gaussian, in C samples) ---------
 // x pass: T[plane][row][jb] = sum_t g[t] C[plane][row][clamp(4(jb-PB)+PC+t-16, 0, wC-1)], rows [r0, r1).
 // A CTA stages the edge-clamped C row segment of kDecXTile outputs in shared memory (one pad float after every

@@ -781,7 +781,7 @@ int msrcr_pyramid_run_io(llie_ctx* ctx, const void* in, void* out, int iot, int 
     dim3 grid(ceil_div(wC, 128), ceil_div(hC, kColsRows), planes_v);
     if (nhwc)
       LLIE_LAUNCH(ctx, st, "down4_cols_kernel",
-                  down4_cols_kernel<3><<<grid, 128, 0, st>>>((const float*)dV, (float*)dC, RW, w, hC, wC, 0, hC, in_scale, p.in_bias));
+                  down4_cols4_kernel<<<dim3(ceil_div(wC, kCols4Out), grid.y, grid.z), 128, 0, st>>>((const float*)dV, (float*)dC, RW, w, hC, wC, 0, hC, in_scale, p.in_bias));
     else
       LLIE_LAUNCH(ctx, st, "down4_cols_kernel",
                   down4_cols_kernel<1><<<grid, 128, 0, st>>>((const float*)dV, (float*)dC, RW, w, hC, wC, 0, hC, in_scale, p.in_bias));
@@ -945,9 +945,9 @@ int tiled_phase_a_body(llie_ctx* ctx, cudaStream_t st, int d, int n_dev, llie_ct
   if (!first) LLIE_TRY(rows_launch(b.band_top, g.R0 - kHaloRaw, kBandTopRows, g.own_lo, vi_lo, 1));
   if (!last) LLIE_TRY(rows_launch(b.band_bot, g.R1 - (kBandBotRows - kHaloRaw), kBandBotRows, vi_hi, g.own_hi, 1));
   LLIE_TRY(rows_launch(in[d], g.R0, rows[d], vi_lo, vi_hi, 8 * ctx->sm_count));
-  dim3 grid(ceil_div(wC, 128), ceil_div(g.own_hi - g.own_lo, kColsRows), 1);
+  dim3 grid(ceil_div(wC, kCols4Out), ceil_div(g.own_hi - g.own_lo, kColsRows), 1);
   LLIE_LAUNCH(ctx, st, "down4_cols_kernel",
-              down4_cols_kernel<3><<<grid, 128, 0, st>>>(b.V, b.C, RW, W, hC, wC, g.own_lo, g.own_hi, p.in_scale, p.in_bias));
+              down4_cols4_kernel<<<grid, 128, 0, st>>>(b.V, b.C, RW, W, hC, wC, g.own_lo, g.own_hi, p.in_scale, p.in_bias));
   return LLIE_OK;
 }
 
