@@ -225,7 +225,7 @@ constexpr int kCols4Vec = kCols4Px * 3 / 4;                 // float4 per segmen
 constexpr int kCols4Pad = kCols4Vec + kCols4Vec / 12;       // ... with the pads
 constexpr int kCols4Stage = (kCols4Vec + 127) / 128;        // float4 per thread and row in flight
 static_assert(kCols4Px % 16 == 0 && kCols4Vec % 12 == 0, "segment must be whole 16-pixel (12 float4) blocks");
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(128, 4)  // 128 registers: 0.187 ms on 32 x 4K (142 registers / 3 CTAs: 0.207; 96 / 5: 0.196)
 down4_cols4_kernel(const float* __restrict__ V, float* __restrict__ Cout, int RW, int W, int hC, int wC,
                    int row_begin, int row_end, float a, float b) {
   __shared__ __align__(16) float4 seg[kCols4Pad];
