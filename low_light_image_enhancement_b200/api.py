@@ -22,8 +22,18 @@ DCE_LAYERS = ((32, 3), (32, 32), (32, 32), (32, 32), (32, 64), (32, 64), (24, 64
 DCE_NUM_PARAMS = sum(co * ci * 9 + co for co, ci in DCE_LAYERS)
 
 
+_MSRCR_DEFAULTS: dict | None = None
+
+
 def default_msrcr_params() -> dict:
-    """SURVEY.md 9.1 defaults (filled by the library so both sides agree)."""
+    """SURVEY.md 9.1 defaults (filled by the library so both sides agree; fetched once)."""
+    global _MSRCR_DEFAULTS
+    if _MSRCR_DEFAULTS is None:
+        _MSRCR_DEFAULTS = _fetch_msrcr_defaults()
+    return dict(_MSRCR_DEFAULTS)
+
+
+def _fetch_msrcr_defaults() -> dict:
     p = MsrcrParams()
     p.struct_size = C.sizeof(MsrcrParams)   # the caller states its struct's size; the library writes no further
     _lib.check(_lib.load().llie_msrcr_default_params(C.byref(p)))
