@@ -218,3 +218,28 @@ def test_product_package_never_imports_the_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h")):
                 text = open(os.path.join(dirpath, f)).read()
                 assert not re.search(r"^\s*(import|from)\s+oracle\b", text, flags=re.M), f
+
+
+def test_sharder_entry_points_validate_before_touching_cuda(lib_built):
+    """llie_enhance_sharded / llie_create_group (SURVEY.md 8(b)): argument errors are status codes on any machine;
+    without a GPU creating a group fails loudly (no CPU fallback)."""
+    VP1, I1 = C.c_void_p * 1, C.c_int * 1
+    p = _lib.MsrcrParams()
+    p.struct_size = C.sizeof(_lib.MsrcrParams)
+    _lib.check(lib_built.llie_msrcr_default_params(C.byref(p)))
+    pv = C.cast(C.byref(p), C.c_void_p)
+    f = lib_built.llie_enhance_sharded
+    assert f(None, 1, 0, 0, VP1(None), VP1(None), I1(1), 8, 8, 0, pv, 0) == _lib.E_ARG          # null ctx array
+    assert f(VP1(None), 1, 0, 0, VP1(None), VP1(None), I1(1), 8, 8, 0, pv, 0) == _lib.E_ARG     # null ctx in slot 0
+    assert f(VP1(None), 0, 0, 0, VP1(None), VP1(None), I1(1), 8, 8, 0, pv, 0) == _lib.E_ARG     # n_dev out of range
+    assert f(VP1(None), 1, 7, 0, VP1(None), VP1(None), I1(1), 8, 8, 0, pv, 0) == _lib.E_ARG     # unknown method
+    assert f(VP1(None), 1, 0, 9, VP1(None), VP1(None), I1(1), 8, 8, 0, pv, 0) == _lib.E_DTYPE   # unknown io type
+    assert f(VP1(None), 1, 0, 0, VP1(None), VP1(None), I1(1), 0, 8, 0, pv, 0) == _lib.E_SHAPE
+    assert b"ctx" in lib_built.llie_last_error() or b"shape" in lib_built.llie_last_error()
+    ms = C.c_float()
+    assert lib_built.llie_shard_last_ms(None, C.byref(ms)) == _lib.E_ARG
+    if not HAS_GPU:
+        out = VP1(None)
+        assert lib_built.llie_create_group(out, I1(0), 1) == _lib.E_CUDA and out[0] is None
+        with pytest.raises(L.LlieError):
+            L.enhance(np.zeros((2, 8, 8, 3), np.float32), "msrcr", devices=[0, 0])
