@@ -193,6 +193,7 @@ int llie_destroy(llie_ctx* ctx) {
   msrcr_plan_free(ctx->plan);
   dce_weights_free(ctx->dce);
   dce_tc_release(ctx);
+  if (ctx->aux_stream) { cudaEventDestroy(ctx->aux_ev[0]); cudaEventDestroy(ctx->aux_ev[1]); cudaStreamDestroy(ctx->aux_stream); }
   for (auto& gs : ctx->g_tile)
     if (gs.exec) cudaGraphExecDestroy(gs.exec);
   if (ctx->tile_event) { cudaEventDestroy(ctx->tile_event); cudaEventDestroy(ctx->tile_t0); cudaEventDestroy(ctx->tile_t1); }

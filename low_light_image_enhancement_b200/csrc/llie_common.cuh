@@ -169,6 +169,8 @@ struct llie_ctx {
   void* sh_pin[2][3] = {{nullptr, nullptr, nullptr}, {nullptr, nullptr, nullptr}};
   size_t sh_pin_bytes[2][3] = {{0, 0, 0}, {0, 0, 0}};
   float shard_ms = -1.f;
+  cudaStream_t aux_stream = nullptr;  // MSRCR: the stride-16 branch runs beside the stride-4 FIRs
+  cudaEvent_t aux_ev[2] = {nullptr, nullptr};
   // CUDA graphs of the row-tiled path's launch sequences (phase A; the local tail of phase B), replayed while the
   // key -- pointers, geometry, parameters, workspace generation -- stays the same
   struct GraphSlot { uint64_t key = 0; cudaGraphExec_t exec = nullptr; uint64_t launches = 0; int seen = 0; };

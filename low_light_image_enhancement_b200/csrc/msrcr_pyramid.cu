@@ -786,9 +786,27 @@ int msrcr_pyramid_run_io(llie_ctx* ctx, const void* in, void* out, int iot, int 
       LLIE_LAUNCH(ctx, st, "down4_cols_kernel",
                   down4_cols_kernel<1><<<grid, 128, 0, st>>>((const float*)dV, (float*)dC, RW, w, hC, wC, 0, hC, in_scale, p.in_bias));
   }
+  // The stride-16 branch (decimation, the stride-16 FIRs, both upsamplers: ten small, latency-bound launches on
+  // 1/16 .. 1/256 of the pixels) and the stride-4 FIRs (issue-bound) both depend on level C only: they run on two
+  // streams, forked and joined by events, so the small launches fill in underneath the large ones.
+  int n_c = 0;
+  for (auto& sc0 : pl->scales) n_c += sc0.level == 0;
+  cudaStream_t sb = st;
+  if (n_b && n_c) {
+    if (!ctx->aux_stream) {
+      int prio_lo = 0, prio_hi = 0;  // highest priority: its small CTAs take the slots the large launches free
+      LLIE_CUDA_OK(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+      LLIE_CUDA_OK(cudaStreamCreateWithPriority(&ctx->aux_stream, cudaStreamNonBlocking, prio_hi));
+      LLIE_CUDA_OK(cudaEventCreateWithFlags(&ctx->aux_ev[0], cudaEventDisableTiming));
+      LLIE_CUDA_OK(cudaEventCreateWithFlags(&ctx->aux_ev[1], cudaEventDisableTiming));
+    }
+    sb = ctx->aux_stream;
+    LLIE_CUDA_OK(cudaEventRecord(ctx->aux_ev[0], st));
+    LLIE_CUDA_OK(cudaStreamWaitEvent(sb, ctx->aux_ev[0], 0));
+  }
   if (n_b) {
-    LLIE_LAUNCH(ctx, st, "decim4_x_kernel", decim4_x_kernel<<<dim3(ceil_div(wB, kDecXTile), hC, planes), 128, 0, st>>>((const float*)dC, (float*)dTB, hC, wC, wB, 0, hC));
-    LLIE_LAUNCH(ctx, st, "decim4_y_kernel", decim4_y_kernel<<<dim3(ceil_div(wB, 128), ceil_div(hB, kDecQ), planes), 128, 0, st>>>((const float*)dTB, (float*)dB, hC, hB, wB, 0, hB));
+    LLIE_LAUNCH(ctx, sb, "decim4_x_kernel", decim4_x_kernel<<<dim3(ceil_div(wB, kDecXTile), hC, planes), 128, 0, sb>>>((const float*)dC, (float*)dTB, hC, wC, wB, 0, hC));
+    LLIE_LAUNCH(ctx, sb, "decim4_y_kernel", decim4_y_kernel<<<dim3(ceil_div(wB, 128), ceil_div(hB, kDecQ), planes), 128, 0, sb>>>((const float*)dTB, (float*)dB, hC, hB, wB, 0, hB));
   }
   (void)CS;
   std::vector<int> b_scales;  // stride-16 scales in T2 order
@@ -807,15 +825,19 @@ int msrcr_pyramid_run_io(llie_ctx* ctx, const void* in, void* out, int iot, int 
       LLIE_LAUNCH(ctx, st, "fir_y_kernel", (launch_fir_y8(tp, gy, smy, st, (const float*)dCt, sc, taps, r, hC, wC, 0, hC, 0, hC, 0, hC, ft)));
     } else {
       dim3 gx((unsigned)((long long)planes * hB), ceil_div(wB, kFirX8Tile)), gy(ceil_div(wB, 128), ceil_div(hB, kFir8), planes);
-      LLIE_LAUNCH(ctx, st, "fir_x_kernel", (launch_fir_x8(tp, gx, smx, st, (const float*)dB, (float*)dBt, taps, r, wB, planes * hB, 0, 0, ft)));
-      LLIE_LAUNCH(ctx, st, "fir_y_kernel", (launch_fir_y8(tp, gy, smy, st, (const float*)dBt, (float*)dSB, taps, r, hB, wB, 0, hB, 0, hB, 0, hB, ft)));
+      LLIE_LAUNCH(ctx, sb, "fir_x_kernel", (launch_fir_x8(tp, gx, smx, sb, (const float*)dB, (float*)dBt, taps, r, wB, planes * hB, 0, 0, ft)));
+      LLIE_LAUNCH(ctx, sb, "fir_y_kernel", (launch_fir_y8(tp, gy, smy, sb, (const float*)dBt, (float*)dSB, taps, r, hB, wB, 0, hB, 0, hB, 0, hB, ft)));
       dim3 ux(ceil_div((long long)hB * up_bc_x_groups(wC), 256), 1, planes);
-      LLIE_LAUNCH(ctx, st, "up_bc_x_kernel", up_bc_x_kernel<<<ux, 256, 0, st>>>((const float*)dSB, (float*)dT2 + b_scales.size() * t2_elems, hB, wB, wC, 0, hB, pl->uw));
+      LLIE_LAUNCH(ctx, sb, "up_bc_x_kernel", up_bc_x_kernel<<<ux, 256, 0, sb>>>((const float*)dSB, (float*)dT2 + b_scales.size() * t2_elems, hB, wB, wC, 0, hB, pl->uw));
       b_scales.push_back(k);
     }
   }
   if (!b_scales.empty())
-    LLIE_TRY(launch_up_bc_y(ctx, st, pl, b_scales, (const float*)dT2, t2_elems, (float*)dSC, c_elems, hB, hC, wC, 0, hC, planes));
+    LLIE_TRY(launch_up_bc_y(ctx, sb, pl, b_scales, (const float*)dT2, t2_elems, (float*)dSC, c_elems, hB, hC, wC, 0, hC, planes));
+  if (sb != st) {
+    LLIE_CUDA_OK(cudaEventRecord(ctx->aux_ev[1], sb));
+    LLIE_CUDA_OK(cudaStreamWaitEvent(st, ctx->aux_ev[1], 0));
+  }
   LLIE_TRY(final_passes(ctx, st, pl, p, in, out, v, vec, nhwc, n, h, w, 0, 0, h, hC, wC, (const float*)dSC, c_elems,
                         (float*)dAcc, iot));
   return LLIE_OK;
