@@ -237,24 +237,34 @@ static int dce_forward_tc(llie_ctx* ctx, const void* in_v, void* out_v, float* m
     pk.xin = (__nv_bfloat16*)ws + (size_t)6 * chunk * act_elems_per_img;
   }
   const ImgView vx = make_view(layout, 3, h, w), vm = make_view(layout, 24, h, w);
+  // Several passes (64 frames = 22 + 21 + 21): the packed input is only read by the first chain of a pass, so the
+  // NEXT pass's pack kernel (HBM-bound, no shared memory: it fits beside the persistent chain CTAs) runs on the ctx's
+  // second stream underneath conv4-5 / conv6-7 of the current pass.
+  const bool overlap_pack = !split && !pk.unfused && n > chunk;
+  if (overlap_pack) LLIE_TRY(ensure_aux_stream(ctx));
+  auto pack = [&](long long n0, cudaStream_t s2) -> int {
+    const int nb = (int)((n - n0 < chunk) ? (n - n0) : chunk);
+    const float* x = reinterpret_cast<const float*>(static_cast<const char*>(in_v) + (size_t)n0 * h * w * 3 * esz);
+    dim3 grid((w + 255) / 256, h, nb);
+    if (split)
+      LLIE_LAUNCH(ctx, s2, "dce_pack_input_split_kernel",
+                  (dce_pack_input_kernel<true, float><<<grid, 256, 0, s2>>>(x, vx, pk.xin, h, w, wp)));
+    else if (iot == kIoU8)
+      LLIE_LAUNCH(ctx, s2, "dce_pack_input_kernel",
+                  (dce_pack_input_kernel<false, uint8_t><<<grid, 256, 0, s2>>>(reinterpret_cast<const uint8_t*>(x), vx, pk.xin, h, w, wp)));
+    else if (iot == kIoU16)
+      LLIE_LAUNCH(ctx, s2, "dce_pack_input_kernel",
+                  (dce_pack_input_kernel<false, uint16_t><<<grid, 256, 0, s2>>>(reinterpret_cast<const uint16_t*>(x), vx, pk.xin, h, w, wp)));
+    else
+      LLIE_LAUNCH(ctx, s2, "dce_pack_input_kernel",
+                  (dce_pack_input_kernel<false, float><<<grid, 256, 0, s2>>>(x, vx, pk.xin, h, w, wp)));
+    return LLIE_OK;
+  };
   for (long long n0 = 0; n0 < n; n0 += chunk) {
     const int nb = (int)((n - n0 < chunk) ? (n - n0) : chunk);
     const float* x = reinterpret_cast<const float*>(static_cast<const char*>(in_v) + (size_t)n0 * h * w * 3 * esz);
-    {
-      dim3 grid((w + 255) / 256, h, nb);
-      if (split)
-        LLIE_LAUNCH(ctx, st, "dce_pack_input_split_kernel",
-                    (dce_pack_input_kernel<true, float><<<grid, 256, 0, st>>>(x, vx, pk.xin, h, w, wp)));
-      else if (iot == kIoU8)
-        LLIE_LAUNCH(ctx, st, "dce_pack_input_kernel",
-                    (dce_pack_input_kernel<false, uint8_t><<<grid, 256, 0, st>>>(reinterpret_cast<const uint8_t*>(x), vx, pk.xin, h, w, wp)));
-      else if (iot == kIoU16)
-        LLIE_LAUNCH(ctx, st, "dce_pack_input_kernel",
-                    (dce_pack_input_kernel<false, uint16_t><<<grid, 256, 0, st>>>(reinterpret_cast<const uint16_t*>(x), vx, pk.xin, h, w, wp)));
-      else
-        LLIE_LAUNCH(ctx, st, "dce_pack_input_kernel",
-                    (dce_pack_input_kernel<false, float><<<grid, 256, 0, st>>>(x, vx, pk.xin, h, w, wp)));
-    }
+    if (!overlap_pack || n0 == 0) LLIE_TRY(pack(n0, st));
+    else LLIE_CUDA_OK(cudaStreamWaitEvent(st, ctx->aux_ev[1], 0));  // this pass's input was packed under the previous pass
     ChainArgs a;
     memset(&a, 0, sizeof(a));
     a.N = nb; a.H = h; a.W = w; a.Wp = wp;
@@ -287,6 +297,12 @@ static int dce_forward_tc(llie_ctx* ctx, const void* in_v, void* out_v, float* m
       stage(0, 0, x1); stage(1, 1, x2); stage(2, 2, x3);
       a.ext[0][0][0] = pk.xin;
       LLIE_TRY((launch_chain<0>(ctx, st, a, "dce_chain_c123_kernel")));
+      if (overlap_pack && n0 + chunk < n) {  // the packed input is free again: pack the next pass beside conv4..7
+        LLIE_CUDA_OK(cudaEventRecord(ctx->aux_ev[0], st));
+        LLIE_CUDA_OK(cudaStreamWaitEvent(ctx->aux_stream, ctx->aux_ev[0], 0));
+        LLIE_TRY(pack(n0 + chunk, ctx->aux_stream));
+        LLIE_CUDA_OK(cudaEventRecord(ctx->aux_ev[1], ctx->aux_stream));
+      }
       // conv4 + conv5: reads x3 (twice: as conv4's input and as the first half of conv5's), writes x5
       memset(a.ext, 0, sizeof(a.ext));
       stage(0, 3, pk.keep_all ? x4 : nullptr); stage(1, 4, x5);

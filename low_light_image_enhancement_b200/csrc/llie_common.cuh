@@ -283,6 +283,16 @@ int run_as_graph(llie_ctx* ctx, llie_ctx::GraphSlot& slot, uint64_t key, cudaStr
   ctx->launches += slot.launches;
   return LLIE_OK;
 }
+// The ctx's auxiliary stream (highest priority: its small CTAs take the slots the large launches free) + two events.
+inline int ensure_aux_stream(llie_ctx* ctx) {
+  if (ctx->aux_stream) return LLIE_OK;
+  int prio_lo = 0, prio_hi = 0;
+  LLIE_CUDA_OK(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+  LLIE_CUDA_OK(cudaStreamCreateWithPriority(&ctx->aux_stream, cudaStreamNonBlocking, prio_hi));
+  LLIE_CUDA_OK(cudaEventCreateWithFlags(&ctx->aux_ev[0], cudaEventDisableTiming));
+  LLIE_CUDA_OK(cudaEventCreateWithFlags(&ctx->aux_ev[1], cudaEventDisableTiming));
+  return LLIE_OK;
+}
 inline uint64_t fnv1a(const void* data, size_t n, uint64_t h = 1469598103934665603ull) {
   const unsigned char* p = static_cast<const unsigned char*>(data);
   for (size_t i = 0; i < n; ++i) { h ^= p[i]; h *= 1099511628211ull; }

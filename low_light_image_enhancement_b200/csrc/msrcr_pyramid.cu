@@ -793,13 +793,7 @@ int msrcr_pyramid_run_io(llie_ctx* ctx, const void* in, void* out, int iot, int 
   for (auto& sc0 : pl->scales) n_c += sc0.level == 0;
   cudaStream_t sb = st;
   if (n_b && n_c) {
-    if (!ctx->aux_stream) {
-      int prio_lo = 0, prio_hi = 0;  // highest priority: its small CTAs take the slots the large launches free
-      LLIE_CUDA_OK(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
-      LLIE_CUDA_OK(cudaStreamCreateWithPriority(&ctx->aux_stream, cudaStreamNonBlocking, prio_hi));
-      LLIE_CUDA_OK(cudaEventCreateWithFlags(&ctx->aux_ev[0], cudaEventDisableTiming));
-      LLIE_CUDA_OK(cudaEventCreateWithFlags(&ctx->aux_ev[1], cudaEventDisableTiming));
-    }
+    LLIE_TRY(ensure_aux_stream(ctx));
     sb = ctx->aux_stream;
     LLIE_CUDA_OK(cudaEventRecord(ctx->aux_ev[0], st));
     LLIE_CUDA_OK(cudaStreamWaitEvent(sb, ctx->aux_ev[0], 0));
