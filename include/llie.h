@@ -126,6 +126,30 @@ int llie_profile_end(llie_ctx* ctx, char* buf, size_t buflen);
 int llie_msrcr_f32(llie_ctx* ctx, const float* in, float* out, int n, int h, int w, int layout,
                    const llie_msrcr_params* params, void* stream);
 
+/* MSRCR of ONE h x w x 3 fp32 image without a ctx and without any allocation -- NO COUNTERPART IN THE REFERENCE (nor
+ * in SURVEY.md 8(b)); it exists for callers that cannot let this library call cudaMalloc: a plug-in inside an
+ * application that has already claimed the whole GPU for its own pool (the library's cudaMalloc would fail there),
+ * a frame loop that cannot afford the device-wide synchronisation a cudaMalloc / cudaFree implies, or a runtime whose
+ * policy forbids device allocation after start-up.  in / out are device pointers on the CURRENT device (out may not
+ * alias in); everything in between lives in one fixed array of LLIE_STATIC_SCRATCH_BYTES that is part of the library's
+ * device image, so every GPU that uses this function gives up that much memory until the process exits.
+ *   - Arithmetic: the exact truncated FIR (what llie_msrcr_f32 does for blur = LLIE_BLUR_DIRECT; params->blur is
+ *     ignored) and the plain clip; params->finish must be LLIE_FINISH_NONE.
+ *   - Limits: (1 + n_scales) * h * w * 12 bytes + 4 * LLIE_STATIC_MAX_TAPS must fit the array (three scales: 697 685
+ *     pixels, e.g. 960 x 540), and the filters together may have at most LLIE_STATIC_MAX_TAPS taps (each scale uses
+ *     2 * ceil(truncate * sigma) + 1, rounded up to a multiple of 4).  Anything larger: LLIE_E_NOMEM, nothing is run.
+ *   - The first call on a device looks up the array's address there (and makes the driver load this part of the
+ *     library onto that GPU); make that call during start-up, before any stream capture is begun.
+ *   - All calls on one GPU share the array from its first byte.  Calls that are ordered on the device (same stream,
+ *     or events between streams) are fine; calls that can overlap on the GPU corrupt each other silently.  The array
+ *     keeps the last call's intermediates; the function needs none of it cleared.
+ *   - stream: cudaStream_t as void*, work is enqueued and the call returns; NULL = the default stream and a
+ *     synchronous return.  No cudaMalloc, cudaFree or other allocating call is made, on any call. */
+#define LLIE_STATIC_SCRATCH_BYTES (32u << 20) /* 32 MiB per GPU that loads it */
+#define LLIE_STATIC_MAX_TAPS 16384
+int llie_msrcr_direct_static_f32(const float* in, float* out, int h, int w, int layout,
+                                 const llie_msrcr_params* params, void* stream);
+
 /* SURVEY.md 8(f) rank 1 -- 8-bit images: in/out are n*h*w*3 uint8 device arrays in `layout`; a byte b means the
  * value b/255 and the result is stored as rint(255 * value).  The conversions happen inside the first and last
  * kernels of the path (no extra pass over the image), so the image costs 1 byte per sample on HBM and on PCIe.

@@ -19,6 +19,7 @@ BLUR_PYRAMID, BLUR_DIRECT = 0, 1
 METHOD = {"msrcr": 0, "zero_dce": 1}
 SHARD_DEVICE, SHARD_HOST = 0, 1
 MAX_SCALES = 8
+STATIC_SCRATCH_BYTES, STATIC_MAX_TAPS = 32 << 20, 16384  # llie_msrcr_direct_static_f32
 
 
 class LlieError(RuntimeError):
@@ -69,6 +70,7 @@ EXPORTS = {
     "llie_profile_begin": (_I, [_VP]),
     "llie_profile_end": (_I, [_VP, C.c_char_p, C.c_size_t]),
     "llie_msrcr_f32": (_I, [_VP, _VP, _VP, _I, _I, _I, _I, C.POINTER(MsrcrParams), _VP]),
+    "llie_msrcr_direct_static_f32": (_I, [_VP, _VP, _I, _I, _I, C.POINTER(MsrcrParams), _VP]),
     "llie_msrcr_u8": (_I, [_VP, _VP, _VP, _I, _I, _I, _I, C.POINTER(MsrcrParams), _VP]),
     "llie_dce_forward_u8": (_I, [_VP, _VP, _VP, _VP, _I, _I, _I, _I, C.POINTER(DceParams), _VP]),
     "llie_msrcr_u16": (_I, [_VP, _VP, _VP, _I, _I, _I, _I, C.POINTER(MsrcrParams), _VP]),
