@@ -149,12 +149,21 @@ __global__ void __launch_bounds__(128) fir_x8_kernel(const float* __restrict__ i
     return (long long)pl * plane_rows + row_lo + (ri - pl * rows_per_plane);
   };
   float st[kFirXStage];
+  // Samples i < 128 kFirXStage of row ri go through registers (stored to shared memory one barrier later).  Only
+  // filters too long for the by-value taps can have a longer segment (tile + n_steps > 1280): that tail is written
+  // straight into row ri's buffer, which is free -- its previous user, row ri - 2, was finished by every thread
+  // before the barrier of row ri - 1, and fetch(ri) runs after that barrier.
   auto fetch = [&](int ri) {
     const float* src = in + row_of(ri) * (long long)W;
 #pragma unroll
     for (int k = 0; k < kFirXStage; ++k) {
       const int i = threadIdx.x + k * 128;
       if (i < seg_px) st[k] = __ldg(src + min(max(x0 - r + i, 0), W - 1));
+    }
+    if constexpr (!kParamTaps) {
+      float* tail = seg_all + ((ri - ri0) & 1) * seg_stride;
+      for (int i = threadIdx.x + kFirXStage * 128; i < seg_px; i += 128)
+        tail[i + (i >> 3)] = __ldg(src + min(max(x0 - r + i, 0), W - 1));
     }
   };
   fetch(ri0);

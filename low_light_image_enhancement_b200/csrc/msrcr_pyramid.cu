@@ -544,6 +544,9 @@ static int ensure_plan(llie_ctx* ctx, const llie_msrcr_params& p, cudaStream_t s
     msrcr_plan_free(ctx->plan);
   }
   ctx->plan = pl;
+  // the row-tiled path's captured graphs bake in pl->d_taps addresses: a new plan must change their key, or a later
+  // call with the old parameters and buffers would replay launches that read the freed taps
+  ++ctx->ws_generation;
   return LLIE_OK;
 }
 
@@ -575,7 +578,12 @@ void launch_fir_x8(bool param, dim3 grid, size_t smem, cudaStream_t st, const fl
                    int r, int W, int rows_per_plane, int plane_rows, int row_lo, const FirTaps& ft) {
   const int steps = fir8_steps(r), total = (int)grid.x;  // grid.x arrives as the number of rows
   grid.x = (total + kFirXRows - 1) / kFirXRows;
-  if (!param) fir_x8_kernel<false, 0><<<grid, 128, smem, st>>>(in, out, taps, r, W, rows_per_plane, plane_rows, row_lo, total, ft);
+  if (!param) {
+    // long filters (taps in shared memory): two segment buffers of tile + steps floats can pass the 48 KB default;
+    // beyond the opt-in limit the launch itself fails and LLIE_LAUNCH reports it
+    if (smem > 48 * 1024) cudaFuncSetAttribute(fir_x8_kernel<false, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    fir_x8_kernel<false, 0><<<grid, 128, smem, st>>>(in, out, taps, r, W, rows_per_plane, plane_rows, row_lo, total, ft);
+  }
   else if (steps == 40) fir_x8_kernel<true, 40><<<grid, 128, smem, st>>>(in, out, taps, r, W, rows_per_plane, plane_rows, row_lo, total, ft);
   else if (steps == 64) fir_x8_kernel<true, 64><<<grid, 128, smem, st>>>(in, out, taps, r, W, rows_per_plane, plane_rows, row_lo, total, ft);
   else if (steps == 144) fir_x8_kernel<true, 144><<<grid, 128, smem, st>>>(in, out, taps, r, W, rows_per_plane, plane_rows, row_lo, total, ft);

@@ -47,6 +47,20 @@ def test_msrcr_golden_custom_scales(blur, name):
     assert np.abs(L.enhance(d["x"], "msrcr", p) - d["y"]).max() <= TOL_F32
 
 
+@pytest.mark.parametrize("h,w,sigma,truncate", [(48, 3840, 3000.0, 4.0), (32, 16384, 600.0, 4.0), (24, 1024, 2800.0, 8.0)])
+def test_msrcr_long_filters(h, w, sigma, truncate):
+    """filters too long for the by-value taps take fir_x8_kernel<false, 0>, whose register-staged
+    row fetch covered only 1280 samples; a longer segment (tile + 2 r + 8: 1752, 1336 and 2872 here) left shared
+    memory unwritten.  The last case also needs more than 48 KB of dynamic shared memory."""
+    x = oracle.synth_lowlight(h, w, 5)
+    p = dict(sigmas=(15.0, 80.0, sigma), weights=(0.3, 0.3, 0.4), truncate=truncate)
+    ref = oracle.msrcr(x, p, mode="fft")
+    y = L.enhance(x, "msrcr", p)
+    assert np.isfinite(y).all() and np.abs(y - ref).max() <= TOL_F32
+    y2 = L.enhance(x, "msrcr", p)      # second run of the same shape: same bits (no stale shared memory involved)
+    assert np.array_equal(y, y2)
+
+
 @pytest.mark.parametrize("blur", ["pyramid", "direct"])
 def test_msrcr_config0_600x400(blur):
     """BASELINE configs[0]: 600x400, sigma 15/80/250 -- every radius exceeds the image on one axis."""
@@ -630,6 +644,32 @@ def test_msrcr_tiled_vs_oracle_and_odd_sizes():
     p = dict(sigmas=(20.0, 60.0), weights=(0.4, 0.6), gain=0.5, offset=120.0)
     ref = oracle.msrcr(x, p, mode="fft")
     assert np.abs(_run_tiled(x, 3, p) - ref).max() <= TOL_F32
+
+
+def test_msrcr_tiled_graph_survives_a_plan_change():
+    """the captured graphs of the row-tiled path hold the plan's tap addresses.  Same buffers and
+    parameters P three times (plain, capture, replay), then other parameters on the same ctxs (the plan and its taps
+    are freed and rebuilt twice), then P again with the same buffers: must not replay the graph with the old taps."""
+    x = oracle.synth_lowlight(600, 520, 13)
+    xd = torch.from_numpy(x).cuda()
+    shards = [xd[r0:r0 + r].contiguous() for r0, r in L.tile_rows(600, 3)]
+    outs = [torch.empty_like(t) for t in shards]
+    for _ in range(3):
+        L.msrcr_tiled(shards, None, outs=outs)
+    y0 = torch.cat(outs, 0).clone()
+    assert np.abs(y0.cpu().numpy() - oracle.msrcr(x, mode="fft")).max() <= TOL_F32
+    other = [torch.empty_like(t) for t in shards]
+    q = dict(sigmas=(20.0, 60.0), weights=(0.4, 0.6))
+    r = dict(sigmas=(30.0, 100.0, 300.0), weights=(0.2, 0.3, 0.5))
+    L.msrcr_tiled(shards, q, outs=other)
+    yq = torch.cat(other, 0).cpu().numpy()
+    L.msrcr_tiled(shards, r, outs=other)
+    assert np.abs(yq - oracle.msrcr(x, q, mode="fft")).max() <= TOL_F32
+    for t in outs:
+        t.fill_(float("nan"))
+    for _ in range(3):
+        L.msrcr_tiled(shards, None, outs=outs)
+        assert torch.equal(torch.cat(outs, 0), y0)
 
 
 def test_msrcr_tiled_large_seams_windowed_oracle():
