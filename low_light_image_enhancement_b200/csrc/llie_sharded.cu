@@ -251,7 +251,15 @@ int llie_enhance_sharded(llie_ctx* const* ctxs, int n_dev, int method, int io_ty
         rc[d] = LLIE_E_CUDA;
       }
     }
-    if (rc[d] != LLIE_OK) msg[d] = last_error_text();
+    if (rc[d] != LLIE_OK) {
+      msg[d] = last_error_text();
+      // A shard that failed half-way may still have copies and kernels in flight that touch the caller's buffers:
+      // drain this device's three streams before the caller learns of the error and frees or reuses them (the
+      // output of a failed call is undefined).  Errors of the drain itself add nothing to the one being reported.
+      for (cudaStream_t s : {ctx->stream, ctx->sh_h2d, ctx->sh_d2h})
+        if (s) (void)cudaStreamSynchronize(s);
+      (void)cudaGetLastError();
+    }
     if (prev >= 0) cudaSetDevice(prev);
   };
   for (int d = 0; d < n_dev; ++d) {

@@ -9,6 +9,11 @@
 
 using namespace llie;
 
+namespace {
+std::mutex g_peer_mu;
+uint64_t g_peer_enabled[64];  // bit b of entry a: this process has enabled peer access a -> b
+}  // namespace
+
 extern "C" int llie_msrcr_tiled(llie_ctx* const* ctxs, int n_dev, const float* const* in_shard, float* const* out_shard,
                                 const int* row0, const int* rows, int h_total, int w, const llie_msrcr_params* params) {
   LLIE_REQUIRE(ctxs && in_shard && out_shard && row0 && rows && params, LLIE_E_ARG, "null argument");
@@ -52,29 +57,31 @@ extern "C" int llie_msrcr_tiled(llie_ctx* const* ctxs, int n_dev, const float* c
   for (int d = 0; d < n_dev; ++d) devs.insert(ctxs[d]->device);
   LLIE_REQUIRE(devs.size() == 1 || (int)devs.size() == n_dev, LLIE_E_ARG,
                "ctxs must live on %d distinct devices, or all on one device", n_dev);
-  int prev = 0;
-  LLIE_CUDA_OK(cudaGetDevice(&prev));
   if (devs.size() > 1) {
-    for (int a : devs)
-      for (int b : devs) {
-        if (a == b) continue;
-        int can = 0;
-        LLIE_CUDA_OK(cudaDeviceCanAccessPeer(&can, a, b));
-        if (!can) {
-          cudaSetDevice(prev);
-          set_error("device %d cannot access device %d peer-to-peer (NVLink P2P is required; there is no fallback)", a, b);
-          return LLIE_E_NOPEER;
+    // Peer access is a property of the process: pairs enabled by an earlier call are remembered, so the steady state
+    // costs no CUDA call at all (8 GPUs: 56 ordered pairs x two runtime calls per llie_msrcr_tiled before).
+    int prev = 0;
+    LLIE_CUDA_OK(cudaGetDevice(&prev));
+    const int rc = [&]() -> int {
+      std::lock_guard<std::mutex> lk(g_peer_mu);
+      for (int a : devs)
+        for (int b : devs) {
+          if (a == b || (a < 64 && b < 64 && (g_peer_enabled[a] >> b & 1))) continue;
+          int can = 0;
+          LLIE_CUDA_OK(cudaDeviceCanAccessPeer(&can, a, b));
+          LLIE_REQUIRE(can, LLIE_E_NOPEER,
+                       "device %d cannot access device %d peer-to-peer (NVLink P2P is required; there is no fallback)", a, b);
+          LLIE_CUDA_OK(cudaSetDevice(a));
+          const cudaError_t e = cudaDeviceEnablePeerAccess(b, 0);
+          if (e == cudaErrorPeerAccessAlreadyEnabled) (void)cudaGetLastError();
+          else LLIE_REQUIRE(e == cudaSuccess, LLIE_E_NOPEER, "cudaDeviceEnablePeerAccess(%d -> %d) failed: %s", a, b,
+                            cudaGetErrorString(e));
+          if (a < 64 && b < 64) g_peer_enabled[a] |= 1ull << b;
         }
-        LLIE_CUDA_OK(cudaSetDevice(a));
-        cudaError_t e = cudaDeviceEnablePeerAccess(b, 0);
-        if (e == cudaErrorPeerAccessAlreadyEnabled) (void)cudaGetLastError();
-        else if (e != cudaSuccess) {
-          cudaSetDevice(prev);
-          set_error("cudaDeviceEnablePeerAccess(%d -> %d) failed: %s", a, b, cudaGetErrorString(e));
-          return LLIE_E_NOPEER;
-        }
-      }
-    LLIE_CUDA_OK(cudaSetDevice(prev));
+      return LLIE_OK;
+    }();
+    cudaSetDevice(prev);  // on every path: a failed check must not leave the caller on another device
+    LLIE_TRY(rc);
   }
   return msrcr_tiled_run(ctxs, n_dev, in_shard, out_shard, row0, rows, h_total, w, *params);
 }
