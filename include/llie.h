@@ -204,6 +204,14 @@ int llie_dce_forward_u8(llie_ctx* ctx, const uint8_t* in, uint8_t* out, float* m
 int llie_dce_forward_u16(llie_ctx* ctx, const uint16_t* in, uint16_t* out, float* maps_or_null, int n, int h, int w,
                          int layout, const llie_dce_params* params, void* stream);
 
+/* bfloat16 images ("bf16 torch tensors allowed for zero_dce bf16"): in / out are n*h*w*3 bfloat16
+ * values in [0, 1] (the bit layout of __nv_bfloat16 / torch.bfloat16), read by the first kernel and rounded to nearest
+ * even by the last one, so the image costs 2 bytes per sample on HBM and on PCIe.  LLIE_BF16 precision only; the curve
+ * maps, if requested, stay fp32.  Internally nothing changes: the input is rounded to bf16 for the tensor cores anyway,
+ * so the only extra error against llie_dce_forward is the rounding of the stored result (<= 2^-9 relative). */
+int llie_dce_forward_bf16io(llie_ctx* ctx, const void* in, void* out, float* maps_or_null, int n, int h, int w,
+                            int layout, const llie_dce_params* params, void* stream);
+
 /* Test hook: after a LLIE_BF16 or LLIE_F32 forward, copies inter-layer activation `which` (1..6 = x1..x6 of
  * SURVEY.md 9.2) of frame `frame` of the last processed chunk to HOST memory as fp32 [32][h][w]. */
 int llie_debug_dce_activation(llie_ctx* ctx, int which, int frame, float* host_out);
@@ -233,6 +241,7 @@ int llie_dce_curves(llie_ctx* ctx, const float* in, const float* maps, float* ou
 #define LLIE_IO_F32 0
 #define LLIE_IO_U8 1
 #define LLIE_IO_U16 2
+#define LLIE_IO_BF16 3 /* Zero-DCE (LLIE_BF16 precision) only */
 #define LLIE_SHARD_DEVICE 0
 #define LLIE_SHARD_HOST 1
 int llie_enhance_sharded(llie_ctx* const* ctxs, int n_dev, int method, int io_type, const void* const* in_per_dev,

@@ -9,7 +9,8 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libllie.so")
+# LLIE_LIB_PATH: test tooling only (tools/ovf_check.sh runs the suite on a variant build); unset = the in-tree build
+LIB_PATH = os.environ.get("LLIE_LIB_PATH") or os.path.join(HERE, "libllie.so")
 
 OK, E_ARG, E_SHAPE, E_DTYPE, E_CUDA, E_NOPEER, E_NOMEM, E_STATE = 0, -1, -2, -3, -4, -5, -6, -7
 NHWC, NCHW = 0, 1
@@ -74,6 +75,7 @@ EXPORTS = {
     "llie_msrcr_u8": (_I, [_VP, _VP, _VP, _I, _I, _I, _I, C.POINTER(MsrcrParams), _VP]),
     "llie_dce_forward_u8": (_I, [_VP, _VP, _VP, _VP, _I, _I, _I, _I, C.POINTER(DceParams), _VP]),
     "llie_msrcr_u16": (_I, [_VP, _VP, _VP, _I, _I, _I, _I, C.POINTER(MsrcrParams), _VP]),
+    "llie_dce_forward_bf16io": (_I, [_VP, _VP, _VP, _VP, _I, _I, _I, _I, C.POINTER(DceParams), _VP]),
     "llie_dce_forward_u16": (_I, [_VP, _VP, _VP, _VP, _I, _I, _I, _I, C.POINTER(DceParams), _VP]),
     "llie_msrcr_plan_query": (_I, [_F, _F, C.POINTER(_I), C.POINTER(C.c_double), C.POINTER(_I),
                                    C.POINTER(C.c_double)]),

@@ -130,6 +130,9 @@ def shard_slice(n: int, rank: int, world: int) -> slice:
     return slice(start, start + base + (1 if rank < rem else 0))
 
 
+_IMAGE_DTYPES = (torch.float32, torch.uint8, torch.uint16, torch.bfloat16)   # bfloat16: zero_dce, precision bf16
+
+
 def _msrcr_struct(params: dict | None) -> MsrcrParams:
     d = default_msrcr_params()
     if params:
@@ -273,7 +276,8 @@ class Enhancer:
         _lib.check(fn(self._h, x.data_ptr(), out.data_ptr(), n, h, w, layout, C.byref(p), stream_ptr))
 
     def dce_device(self, x, out, maps, n, h, w, layout, p: DceParams, stream_ptr):
-        fn = {torch.uint8: self._lib.llie_dce_forward_u8, torch.uint16: self._lib.llie_dce_forward_u16}.get(x.dtype, self._lib.llie_dce_forward)
+        fn = {torch.uint8: self._lib.llie_dce_forward_u8, torch.uint16: self._lib.llie_dce_forward_u16,
+              torch.bfloat16: self._lib.llie_dce_forward_bf16io}.get(x.dtype, self._lib.llie_dce_forward)
         _lib.check(fn(self._h, x.data_ptr(), out.data_ptr(), maps.data_ptr() if maps is not None else None,
                       n, h, w, layout, C.byref(p), stream_ptr))
 
@@ -290,8 +294,9 @@ class Enhancer:
         if not is_np and not isinstance(images, torch.Tensor):
             raise TypeError("images must be a numpy.ndarray or a torch.Tensor")
         t = torch.from_numpy(images) if is_np else images
-        if t.dtype not in (torch.float32, torch.uint8, torch.uint16):
-            raise TypeError(f"images must be float32 (values in [0,1]), uint8 (b / 255) or uint16 (b / 65535), got {t.dtype}")
+        if t.dtype not in _IMAGE_DTYPES or (t.dtype == torch.bfloat16 and method != "zero_dce"):
+            raise TypeError(f"images must be float32 (values in [0,1]), uint8 (b / 255), uint16 (b / 65535) or, for "
+                            f"zero_dce with precision='bf16', bfloat16 tensors; got {t.dtype} for {method}")
         if not t.is_contiguous():
             raise ValueError("images must be contiguous")
         n, h, w, layout, batched = _resolve_layout(t.shape, params.get("layout"))
@@ -359,7 +364,7 @@ class Enhancer:
                 t = torch.from_numpy(f) if is_np else f
                 if not isinstance(t, torch.Tensor) or t.is_cuda:
                     raise TypeError("enhance_stream takes host frames (numpy.ndarray or CPU torch.Tensor)")
-                if t.dtype not in (torch.float32, torch.uint8, torch.uint16) or not t.is_contiguous():
+                if t.dtype not in _IMAGE_DTYPES or not t.is_contiguous():
                     raise TypeError("frames must be contiguous float32, uint8 or uint16")
                 if shape0 is None:
                     shape0 = (tuple(t.shape), t.dtype)
@@ -627,7 +632,7 @@ def _group_enhancers(devices: Sequence[int]) -> list:
 
 
 def _io_code(dtype) -> int:
-    return {torch.float32: 0, torch.uint8: 1, torch.uint16: 2}[dtype]
+    return {torch.float32: 0, torch.uint8: 1, torch.uint16: 2, torch.bfloat16: 3}[dtype]
 
 
 def enhance_sharded(images, method: str, params: dict | None = None, *, devices: Sequence[int] | None = None, out=None):
@@ -668,8 +673,8 @@ def enhance_sharded(images, method: str, params: dict | None = None, *, devices:
         ts = [first]
     devices = [int(d) for d in devices]
     for t in ts:
-        if t.dtype not in (torch.float32, torch.uint8, torch.uint16) or not t.is_contiguous() or t.dim() != 4:
-            raise TypeError("images must be contiguous 4-D float32 / uint8 / uint16 batches")
+        if t.dtype not in _IMAGE_DTYPES or not t.is_contiguous() or t.dim() != 4:
+            raise TypeError("images must be contiguous 4-D float32 / uint8 / uint16 (zero_dce: also bfloat16) batches")
         if t.dtype != first.dtype or tuple(t.shape[1:]) != tuple(first.shape[1:]):
             raise ValueError("all shards must share dtype and image shape")
     _, h, w, layout, _ = _resolve_layout(first.shape, params.get("layout"))
@@ -724,7 +729,8 @@ def enhance(images, method: str, params: dict | None = None, *, out=None, device
 
     images : numpy.ndarray or torch.Tensor, float32 in [0, 1], uint8 or uint16 (an integer b means b / 255 or
              b / 65535; the result is rint(255 * value) or rint(65535 * value) in the same type, converted inside the
-             first / last kernel), shape (H,W,3), (N,H,W,3) or
+             first / last kernel) -- or, for 'zero_dce' with precision='bf16', torch.bfloat16 tensors in [0, 1]
+             (2 bytes per sample on the host link; result rounded to bfloat16) --, shape (H,W,3), (N,H,W,3) or
              (N,3,H,W) (params['layout'] = 'NHWC' | 'NCHW' when the shape is ambiguous).
              CUDA tensors are processed in place on their device and stream (zero copy); NumPy
              arrays and CPU tensors are staged through pinned memory.

@@ -168,7 +168,7 @@ struct ChainArgs {
   ImgView vx, vm;
   int iters;
   float sign;
-  int u8;  // x / y are integer images: 1 = uint8_t (value = byte / 255; stored as rint(255 * value)), 2 = uint16_t (65535)
+  int u8;  // sample type of x / y: 0 = float, 1 = uint8_t (value = byte / 255; stored as rint(255 * value)), 2 = uint16_t (65535), 3 = bfloat16
   int N, H, W, Wp, strips, segs, seg_rows, units;
 };
 
@@ -615,6 +615,9 @@ __device__ __forceinline__ void epilogue_loop(const ChainArgs& a, const Smem<GID
           } else if (a.u8 == 2) {
 #pragma unroll
             for (int c = 0; c < 3; ++c) p[c] = (float)__ldg(reinterpret_cast<const uint16_t*>(a.x) + bx + c * a.vx.sc) * (1.f / 65535.f);
+          } else if (a.u8 == 3) {
+#pragma unroll
+            for (int c = 0; c < 3; ++c) p[c] = __bfloat162float(__ldg(reinterpret_cast<const __nv_bfloat16*>(a.x) + bx + c * a.vx.sc));
           } else {
 #pragma unroll
             for (int c = 0; c < 3; ++c) p[c] = __ldg(a.x + bx + c * a.vx.sc);
@@ -636,6 +639,9 @@ __device__ __forceinline__ void epilogue_loop(const ChainArgs& a, const Smem<GID
 #pragma unroll
             for (int c = 0; c < 3; ++c)
               reinterpret_cast<uint16_t*>(a.y)[bx + c * a.vx.sc] = (uint16_t)__float2uint_rn(65535.f * __saturatef(p[c]));
+          } else if (a.u8 == 3) {
+#pragma unroll
+            for (int c = 0; c < 3; ++c) reinterpret_cast<__nv_bfloat16*>(a.y)[bx + c * a.vx.sc] = __float2bfloat16_rn(p[c]);
           } else {
 #pragma unroll
             for (int c = 0; c < 3; ++c) a.y[bx + c * a.vx.sc] = p[c];

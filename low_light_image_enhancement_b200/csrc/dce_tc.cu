@@ -36,7 +36,8 @@ dce_pack_input_kernel(const TIn* __restrict__ x, ImgView v, __nv_bfloat16* __res
   const long long n = blockIdx.z;
   if (xx >= W) return;
   const TIn* p = x + n * v.sn + (long long)yy * v.sy + (long long)xx * v.sx;
-  constexpr float kIn = sizeof(TIn) == 1 ? 1.f / 255.f : (sizeof(TIn) == 2 ? 1.f / 65535.f : 1.f);  // an integer b means b / 255 (65535)
+  // an integer b means b / 255 (65535); float and bfloat16 samples are the value itself
+  constexpr float kIn = std::is_same<TIn, uint8_t>::value ? 1.f / 255.f : (std::is_same<TIn, uint16_t>::value ? 1.f / 65535.f : 1.f);
   const float r = kIn * (float)__ldg(p), g = kIn * (float)__ldg(p + v.sc), b = kIn * (float)__ldg(p + 2 * v.sc);
   const __nv_bfloat162 rg = __floats2bfloat162_rn(r, g);
   uint4 o;
@@ -255,6 +256,9 @@ static int dce_forward_tc(llie_ctx* ctx, const void* in_v, void* out_v, float* m
     else if (iot == kIoU16)
       LLIE_LAUNCH(ctx, s2, "dce_pack_input_kernel",
                   (dce_pack_input_kernel<false, uint16_t><<<grid, 256, 0, s2>>>(reinterpret_cast<const uint16_t*>(x), vx, pk.xin, h, w, wp)));
+    else if (iot == kIoBF16)
+      LLIE_LAUNCH(ctx, s2, "dce_pack_input_kernel",
+                  (dce_pack_input_kernel<false, __nv_bfloat16><<<grid, 256, 0, s2>>>(reinterpret_cast<const __nv_bfloat16*>(x), vx, pk.xin, h, w, wp)));
     else
       LLIE_LAUNCH(ctx, s2, "dce_pack_input_kernel",
                   (dce_pack_input_kernel<false, float><<<grid, 256, 0, s2>>>(x, vx, pk.xin, h, w, wp)));
@@ -269,7 +273,7 @@ static int dce_forward_tc(llie_ctx* ctx, const void* in_v, void* out_v, float* m
     memset(&a, 0, sizeof(a));
     a.N = nb; a.H = h; a.W = w; a.Wp = wp;
     a.x = x; a.y = reinterpret_cast<float*>(static_cast<char*>(out_v) + (size_t)n0 * h * w * 3 * esz);
-    a.u8 = iot;  // kIoF32 / kIoU8 / kIoU16 = 0 / 1 / 2
+    a.u8 = iot;  // kIoF32 / kIoU8 / kIoU16 / kIoBF16 = 0 / 1 / 2 / 3
     a.maps = maps ? maps + n0 * (long long)h * w * 24 : nullptr;
     a.vx = vx; a.vm = vm; a.iters = p.iters; a.sign = p.curve_sign >= 0 ? 1.f : -1.f;
     // stage slot <- layer l (0..6): weights, bias, HBM destination (nullptr = keep on chip)
@@ -322,7 +326,7 @@ static int dce_forward_tc(llie_ctx* ctx, const void* in_v, void* out_v, float* m
       single(0, pk.xin, nullptr, x1); LLIE_TRY((launch_chain<3>(ctx, st, a, "dce_conv_tc_first_kernel")));
       single(1, x1, nullptr, x2); LLIE_TRY((launch_chain<4>(ctx, st, a, "dce_conv_tc_k32_kernel")));
       single(2, x2, nullptr, x3); LLIE_TRY((launch_chain<4>(ctx, st, a, "dce_conv_tc_k32_kernel")));
-      single(3, x3, nullptr, x4); LLIE_TRY((launch_chain<11>(ctx, st, a, "dce_conv_tc_k32_kernel")));  // summed as inside conv4+5
+      single(3, x3, nullptr, x4); LLIE_TRY((launch_chain<11>(ctx, st, a, "dce_conv_tc_k32_kernel")));  // group 11 = group 4 unless built with -DLLIE_OVF=1 (overflow slots)
       single(4, x3, x4, x5); LLIE_TRY((launch_chain<5>(ctx, st, a, "dce_conv_tc_k64_kernel")));
       single(5, x2, x5, x6); LLIE_TRY((launch_chain<5>(ctx, st, a, "dce_conv_tc_k64_kernel")));
       single(6, x1, x6, nullptr); LLIE_TRY((launch_chain<6>(ctx, st, a, "dce_conv_tc_last_kernel")));

@@ -388,13 +388,18 @@ static int dce_int(llie_ctx* ctx, const void* in, void* out, int iot, float* map
   LLIE_REQUIRE(ctx, LLIE_E_ARG, "null ctx");
   LLIE_TRY(check_batch(in, out, n, h, w, layout));
   LLIE_TRY(check_dce_params(params));
-  LLIE_REQUIRE(params->precision == LLIE_BF16, LLIE_E_DTYPE, "integer images are supported by the LLIE_BF16 path only");
+  LLIE_REQUIRE(params->precision == LLIE_BF16, LLIE_E_DTYPE, "integer and bfloat16 images are supported by the LLIE_BF16 path only");
   if (n == 0) return LLIE_OK;
   DeviceGuard g(ctx->device);
   cudaStream_t st = stream ? (cudaStream_t)stream : ctx->stream;
   LLIE_TRY(dce_forward_int(ctx, in, out, iot, maps_or_null, n, h, w, layout, *params, st));
   if (!stream) LLIE_CUDA_OK(cudaStreamSynchronize(st));
   return LLIE_OK;
+}
+
+int llie_dce_forward_bf16io(llie_ctx* ctx, const void* in, void* out, float* maps_or_null, int n, int h, int w,
+                            int layout, const llie_dce_params* params, void* stream) {
+  return dce_int(ctx, in, out, kIoBF16, maps_or_null, n, h, w, layout, params, stream);
 }
 
 int llie_dce_forward_u8(llie_ctx* ctx, const uint8_t* in, uint8_t* out, float* maps_or_null, int n, int h, int w,

@@ -216,9 +216,10 @@ inline int check_launch(llie_ctx* ctx, const char* what, cudaStream_t st = nullp
   } while (0)
 
 // image sample types of the typed entry points: float in [0, 1], or an integer b meaning b / io_levels
-constexpr int kIoF32 = 0, kIoU8 = 1, kIoU16 = 2;
+// (kIoBF16: a bfloat16 in [0, 1] -- Zero-DCE with bf16 operands only)
+constexpr int kIoF32 = 0, kIoU8 = 1, kIoU16 = 2, kIoBF16 = 3;
 inline float io_levels(int iot) { return iot == kIoU8 ? 255.f : (iot == kIoU16 ? 65535.f : 1.f); }
-inline size_t io_bytes(int iot) { return iot == kIoU8 ? 1 : (iot == kIoU16 ? 2 : 4); }
+inline size_t io_bytes(int iot) { return iot == kIoU8 ? 1 : ((iot == kIoU16 || iot == kIoBF16) ? 2 : 4); }
 
 // kernels' host entry points (one per .cu)
 int msrcr_direct_run(llie_ctx* ctx, const float* in, float* out, int n, int h, int w, int layout,

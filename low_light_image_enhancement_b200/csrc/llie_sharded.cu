@@ -32,6 +32,7 @@ int run_frames(llie_ctx* ctx, const ShardJob& j, const void* in, void* out, int 
     return llie_msrcr_f32(ctx, (const float*)in, (float*)out, n, j.h, j.w, j.layout, &j.mp, st);
   }
   if (j.iot == LLIE_IO_U8) return llie_dce_forward_u8(ctx, (const uint8_t*)in, (uint8_t*)out, nullptr, n, j.h, j.w, j.layout, &j.dp, st);
+  if (j.iot == LLIE_IO_BF16) return llie_dce_forward_bf16io(ctx, in, out, nullptr, n, j.h, j.w, j.layout, &j.dp, st);
   if (j.iot == LLIE_IO_U16) return llie_dce_forward_u16(ctx, (const uint16_t*)in, (uint16_t*)out, nullptr, n, j.h, j.w, j.layout, &j.dp, st);
   return llie_dce_forward(ctx, (const float*)in, (float*)out, nullptr, n, j.h, j.w, j.layout, &j.dp, st);
 }
@@ -202,7 +203,9 @@ int llie_enhance_sharded(llie_ctx* const* ctxs, int n_dev, int method, int io_ty
   LLIE_REQUIRE(ctxs && in_per_dev && out_per_dev && n_per_dev && params, LLIE_E_ARG, "null argument");
   LLIE_REQUIRE(n_dev >= 1 && n_dev <= 64, LLIE_E_ARG, "n_dev %d out of range [1,64]", n_dev);
   LLIE_REQUIRE(method == LLIE_METHOD_MSRCR || method == LLIE_METHOD_ZERO_DCE, LLIE_E_ARG, "unknown method %d", method);
-  LLIE_REQUIRE(io_type == LLIE_IO_F32 || io_type == LLIE_IO_U8 || io_type == LLIE_IO_U16, LLIE_E_DTYPE, "unknown io_type %d", io_type);
+  LLIE_REQUIRE(io_type == LLIE_IO_F32 || io_type == LLIE_IO_U8 || io_type == LLIE_IO_U16 || io_type == LLIE_IO_BF16, LLIE_E_DTYPE,
+               "unknown io_type %d", io_type);
+  LLIE_REQUIRE(io_type != LLIE_IO_BF16 || method == LLIE_METHOD_ZERO_DCE, LLIE_E_DTYPE, "bfloat16 images are a Zero-DCE format; MSRCR takes float32, uint8 or uint16");
   LLIE_REQUIRE(where == LLIE_SHARD_DEVICE || where == LLIE_SHARD_HOST, LLIE_E_ARG, "unknown buffer location %d", where);
   LLIE_REQUIRE(h > 0 && w > 0 && (long long)h * w <= (1ll << 31), LLIE_E_SHAPE, "bad shape h=%d w=%d", h, w);
   LLIE_REQUIRE(layout == LLIE_NHWC || layout == LLIE_NCHW, LLIE_E_ARG, "unknown layout %d", layout);

@@ -480,6 +480,40 @@ def test_dce_u16_matches_oracle(blob):
         L.enhance(x, "msrcr", dict(blur="direct"))
 
 
+@pytest.mark.parametrize("layout", ["NHWC", "NCHW"])
+def test_dce_bf16_tensor_io(layout, blob):
+    """"bf16 torch tensors allowed for zero_dce bf16".  The network rounds its input to bf16 anyway, so
+    bf16 frames give exactly the fp32-I/O result of the same (bf16-representable) pixels, rounded once to bf16 on the
+    way out; against the fp64 oracle that rounding (2^-9 relative) still clears the 50 dB bar."""
+    prm = dict(weights=blob, precision="bf16", return_maps=True)
+    x = np.stack([oracle.synth_lowlight(135, 240, 30 + i) for i in range(3)])
+    xb = torch.from_numpy(x).to(torch.bfloat16)
+    if layout == "NCHW":
+        xb = xb.permute(0, 3, 1, 2).contiguous()
+        prm["layout"] = "NCHW"
+    xd = xb.cuda()
+    y, maps = L.enhance(xd, "zero_dce", prm)
+    assert y.dtype == torch.bfloat16 and y.shape == xd.shape and maps.dtype == torch.float32
+    yf, maps_f = L.enhance(xd.float(), "zero_dce", prm)
+    assert torch.equal(y, yf.to(torch.bfloat16)) and torch.equal(maps, maps_f)
+    ws = oracle.init_weights(0)
+    x64 = xb.float().numpy() if layout == "NHWC" else xb.float().permute(0, 2, 3, 1).numpy()
+    yn = y.float().cpu().numpy() if layout == "NHWC" else y.float().permute(0, 2, 3, 1).cpu().numpy()
+    for i in range(3):
+        assert psnr(yn[i], oracle.zero_dce(x64[i], ws)) >= PSNR_BF16
+    # host tensors (pageable and pinned) take the staged pipeline and the sharder with 2 bytes per sample
+    p2 = {k: v for k, v in prm.items() if k != "return_maps"}
+    assert torch.equal(L.enhance(xb, "zero_dce", p2), y.cpu())
+    assert torch.equal(L.enhance(xb.pin_memory(), "zero_dce", p2, devices=[0, 0]), y.cpu())
+    outs = L.enhance([xd[:2].contiguous(), xd[2:].contiguous()], "zero_dce", p2, devices=[0, 0])
+    assert torch.equal(torch.cat(outs, 0), y)
+    # bf16 frames are a Zero-DCE / bf16-operand format only
+    with pytest.raises(L.LlieError):
+        L.enhance(xd, "zero_dce", dict(p2, precision="fp32"))
+    with pytest.raises(TypeError):
+        L.enhance(xd, "msrcr", {k: v for k, v in p2.items() if k == "layout"})
+
+
 def test_u8_rejections_and_host_pipeline(blob):
     x = _u8_image(64, 96, 9)
     with pytest.raises(L.LlieError):
