@@ -17,7 +17,8 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 
 UNIT = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "Tbyte": 1e12}
-CHAIN = {"0": "dce_chain_c123_kernel", "1": "dce_chain_c45_kernel", "2": "dce_chain_c67_kernel"}
+CHAIN = {"0": "dce_chain_c123_kernel", "1": "dce_chain_c45_kernel", "2": "dce_chain_c67_kernel",
+         "7": "dce_split_first_kernel", "8": "dce_split_k32_kernel", "9": "dce_split_k64_kernel", "10": "dce_split_last_kernel"}
 
 
 def bench_name(ncu_name: str) -> str:
@@ -46,6 +47,7 @@ def main():
     ap.add_argument("--dce", nargs=2, metavar=("CSV", "FRAMES"))
     ap.add_argument("--msrcr", nargs=2, metavar=("CSV", "FRAMES"))
     ap.add_argument("--msrcr-u8", nargs=2, metavar=("CSV", "FRAMES"))
+    ap.add_argument("--dce32", nargs=2, metavar=("CSV", "FRAMES"), help="Zero-DCE fp32 (hi/lo split) on 1080p frames")
     ap.add_argument("--capture", default="")
     a = ap.parse_args()
     import bench
@@ -55,6 +57,12 @@ def main():
         k = per_kernel(a.dce[0])
         doc["kernels"].update({n: b / px for n, b in k.items()})
         doc["dce_step_bytes_per_px"] = sum(k.values()) / px
+    if a.dce32:
+        px = int(a.dce32[1]) * 1920 * 1080
+        k = per_kernel(a.dce32[0])
+        k = {("dce_pack_input_split_kernel" if n == "dce_pack_input_kernel" else n): b for n, b in k.items()}
+        doc["kernels"].update({n: b / px for n, b in k.items()})
+        doc["dce32_step_bytes_per_px"] = sum(k.values()) / px
     if a.msrcr:
         px = int(a.msrcr[1]) * 3840 * 2160
         k = per_kernel(a.msrcr[0])
